@@ -1,0 +1,198 @@
+/*
+ * swarm_b200.h -- C-ABI of libswarm_b200.so, the B200-native (sm_100a) engine for
+ * the SwarmRL rollout hot path.
+ *
+ * The reference reaches its physics through the Python/Cython handles of
+ * `espressomd` (a third-party C++ package); every entry point below cites the
+ * reference call site it replaces (paths relative to /root/reference).  All
+ * pointers named *_dev are CUDA device pointers owned by the caller (torch
+ * tensors on the Python side, exchanged zero-copy); *_host are host pointers.
+ * No call throws; every call returns 0 on success or a negative swarm_status_t
+ * and leaves a message for swarm_last_error().  Calls that take a `stream`
+ * only enqueue work on that cudaStream_t (passed as void*) and do not
+ * synchronise unless stated.
+ *
+ * State layout (HBM, structure of arrays, fp64, one element per particle,
+ * particle index == particle id == creation order, as in ESPResSo):
+ *   x,y,z            unfolded positions           (espresso.py:1122,1333)
+ *   theta            2-D orientation angle; director = (cos, sin, 0)
+ *   q0..q3           3-D orientation quaternion; director = body z axis
+ *   vx..vz, wx..wz   velocity / lab angular velocity, materialised at the end
+ *                    of every swarm_run chunk
+ *   f_swim           Action.force  (espresso.py:1228)
+ *   tqx..tqz         Action.torque (espresso.py:1229-1235), lab frame
+ *   fex..fez         ext_force     (espresso.py:834-851); may be NULL
+ *   species          int32 index into the species table (see swarm_set_species)
+ */
+#ifndef SWARM_B200_H
+#define SWARM_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SWARM_MAX_SPECIES 16
+#define SWARM_MAX_TYPES 8
+#define SWARM_ABI_VERSION 1
+
+typedef enum {
+  SWARM_OK = 0,
+  SWARM_ERR_INVALID = -1,   /* bad argument (the reference raises ValueError) */
+  SWARM_ERR_STATE = -2,     /* call order violated (the reference raises RuntimeError) */
+  SWARM_ERR_CUDA = -3,      /* CUDA runtime error; message holds cudaGetErrorString */
+  SWARM_ERR_OVERFLOW = -4,  /* a fixed-capacity device structure overflowed */
+  SWARM_ERR_NOMEM = -5
+} swarm_status_t;
+
+typedef struct swarm swarm_t;
+
+/* espresso.py:143-152 (n_dims, seed), :267-270 (box, time_step, skin, periodicity),
+ * :1170-1186 (kT, thermostat seed). */
+typedef struct {
+  int32_t n_dims;        /* 2 or 3 */
+  int32_t periodic[3];
+  double box[3];
+  double dt;
+  double kT;
+  double skin;           /* Verlet skin; affects performance only (espresso.py:268-269) */
+  uint64_t seed;
+  int32_t device;        /* CUDA device ordinal */
+  int32_t max_neighbors; /* Verlet-list capacity per particle; 0 = default (16 in 2-D, 64 in 3-D) */
+  int32_t n_envs;        /* 1 = one swarm; >1 = that many independent environments of n/n_envs
+                            consecutive particles each (ensemble batching, BASELINE config 3) */
+  int32_t flags;         /* SWARM_FLAG_* */
+} swarm_config_t;
+
+#define SWARM_FLAG_NO_PERSISTENT 1 /* one launch per step instead of the cooperative kernel */
+
+typedef struct {
+  double *x, *y, *z;
+  double *theta;
+  double *q0, *q1, *q2, *q3;
+  double *vx, *vy, *vz;
+  double *wx, *wy, *wz;
+  int32_t *species;
+} swarm_state_dev_t;
+
+typedef struct {
+  double *f_swim;
+  double *tqx, *tqy, *tqz;
+  double *fex, *fey, *fez;     /* may be NULL */
+  double *ndx, *ndy, *ndz;     /* Action.new_direction; may be NULL */
+  int32_t *has_nd;             /* 1 where new_direction is set; may be NULL */
+} swarm_actions_dev_t;
+
+typedef struct {
+  int64_t steps_done;      /* integrator steps completed by the last swarm_run / swarm_relax */
+  int64_t steps_requested;
+  int64_t rebuilds;        /* neighbour-list rebuilds since creation */
+  int64_t launches;        /* kernels launched by this handle since creation */
+  int32_t overflow;        /* 1 if the Verlet list capacity was exceeded (run halted early) */
+  int32_t max_neighbors_seen;
+  int32_t capacity;        /* current Verlet capacity */
+  int32_t persistent;      /* 1 if the cooperative persistent kernel is in use */
+} swarm_stats_t;
+
+const char *swarm_last_error(void);
+int swarm_abi_version(void);
+
+/* espressomd.System(...) + _init_system  (espresso.py:193, 236-288) */
+int swarm_create(const swarm_config_t *cfg, swarm_t **out);
+int swarm_destroy(swarm_t *s);
+
+/* system.part.add(gamma=, gamma_rot=, mass=, rinertia=, type=) (espresso.py:416-441):
+ * one species per distinct property set.  gamma_t / gamma_r / rinertia are body-frame
+ * diagonals, 3 per species. */
+int swarm_set_species(swarm_t *s, int32_t n_species, const int32_t *type, const double *gamma_t,
+                      const double *gamma_r, const double *mass, const double *rinertia);
+
+/* non_bonded_inter[a,b].wca.set_params(sigma, epsilon)  (espresso.py:810-819); row-major T x T.
+ * cut = sigma * 2^(1/6). */
+int swarm_set_wca(swarm_t *s, int32_t n_types, const double *sigma, const double *eps, const double *cut);
+
+/* constraints.add(ShapeBasedConstraint(Wall...)) on the box faces (espresso.py:667-711). */
+int swarm_set_walls(swarm_t *s, int32_t enabled, const double *sigma, const double *eps, const double *cut);
+
+/* thermostat.set_brownian(kT, seed) (espresso.py:1180-1186) -- may be changed between runs */
+int swarm_set_thermostat(swarm_t *s, double kT, uint64_t seed);
+
+/* Bind caller-owned device arrays (no copy).  n must be a multiple of n_envs. */
+int swarm_bind_state(swarm_t *s, int64_t n, const swarm_state_dev_t *st);
+int swarm_bind_actions(swarm_t *s, const swarm_actions_dev_t *act);
+
+/* manage_forces' new_direction branch (espresso.py:1236-1249): 3-D overwrite the director,
+ * 2-D rotate in plane by acos(new . old) when > 1e-6, about sign((old x new)_z). */
+int swarm_apply_new_direction(swarm_t *s, void *stream);
+
+/* _remove_overlap: integrator.set_steepest_descent(f_max=0, gamma, max_displacement); run(n_iter)
+ * (espresso.py:1163-1167).  Simulation time is not advanced. */
+int swarm_relax(swarm_t *s, int64_t n_iter, double gamma, double max_disp, void *stream);
+
+/* integrator.run(n_steps)  (espresso.py:1304-1306) with the Brownian integrator: WCA + swim +
+ * external force/torque + Philox noise, fused.  step0 = global index of the first step (the
+ * Philox counter).  Enqueues only; call swarm_sync_stats to learn whether it ran to completion. */
+int swarm_run(swarm_t *s, int64_t n_steps, uint64_t step0, void *stream);
+
+/* Synchronises `stream` and reports counters of the last run. */
+int swarm_sync_stats(swarm_t *s, void *stream, swarm_stats_t *out);
+
+/* Grow the Verlet capacity after an overflow (invalidates the current list). */
+int swarm_set_max_neighbors(swarm_t *s, int32_t max_neighbors);
+
+/* director of every particle (particle.director), 3 arrays of n */
+int swarm_directors(swarm_t *s, double *ex_dev, double *ey_dev, double *ez_dev, void *stream);
+
+/* Neighbour-structure introspection for the bit-exact list checks (synchronous, host out).
+ * Rebuilds the Verlet list at the current positions, then writes every ordered pair (i,j)
+ * with r_ij < cut(type_i,type_j) + skin, sorted by (i,j).  *count = number of pairs. */
+int swarm_neighbors_dump(swarm_t *s, int32_t *pairs_host, int64_t cap, int64_t *count);
+/* cell index of every particle on a grid of nc[] cells over the box (the cell hash) */
+int swarm_cell_index(swarm_t *s, const int32_t nc[3], int32_t *cell_host);
+/* total force on every particle at the current state (debug / parity), device out */
+int swarm_forces(swarm_t *s, double *fx_dev, double *fy_dev, double *fz_dev, void *stream);
+
+/* Philox4x64-10 block and the 4 Gaussians of (seed, id, step, stream) -- parity hooks */
+int swarm_philox_host(const uint64_t ctr[4], const uint64_t key[2], uint64_t out[4]);
+int swarm_gaussians(swarm_t *s, int64_t n, uint64_t step, uint64_t stream_id, double *out4n_dev, void *stream);
+
+/* ---- observables / tasks -------------------------------------------------------------- */
+typedef enum { SWARM_DECAY_NONE = 0, SWARM_DECAY_LINEAR = 1, SWARM_DECAY_EXP = 2, SWARM_DECAY_INVERSE = 3 } swarm_decay_t;
+
+/* ConcentrationField.compute_observable (observables/concentration_field.py:84-138) and
+ * GradientSensing.__call__ (tasks/searching/gradient_sensing.py:92-150):
+ *   p = pos/box_length; d_now = |src - p|; d_prev = |src - hist|; hist <- p
+ *   out = scale * (decay(d_now) - decay(d_prev)), clipped to >= 0 when clip_nonneg.
+ * row_of_dev[i] = output row of particle i, or -1 to skip it (type filter).
+ * decay: NONE writes only d_now/d_prev; LINEAR c0 + c1 d; EXP c0 exp(-c1 d); INVERSE c0/(d + c1).
+ * hist_dev = [3][n].  out_dev / d_now_dev / d_prev_dev may be NULL. */
+int swarm_obs_field(swarm_t *s, const int32_t *row_of_dev, const double src[3], const double box_length[3],
+                    double *hist_dev, int32_t decay, double c0, double c1, double scale, int32_t clip_nonneg,
+                    double *out_dev, double *d_now_dev, double *d_prev_dev, void *stream);
+
+/* SubdividedVisionCones.compute_observable (observables/subdivided_vision_cones.py:83-258):
+ * out[row, cone, col] over every particle j (raw unfolded differences, observer included),
+ * col = type_col_dev[type_j] (or -1 = undetected), radius of the SEEN particle.
+ * out_dev = [rows][n_cones][n_cols], overwritten. */
+int swarm_obs_vision(swarm_t *s, const int32_t *row_of_dev, int64_t rows, double vision_range, double half_angle,
+                     int32_t n_cones, const double *radii_dev, const int32_t *type_col_dev, int32_t n_type_col,
+                     int32_t n_cols, double *out_dev, void *stream);
+
+/* PositionObservable (observables/position.py:32-60): out[row] = pos / box_length, [rows][3] */
+int swarm_obs_position(swarm_t *s, const int32_t *row_of_dev, const double box_length[3], double *out_dev, void *stream);
+
+/* Trainer.update_rl mean reward (trainers/trainer.py:92-95): out_dev[0] = sum, out_dev[1] = mean.
+ * Deterministic two-stage reduction. */
+int swarm_reduce_mean(swarm_t *s, const double *in_dev, int64_t n, double *out2_dev, void *stream);
+
+/* ---- host-buffer entry points (what a cgo/ctypes binding of the reference would call) --- */
+/* manage_forces: write f_swim and ext torque of every particle (espresso.py:1227-1235) */
+int swarm_set_actions_host(swarm_t *s, const double *f_swim_host, const double *torque3n_host, void *stream);
+/* get_particle_data (espresso.py:1320-1336): [n][3] row-major outputs; synchronises */
+int swarm_get_particle_data_host(swarm_t *s, double *pos_n3, double *vel_n3, double *dir_n3, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SWARM_B200_H */

@@ -1,0 +1,279 @@
+"""
+ctypes front-end of the CPU oracle (oracle/swarm_oracle.c).
+
+TEST INFRASTRUCTURE ONLY: imported by tests/, __graft_entry__.smoke() and the
+cpu_baseline / --impl reference legs of bench.py.  Nothing under swarmrl_b200/
+imports this module.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import pathlib
+import subprocess
+
+import numpy as np
+
+_HERE = pathlib.Path(__file__).resolve().parent
+_LIB_PATH = _HERE / "_build" / "libswarm_oracle.so"
+
+MAX_SPECIES = 64
+MAX_TYPES = 16
+
+
+def build(force: bool = False) -> pathlib.Path:
+    """Compile the oracle with the committed Makefile (gcc, OpenMP)."""
+    src = _HERE / "swarm_oracle.c"
+    if force or not _LIB_PATH.exists() or _LIB_PATH.stat().st_mtime < src.stat().st_mtime:
+        subprocess.run(["make", "-C", str(_HERE), "-B"], check=True, capture_output=True)
+    return _LIB_PATH
+
+
+class Params(C.Structure):
+    _fields_ = [
+        ("n_dims", C.c_int),
+        ("periodic", C.c_int * 3),
+        ("box", C.c_double * 3),
+        ("dt", C.c_double),
+        ("kT", C.c_double),
+        ("seed", C.c_uint64),
+        ("n_species", C.c_int),
+        ("n_types", C.c_int),
+        ("sp_type", C.c_int * MAX_SPECIES),
+        ("sp_gamma_t", (C.c_double * 3) * MAX_SPECIES),
+        ("sp_gamma_r", (C.c_double * 3) * MAX_SPECIES),
+        ("sp_mass", C.c_double * MAX_SPECIES),
+        ("sp_rinertia", (C.c_double * 3) * MAX_SPECIES),
+        ("wca_sigma", (C.c_double * MAX_TYPES) * MAX_TYPES),
+        ("wca_eps", (C.c_double * MAX_TYPES) * MAX_TYPES),
+        ("wca_cut", (C.c_double * MAX_TYPES) * MAX_TYPES),
+        ("walls", C.c_int),
+        ("wall_sigma", C.c_double * MAX_TYPES),
+        ("wall_eps", C.c_double * MAX_TYPES),
+        ("wall_cut", C.c_double * MAX_TYPES),
+    ]
+
+
+_DP = C.POINTER(C.c_double)
+_IP = C.POINTER(C.c_int32)
+
+
+class State(C.Structure):
+    _fields_ = [("n", C.c_int64)] + [
+        (name, _DP)
+        for name in (
+            "x y z theta q0 q1 q2 q3 vx vy vz wx wy wz f_swim tx ty tz fx fy fz".split()
+        )
+    ] + [("species", _IP)]
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        L = C.CDLL(str(_LIB_PATH))
+        L.orc_philox4x64_10.argtypes = [C.POINTER(C.c_uint64)] * 3
+        L.orc_gaussians.argtypes = [C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, _DP]
+        L.orc_forces.argtypes = [C.POINTER(Params), C.POINTER(State), C.c_int, C.c_int, _DP, _DP, _DP]
+        L.orc_bd_steps.argtypes = [C.POINTER(Params), C.POINTER(State), C.c_uint64, C.c_int64, C.c_int]
+        L.orc_sd_steps.argtypes = [C.POINTER(Params), C.POINTER(State), C.c_int64, C.c_double, C.c_double, C.c_int]
+        L.orc_pairs_within.argtypes = [C.POINTER(Params), C.POINTER(State), C.c_double, _IP, C.c_int64]
+        L.orc_pairs_within.restype = C.c_int64
+        L.orc_cell_index.argtypes = [C.POINTER(Params), C.POINTER(State), C.POINTER(C.c_int), _IP]
+        L.orc_field_distances.argtypes = [C.POINTER(State), _IP, C.c_int, _DP, _DP, _DP, _DP, _DP]
+        L.orc_field_distances.restype = C.c_int64
+        L.orc_vision_cones.argtypes = [
+            C.POINTER(State), _DP, _IP, C.c_int, C.c_double, C.c_double, C.c_int, _DP, _IP, C.c_int, C.c_int, _DP,
+        ]
+        L.orc_vision_cones.restype = C.c_int64
+        L.orc_num_threads.restype = C.c_int
+        L.orc_set_num_threads.argtypes = [C.c_int]
+        _lib = L
+    return _lib
+
+
+def _dp(a):
+    return a.ctypes.data_as(_DP)
+
+
+def _ip(a):
+    return a.ctypes.data_as(_IP)
+
+
+def philox4x64(ctr, key):
+    c = (C.c_uint64 * 4)(*[int(v) for v in ctr])
+    k = (C.c_uint64 * 2)(*[int(v) for v in key])
+    o = (C.c_uint64 * 4)()
+    lib().orc_philox4x64_10(c, k, o)
+    return np.array(list(o), dtype=np.uint64)
+
+
+def gaussians(seed, pid, step, stream):
+    g = np.zeros(4)
+    lib().orc_gaussians(int(seed), int(pid), int(step), int(stream), _dp(g))
+    return g
+
+
+class OracleSwarm:
+    """
+    Host-side swarm advanced by the C oracle.  Mirrors the data model of the
+    CUDA library (SoA fp64 + species table) so tests can drive both with the
+    same inputs.
+    """
+
+    def __init__(self, n_dims, box, periodic, dt, kT, seed, species, wca, walls=None):
+        """
+        species: list of dicts {type, gamma_t(3), gamma_r(3), mass, rinertia(3)}
+        wca: dict with 'sigma','eps','cut' (T,T) arrays
+        walls: None or dict with 'sigma','eps','cut' (T,) arrays
+        """
+        p = Params()
+        p.n_dims = int(n_dims)
+        per = [bool(periodic)] * 3 if np.isscalar(periodic) else list(periodic)
+        for a in range(3):
+            p.periodic[a] = int(per[a])
+            p.box[a] = float(box[a])
+        p.dt, p.kT, p.seed = float(dt), float(kT), int(seed)
+        p.n_species = len(species)
+        T = np.asarray(wca["sigma"]).shape[0]
+        p.n_types = T
+        for s, sp in enumerate(species):
+            p.sp_type[s] = int(sp["type"])
+            p.sp_mass[s] = float(sp["mass"])
+            for a in range(3):
+                p.sp_gamma_t[s][a] = float(sp["gamma_t"][a])
+                p.sp_gamma_r[s][a] = float(sp["gamma_r"][a])
+                p.sp_rinertia[s][a] = float(sp["rinertia"][a])
+        for a in range(T):
+            for b in range(T):
+                p.wca_sigma[a][b] = float(wca["sigma"][a][b])
+                p.wca_eps[a][b] = float(wca["eps"][a][b])
+                p.wca_cut[a][b] = float(wca["cut"][a][b])
+        p.walls = 0
+        if walls is not None:
+            p.walls = 1
+            for a in range(T):
+                p.wall_sigma[a] = float(walls["sigma"][a])
+                p.wall_eps[a] = float(walls["eps"][a])
+                p.wall_cut[a] = float(walls["cut"][a])
+        self.params = p
+        self.n_dims = int(n_dims)
+        self.species_table = species
+        self.n = 0
+
+    def set_state(self, pos, species, theta=None, quat=None):
+        pos = np.asarray(pos, dtype=np.float64)
+        n = pos.shape[0]
+        self.n = n
+        self.x, self.y, self.z = (np.ascontiguousarray(pos[:, a]).copy() for a in range(3))
+        self.theta = np.zeros(n) if theta is None else np.array(theta, dtype=np.float64)
+        q = np.tile([1.0, 0, 0, 0], (n, 1)) if quat is None else np.asarray(quat, dtype=np.float64)
+        self.q = [np.ascontiguousarray(q[:, a]).copy() for a in range(4)]
+        self.v = [np.zeros(n) for _ in range(3)]
+        self.w = [np.zeros(n) for _ in range(3)]
+        self.f_swim = np.zeros(n)
+        self.torque = [np.zeros(n) for _ in range(3)]
+        self.ext_force = [np.zeros(n) for _ in range(3)]
+        self.species = np.ascontiguousarray(species, dtype=np.int32).copy()
+        self.ptype = np.array([self.species_table[s]["type"] for s in self.species], dtype=np.int32)
+        self._mk_state()
+
+    def _mk_state(self):
+        s = State()
+        s.n = self.n
+        s.x, s.y, s.z = _dp(self.x), _dp(self.y), _dp(self.z)
+        s.theta = _dp(self.theta)
+        s.q0, s.q1, s.q2, s.q3 = (_dp(a) for a in self.q)
+        s.vx, s.vy, s.vz = (_dp(a) for a in self.v)
+        s.wx, s.wy, s.wz = (_dp(a) for a in self.w)
+        s.f_swim = _dp(self.f_swim)
+        s.tx, s.ty, s.tz = (_dp(a) for a in self.torque)
+        s.fx, s.fy, s.fz = (_dp(a) for a in self.ext_force)
+        s.species = _ip(self.species)
+        self.state = s
+
+    # --- views -------------------------------------------------------
+    @property
+    def pos(self):
+        return np.stack([self.x, self.y, self.z], axis=1)
+
+    @property
+    def directors(self):
+        if self.n_dims == 2:
+            return np.stack([np.cos(self.theta), np.sin(self.theta), np.zeros(self.n)], axis=1)
+        a, b, c, d = self.q
+        return np.stack([2 * (b * d + a * c), 2 * (c * d - a * b), a * a - b * b - c * c + d * d], axis=1)
+
+    @property
+    def velocities(self):
+        return np.stack(self.v, axis=1)
+
+    @property
+    def omegas(self):
+        return np.stack(self.w, axis=1)
+
+    # --- arithmetic ----------------------------------------------------
+    def forces(self, mode=0, with_swim=True):
+        F = [np.zeros(self.n) for _ in range(3)]
+        lib().orc_forces(C.byref(self.params), C.byref(self.state), mode, int(with_swim), *(_dp(f) for f in F))
+        return np.stack(F, axis=1)
+
+    def bd_steps(self, step0, nsteps, mode=0):
+        lib().orc_bd_steps(C.byref(self.params), C.byref(self.state), int(step0), int(nsteps), mode)
+
+    def sd_steps(self, nsteps, gamma=0.1, max_disp=0.1, mode=0):
+        lib().orc_sd_steps(C.byref(self.params), C.byref(self.state), int(nsteps), gamma, max_disp, mode)
+
+    def pairs_within(self, skin=0.0):
+        cap = max(16, 64 * self.n)
+        while True:
+            buf = np.zeros((cap, 2), dtype=np.int32)
+            cnt = lib().orc_pairs_within(C.byref(self.params), C.byref(self.state), float(skin), _ip(buf), cap)
+            if cnt <= cap:
+                return buf[:cnt].copy()
+            cap = cnt
+
+    def cell_index(self, nc):
+        out = np.zeros(self.n, dtype=np.int32)
+        ncv = (C.c_int * 3)(*[int(v) for v in nc])
+        lib().orc_cell_index(C.byref(self.params), C.byref(self.state), ncv, _ip(out))
+        return out
+
+    def field_distances(self, want_type, src, box, hist):
+        """hist: (3, n) array, updated in place. Returns (d_now, d_prev)."""
+        rows = int(np.sum(self.ptype == want_type))
+        d_now, d_prev = np.zeros(rows), np.zeros(rows)
+        src = np.ascontiguousarray(src, dtype=np.float64)
+        box = np.ascontiguousarray(box, dtype=np.float64)
+        assert hist.shape == (3, self.n) and hist.flags.c_contiguous
+        r = lib().orc_field_distances(
+            C.byref(self.state), _ip(self.ptype), int(want_type), _dp(src), _dp(box), _dp(hist), _dp(d_now), _dp(d_prev)
+        )
+        assert r == rows
+        return d_now, d_prev
+
+    def vision_cones(self, want_type, vision_range, half_angle, n_cones, radii, detected_types):
+        rows = int(np.sum(self.ptype == want_type))
+        n_det = len(detected_types)
+        tmax = int(max(int(self.ptype.max(initial=0)), max(detected_types, default=0))) + 1
+        type_col = -np.ones(tmax, dtype=np.int32)
+        for c, t in enumerate(detected_types):
+            type_col[int(t)] = c
+        out = np.zeros((rows, n_cones, n_det))
+        dirs = np.ascontiguousarray(self.directors.T)
+        radii = np.ascontiguousarray(radii, dtype=np.float64)
+        lib().orc_vision_cones(
+            C.byref(self.state), _dp(dirs), _ip(self.ptype), int(want_type), float(vision_range), float(half_angle),
+            int(n_cones), _dp(radii), _ip(type_col), tmax, n_det, _dp(out),
+        )
+        return out
+
+
+def num_threads():
+    return lib().orc_num_threads()
+
+
+def set_num_threads(t):
+    lib().orc_set_num_threads(int(t))

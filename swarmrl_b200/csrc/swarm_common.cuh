@@ -1,0 +1,205 @@
+// swarm_common.cuh -- shared device structs, Philox4x64-10, geometry helpers (sm_100a).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/swarm_b200.h"
+
+#define SW_S SWARM_MAX_SPECIES
+#define SW_T SWARM_MAX_TYPES
+
+typedef unsigned long long u64;
+
+// ---------------------------------------------------------------------------------------------
+// parameters passed by value to every kernel (< 4 KB)
+// ---------------------------------------------------------------------------------------------
+struct DevParams {
+  int n_dims;
+  int periodic[3];
+  double box[3], inv_box[3];
+  double dt, kT;
+  u64 seed;
+  int n_species, n_types;
+  int sp_type[SW_S];
+  double sp_gt[SW_S][3], sp_gr[SW_S][3], sp_mass[SW_S], sp_rin[SW_S][3];
+  double wca_sigma[SW_T][SW_T], wca_eps[SW_T][SW_T], wca_cut[SW_T][SW_T];
+  int walls;
+  double wall_sigma[SW_T], wall_eps[SW_T], wall_cut[SW_T];
+  double max_cut, skin;
+  int nc[3];      // Verlet-build cell grid per environment
+  int ncell_env;  // nc[0]*nc[1]*nc[2]
+  int n_envs;
+  int env_size;   // particles per environment
+};
+
+// device-side control block (one per swarm handle)
+struct Ctl {
+  unsigned int barrier;   // grid barrier arrival counter (zeroed before each cooperative launch)
+  int halted;             // set when a run stopped early (Verlet overflow); later launches no-op
+  int overflow;
+  int rebuild_flag[3];    // rotating "some particle moved > skin/2" flags
+  int max_nbr_seen;
+  int pad;
+  long long steps_done;   // steps completed by the last launch sequence
+  long long rebuilds;
+};
+
+struct DevArrays {
+  long long n;
+  long long n_pad;
+  double *x[2], *y[2], *z[2];  // [0] caller-bound, [1] library scratch (double buffer)
+  double *theta, *q0, *q1, *q2, *q3;
+  double *vx, *vy, *vz, *wx, *wy, *wz;
+  double *f_swim, *tqx, *tqy, *tqz, *fex, *fey, *fez;
+  const int *species;
+  double *xr, *yr, *zr;        // positions at the last Verlet rebuild
+  int *head, *next, *cellof;   // linked cells
+  int *nbr, *nbr_cnt;          // Verlet list: nbr[k * n_pad + i], k < cap
+  int cap;
+  Ctl *ctl;
+};
+
+// ---------------------------------------------------------------------------------------------
+// host handle
+// ---------------------------------------------------------------------------------------------
+struct swarm {
+  swarm_config_t cfg;
+  DevParams P;
+  DevArrays A;
+  bool species_set = false, wca_set = false, state_bound = false, actions_bound = false;
+  swarm_actions_dev_t act{};
+  swarm_state_dev_t st{};
+  bool list_valid = false;
+  long long launches = 0;
+  long long steps_requested = 0;
+  int num_sms = 0;
+  int coop_blocks_per_sm = 0;
+  bool persistent = true;
+  long long ncell_alloc = 0;
+  // scratch owned by the library
+  std::vector<void *> owned;
+  double *zeros = nullptr;  // n zeros (for unbound optional arrays)
+  // observables scratch
+  void *obs_scratch = nullptr;
+  size_t obs_scratch_bytes = 0;
+  double *red_scratch = nullptr;
+  void *vis_buf = nullptr;   // vision-cone cell structure + packed copies
+  size_t vis_bytes = 0;
+  Ctl *ctl_host = nullptr;  // pinned
+};
+
+void sw_set_error(const std::string &msg);
+int sw_cuda_fail(cudaError_t e, const char *what);
+#define SW_CUDA(expr)                                             \
+  do {                                                            \
+    cudaError_t _e = (expr);                                      \
+    if (_e != cudaSuccess) return sw_cuda_fail(_e, #expr);        \
+  } while (0)
+
+// ---------------------------------------------------------------------------------------------
+// Philox4x64-10 (Salmon et al., SC'11).  Same layout as the oracle (swarm_oracle.c):
+// counter = (step, stream, 0, 0), key = (particle id, seed).
+// ---------------------------------------------------------------------------------------------
+__host__ __device__ __forceinline__ void sw_mulhilo(u64 a, u64 b, u64 &hi, u64 &lo) {
+#ifdef __CUDA_ARCH__
+  hi = __umul64hi(a, b);
+  lo = a * b;
+#else
+  unsigned __int128 p = (unsigned __int128)a * b;
+  hi = (u64)(p >> 64);
+  lo = (u64)p;
+#endif
+}
+
+__host__ __device__ __forceinline__ void sw_philox4x64_10(u64 c0, u64 c1, u64 c2, u64 c3, u64 k0, u64 k1, u64 out[4]) {
+  const u64 M0 = 0xD2E7470EE14C6C93ULL, M1 = 0xCA5A826395121157ULL;
+  const u64 W0 = 0x9E3779B97F4A7C15ULL, W1 = 0xBB67AE8584CAA73BULL;
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    u64 hi0, lo0, hi1, lo1;
+    sw_mulhilo(M0, c0, hi0, lo0);
+    sw_mulhilo(M1, c2, hi1, lo1);
+    u64 n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+    c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+    k0 += W0; k1 += W1;
+  }
+  out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+
+__device__ __forceinline__ double sw_u01(u64 r) {
+  return ((double)(r >> 12) + 0.5) * (1.0 / 4503599627370496.0);
+}
+
+// four standard normals for (seed, id, step, stream): Box-Muller on (u0,u1), (u2,u3)
+__device__ __forceinline__ void sw_gaussians(u64 seed, u64 id, u64 step, u64 stream, double g[4]) {
+  u64 r[4];
+  sw_philox4x64_10(step, stream, 0ULL, 0ULL, id, seed, r);
+  double m0 = sqrt(-2.0 * log(sw_u01(r[0])));
+  double m1 = sqrt(-2.0 * log(sw_u01(r[2])));
+  double s0, c0, s1, c1;
+  sincospi(2.0 * sw_u01(r[1]), &s0, &c0);
+  sincospi(2.0 * sw_u01(r[3]), &s1, &c1);
+  g[0] = m0 * c0; g[1] = m0 * s0; g[2] = m1 * c1; g[3] = m1 * s1;
+}
+
+// ---------------------------------------------------------------------------------------------
+// geometry.  Everything that decides SET MEMBERSHIP (cell index, r < cut) uses the explicit
+// round-to-nearest intrinsics so nvcc cannot contract it into FMAs: the oracle is compiled with
+// -ffp-contract=off and the neighbour / cell lists must agree bit for bit.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ double sw_min_image(double d, double L, double invL, int periodic) {
+  if (periodic) d = __dsub_rn(d, __dmul_rn(L, rint(__dmul_rn(d, invL))));
+  return d;
+}
+
+__device__ __forceinline__ int sw_cell_coord(double x, double invL, int nc, int periodic) {
+  double u = __dmul_rn(x, invL);
+  if (periodic) u = __dsub_rn(u, floor(u));
+  double cf = floor(__dmul_rn(u, (double)nc));
+  int c;
+  if (cf < 0.0) c = 0;
+  else if (cf >= (double)nc) c = nc - 1;
+  else c = (int)cf;
+  return c;
+}
+
+__device__ __forceinline__ double sw_r2(double dx, double dy, double dz) {
+  return __dadd_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), __dmul_rn(dz, dz));
+}
+
+// WCA pair-force factor: F_i += fac * (x_i - x_j)   (oracle: wca_factor)
+__device__ __forceinline__ double sw_wca_factor(double r2, double sigma, double eps) {
+  double f2 = sigma * sigma / r2;
+  double f6 = f2 * f2 * f2;
+  return 48.0 * eps * f6 * (f6 - 0.5) / r2;
+}
+
+// loads of data that other CTAs rewrite inside the same (persistent) kernel: bypass L1
+__device__ __forceinline__ double ldcg(const double *p) { return __ldcg(p); }
+__device__ __forceinline__ int ldcg(const int *p) { return __ldcg(p); }
+__device__ __forceinline__ long long ldcg(const long long *p) { return __ldcg(p); }
+
+__device__ __forceinline__ void sw_quat_to_mat(const double q[4], double R[3][3]) {
+  double a = q[0], b = q[1], c = q[2], d = q[3];
+  R[0][0] = a * a + b * b - c * c - d * d; R[0][1] = 2 * (b * c - a * d); R[0][2] = 2 * (b * d + a * c);
+  R[1][0] = 2 * (b * c + a * d); R[1][1] = a * a - b * b + c * c - d * d; R[1][2] = 2 * (c * d - a * b);
+  R[2][0] = 2 * (b * d - a * c); R[2][1] = 2 * (c * d + a * b); R[2][2] = a * a - b * b - c * c + d * d;
+}
+
+__device__ __forceinline__ void sw_quat_rotate_body(double q[4], const double ax[3], double angle) {
+  double s, c;
+  sincos(0.5 * angle, &s, &c);
+  double r0 = c, r1 = s * ax[0], r2 = s * ax[1], r3 = s * ax[2];
+  double o0 = q[0] * r0 - q[1] * r1 - q[2] * r2 - q[3] * r3;
+  double o1 = q[0] * r1 + q[1] * r0 + q[2] * r3 - q[3] * r2;
+  double o2 = q[0] * r2 - q[1] * r3 + q[2] * r0 + q[3] * r1;
+  double o3 = q[0] * r3 + q[1] * r2 - q[2] * r1 + q[3] * r0;
+  double nrm = sqrt(o0 * o0 + o1 * o1 + o2 * o2 + o3 * o3);
+  q[0] = o0 / nrm; q[1] = o1 / nrm; q[2] = o2 / nrm; q[3] = o3 / nrm;
+}
+
+// launch bookkeeping
+static inline int sw_blocks(long long n, int threads) { return (int)((n + threads - 1) / threads); }

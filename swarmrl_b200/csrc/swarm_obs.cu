@@ -1,0 +1,450 @@
+// swarm_obs.cu -- per-agent observable and task-reward kernels (sm_100a) and their C-ABI.
+//
+// Replaces the per-colloid Python/JAX loops of
+//   swarmrl/observables/concentration_field.py:84-138, swarmrl/tasks/searching/gradient_sensing.py:92-150,
+//   swarmrl/observables/subdivided_vision_cones.py:83-258 (+ swarmrl/utils/utils.py:297-332),
+//   swarmrl/observables/position.py:32-60 and the mean of swarmrl/trainers/trainer.py:92-95.
+//
+// Vision cones are O(N^2) in the reference (every observer visits every particle).  Here the
+// particles are binned on a uniform grid of edge >= vision_range laid over the bounding box of the
+// UNFOLDED positions (the reference takes raw differences, no minimum image):
+//   cell hash -> counting sort on the cell key (a one-digit radix sort: histogram, exclusive scan =
+//   cell-start table, scatter) -> per-cell index sort (makes the order deterministic and equal to
+//   what a stable radix sort yields) -> packed cell-ordered copies of (x, y, z, radius, column) ->
+//   one thread per observer walks the 3^d neighbouring cells, each row of which is ONE contiguous
+//   range of the packed arrays.
+#include <math.h>
+
+#include "swarm_common.cuh"
+
+struct VisGrid {
+  double lo[3];
+  double cs;       // cell edge
+  double inv_cs;
+  int nc[3];
+  int ncell;
+  unsigned long long mn[3], mx[3];  // ordered-uint encodings for atomicMin / atomicMax
+};
+
+__device__ __forceinline__ unsigned long long enc_double(double v) {
+  unsigned long long b = (unsigned long long)__double_as_longlong(v);
+  return (b & 0x8000000000000000ULL) ? ~b : (b | 0x8000000000000000ULL);
+}
+__device__ __forceinline__ double dec_double(unsigned long long e) {
+  unsigned long long b = (e & 0x8000000000000000ULL) ? (e & 0x7FFFFFFFFFFFFFFFULL) : ~e;
+  return __longlong_as_double((long long)b);
+}
+
+__global__ void k_vis_init(VisGrid *G, int *count, long long ncell_max) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i == 0)
+    for (int a = 0; a < 3; ++a) { G->mn[a] = ~0ULL; G->mx[a] = 0ULL; }
+  for (; i <= ncell_max; i += (long long)gridDim.x * blockDim.x) count[i] = 0;
+}
+
+__global__ void k_vis_bbox(long long n, const double *x, const double *y, const double *z, VisGrid *G) {
+  __shared__ unsigned long long smn[3][8], smx[3][8];
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  unsigned long long mn[3] = {~0ULL, ~0ULL, ~0ULL}, mx[3] = {0ULL, 0ULL, 0ULL};
+  for (; i < n; i += (long long)gridDim.x * blockDim.x) {
+    unsigned long long e[3] = {enc_double(x[i]), enc_double(y[i]), enc_double(z[i])};
+#pragma unroll
+    for (int a = 0; a < 3; ++a) { mn[a] = min(mn[a], e[a]); mx[a] = max(mx[a], e[a]); }
+  }
+#pragma unroll
+  for (int a = 0; a < 3; ++a)
+    for (int o = 16; o > 0; o >>= 1) {
+      mn[a] = min(mn[a], __shfl_xor_sync(0xffffffffu, mn[a], o));
+      mx[a] = max(mx[a], __shfl_xor_sync(0xffffffffu, mx[a], o));
+    }
+  int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  if (l == 0)
+    for (int a = 0; a < 3; ++a) { smn[a][w] = mn[a]; smx[a][w] = mx[a]; }
+  __syncthreads();
+  if (threadIdx.x < 3) {
+    int a = threadIdx.x;
+    unsigned long long m0 = ~0ULL, m1 = 0ULL;
+    for (int k = 0; k < (int)(blockDim.x >> 5); ++k) { m0 = min(m0, smn[a][k]); m1 = max(m1, smx[a][k]); }
+    atomicMin(&G->mn[a], m0);
+    atomicMax(&G->mx[a], m1);
+  }
+}
+
+__global__ void k_vis_grid(VisGrid *G, double range, long long ncell_max) {
+  if (blockIdx.x != 0 || threadIdx.x != 0) return;
+  double ext[3];
+  for (int a = 0; a < 3; ++a) {
+    double lo = dec_double(G->mn[a]), hi = dec_double(G->mx[a]);
+    if (!(hi >= lo)) { lo = 0.0; hi = 0.0; }
+    G->lo[a] = lo;
+    ext[a] = hi - lo;
+  }
+  double cs = range > 0.0 ? range : 1.0;
+  for (;;) {
+    long long tot = 1;
+    for (int a = 0; a < 3; ++a) {
+      double f = floor(ext[a] / cs) + 1.0;
+      int nc = (f > 1048576.0) ? 1048576 : (int)f;
+      if (nc < 1) nc = 1;
+      G->nc[a] = nc;
+      tot *= nc;
+      if (tot > ncell_max) break;
+    }
+    if (tot <= ncell_max) { G->ncell = (int)tot; break; }
+    cs *= 1.5;
+  }
+  G->cs = cs;
+  G->inv_cs = 1.0 / cs;
+}
+
+__device__ __forceinline__ int vis_coord(double v, double lo, double inv_cs, int nc) {
+  double cf = floor((v - lo) * inv_cs);
+  if (!(cf >= 0.0)) return 0;
+  if (cf >= (double)nc) return nc - 1;
+  return (int)cf;
+}
+
+__global__ void k_vis_count(long long n, const double *x, const double *y, const double *z, const VisGrid *G,
+                            int *cellid, int *count) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int cx = vis_coord(x[i], G->lo[0], G->inv_cs, G->nc[0]);
+  int cy = vis_coord(y[i], G->lo[1], G->inv_cs, G->nc[1]);
+  int cz = vis_coord(z[i], G->lo[2], G->inv_cs, G->nc[2]);
+  int c = (cz * G->nc[1] + cy) * G->nc[0] + cx;
+  cellid[i] = c;
+  atomicAdd(&count[c], 1);
+}
+
+// ---- exclusive scan of count[0..m) (m = ncell_max + 1) in three launches ---------------------
+#define SCAN_T 256
+#define SCAN_E 4
+#define SCAN_TILE (SCAN_T * SCAN_E)
+
+__device__ __forceinline__ int block_excl_scan(int v, int *total) {
+  __shared__ int wsum[SCAN_T / 32];
+  int l = threadIdx.x & 31, w = threadIdx.x >> 5;
+  int inc = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    int t = __shfl_up_sync(0xffffffffu, inc, o);
+    if (l >= o) inc += t;
+  }
+  if (l == 31) wsum[w] = inc;
+  __syncthreads();
+  if (w == 0) {
+    int s = (l < SCAN_T / 32) ? wsum[l] : 0;
+#pragma unroll
+    for (int o = 1; o < SCAN_T / 32; o <<= 1) {
+      int t = __shfl_up_sync(0xffffffffu, s, o);
+      if (l >= o) s += t;
+    }
+    if (l < SCAN_T / 32) wsum[l] = s;
+  }
+  __syncthreads();
+  int base = (w > 0) ? wsum[w - 1] : 0;
+  *total = wsum[SCAN_T / 32 - 1];
+  __syncthreads();
+  return base + inc - v;
+}
+
+__global__ void k_scan_tiles(long long m, const int *in, int *out, int *tile_sum) {
+  long long base = (long long)blockIdx.x * SCAN_TILE + (long long)threadIdx.x * SCAN_E;
+  int v[SCAN_E], s = 0;
+#pragma unroll
+  for (int k = 0; k < SCAN_E; ++k) { v[k] = (base + k < m) ? in[base + k] : 0; s += v[k]; }
+  int total;
+  int ex = block_excl_scan(s, &total);
+#pragma unroll
+  for (int k = 0; k < SCAN_E; ++k) { if (base + k < m) out[base + k] = ex; ex += v[k]; }
+  if (threadIdx.x == 0) tile_sum[blockIdx.x] = total;
+}
+
+__global__ void k_scan_sums(int ntiles, int *tile_sum) {
+  // single block: sequential over chunks of SCAN_T
+  __shared__ int carry;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  for (int b = 0; b < ntiles; b += SCAN_T) {
+    int idx = b + threadIdx.x;
+    int v = (idx < ntiles) ? tile_sum[idx] : 0;
+    int total;
+    int ex = block_excl_scan(v, &total);
+    int c = carry;
+    if (idx < ntiles) tile_sum[idx] = ex + c;
+    __syncthreads();
+    if (threadIdx.x == 0) carry = c + total;
+    __syncthreads();
+  }
+}
+
+__global__ void k_scan_add(long long m, int *out, const int *tile_sum, int *fill) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= m) return;
+  int v = out[i] + tile_sum[i / SCAN_TILE];
+  out[i] = v;
+  fill[i] = v;
+}
+
+__global__ void k_vis_fill(long long n, const int *cellid, int *fill, int *items) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int p = atomicAdd(&fill[cellid[i]], 1);
+  items[p] = (int)i;
+}
+
+// per-cell insertion sort by particle index: deterministic, == stable radix sort order
+__global__ void k_vis_sortcell(const VisGrid *G, const int *start, int *items) {
+  long long c = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= G->ncell) return;
+  int b = start[c], e = start[c + 1];
+  for (int k = b + 1; k < e; ++k) {
+    int v = items[k], j = k;
+    while (j > b && items[j - 1] > v) { items[j] = items[j - 1]; --j; }
+    items[j] = v;
+  }
+}
+
+__global__ void k_vis_pack(long long n, const int *items, const double *x, const double *y, const double *z,
+                           const double *radii, const int *species, DevParams P, const int *type_col, int n_type_col,
+                           double *sx, double *sy, double *sz, double *sr, int *scol) {
+  long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  int i = items[k];
+  sx[k] = x[i]; sy[k] = y[i]; sz[k] = z[i]; sr[k] = radii[i];
+  int t = P.sp_type[species[i]];
+  scol[k] = (t >= 0 && t < n_type_col) ? type_col[t] : -1;
+}
+
+#define VIS_MAX_ACC 64
+
+// one thread per cell-ordered slot; observers (row_of >= 0) accumulate their cones
+__global__ void __launch_bounds__(128) k_vis_cones(long long n, const int *items, const int *row_of, const VisGrid *G,
+                                                   const int *start, const double *sx, const double *sy,
+                                                   const double *sz, const double *sr, const int *scol, int n_dims,
+                                                   const double *theta, const double *q0, const double *q1,
+                                                   const double *q2, const double *q3, double range,
+                                                   double half_angle, int n_cones, int n_cols, double *out) {
+  long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int i = items[k];
+  const int row = row_of[i];
+  if (row < 0) return;
+  double acc[VIS_MAX_ACC];
+  const int nacc = n_cones * n_cols;
+  for (int a = 0; a < nacc; ++a) acc[a] = 0.0;
+  const double xi = sx[k], yi = sy[k], zi = sz[k];
+  double ex, ey, ez;
+  if (n_dims == 2) { sincos(theta[i], &ey, &ex); ez = 0.0; }
+  else {
+    double a = q0[i], b = q1[i], c = q2[i], d = q3[i];
+    ex = 2 * (b * d + a * c); ey = 2 * (c * d - a * b); ez = a * a - b * b - c * c + d * d;
+  }
+  {
+    double en = sqrt(ex * ex + ey * ey + ez * ez);
+    ex /= en; ey /= en; ez /= en;
+  }
+  const int cx = vis_coord(xi, G->lo[0], G->inv_cs, G->nc[0]);
+  const int cy = vis_coord(yi, G->lo[1], G->inv_cs, G->nc[1]);
+  const int cz = vis_coord(zi, G->lo[2], G->inv_cs, G->nc[2]);
+  const int x0 = max(cx - 1, 0), x1 = min(cx + 1, G->nc[0] - 1);
+  for (int zz = max(cz - 1, 0); zz <= min(cz + 1, G->nc[2] - 1); ++zz)
+    for (int yy = max(cy - 1, 0); yy <= min(cy + 1, G->nc[1] - 1); ++yy) {
+      const long long rowbase = ((long long)zz * G->nc[1] + yy) * G->nc[0];
+      const int b = start[rowbase + x0], e = start[rowbase + x1 + 1];
+      for (int m = b; m < e; ++m) {
+        const int col = __ldg(&scol[m]);
+        if (col < 0) continue;
+        double dx = __ldg(&sx[m]) - xi, dy = __ldg(&sy[m]) - yi, dz = __ldg(&sz[m]) - zi;
+        double d = sqrt(dx * dx + dy * dy + dz * dz);
+        if (!(d < range) || d == 0.0) continue;
+        double w = 2.0 * __ldg(&sr[m]) / d;
+        if (w > 1.0) w = 1.0;
+        double s0 = dx / d, s1 = dy / d, s2 = dz / d;
+        double sn = sqrt(s0 * s0 + s1 * s1 + s2 * s2);
+        s0 /= sn; s1 /= sn; s2 /= sn;
+        double c = s0 * ex + s1 * ey + s2 * ez;
+        c = fmin(1.0, fmax(-1.0, c));
+        double ang = acos(c);
+        double od = s0 * (-ey) + s1 * ex + s2 * ez;
+        if (!(od >= 0.0)) ang = -ang;
+        for (int kc = 0; kc < n_cones; ++kc) {
+          double lo = -half_angle + (double)kc * half_angle * 2.0 / (double)n_cones;
+          double hi = -half_angle + (double)(kc + 1) * half_angle * 2.0 / (double)n_cones;
+          if (lo < ang && hi > ang) acc[kc * n_cols + col] += w;
+        }
+      }
+    }
+  double *o = out + (long long)row * nacc;
+  for (int a = 0; a < nacc; ++a) o[a] = acc[a];
+}
+
+// ---- concentration field / gradient sensing ---------------------------------------------------
+__device__ __forceinline__ double decay_eval(int kind, double c0, double c1, double d) {
+  switch (kind) {
+    case SWARM_DECAY_LINEAR: return c0 + c1 * d;
+    case SWARM_DECAY_EXP: return c0 * exp(-c1 * d);
+    case SWARM_DECAY_INVERSE: return c0 / (d + c1);
+    default: return d;
+  }
+}
+
+__global__ void k_obs_field(long long n, const double *x, const double *y, const double *z, const int *row_of,
+                            double s0, double s1, double s2, double b0, double b1, double b2, double *hist, int decay,
+                            double c0, double c1, double scale, int clip, double *out, double *d_now, double *d_prev) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int row = row_of ? row_of[i] : (int)i;
+  if (row < 0) return;
+  double p0 = x[i] / b0, p1 = y[i] / b1, p2 = z[i] / b2;
+  double h0 = hist[i], h1 = hist[n + i], h2 = hist[2 * n + i];
+  double dn = sqrt((s0 - p0) * (s0 - p0) + (s1 - p1) * (s1 - p1) + (s2 - p2) * (s2 - p2));
+  double dp = sqrt((s0 - h0) * (s0 - h0) + (s1 - h1) * (s1 - h1) + (s2 - h2) * (s2 - h2));
+  hist[i] = p0; hist[n + i] = p1; hist[2 * n + i] = p2;
+  if (d_now) d_now[row] = dn;
+  if (d_prev) d_prev[row] = dp;
+  if (out && decay != SWARM_DECAY_NONE) {
+    double v = scale * (decay_eval(decay, c0, c1, dn) - decay_eval(decay, c0, c1, dp));
+    if (clip && !(v > 0.0)) v = 0.0;
+    out[row] = v;
+  }
+}
+
+__global__ void k_obs_position(long long n, const double *x, const double *y, const double *z, const int *row_of,
+                               double b0, double b1, double b2, double *out) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int row = row_of ? row_of[i] : (int)i;
+  if (row < 0) return;
+  out[3LL * row] = x[i] / b0; out[3LL * row + 1] = y[i] / b1; out[3LL * row + 2] = z[i] / b2;
+}
+
+// ---- deterministic two-stage sum -------------------------------------------------------------
+#define RED_BLOCKS 296
+__global__ void k_reduce_partial(long long n, const double *in, double *partial) {
+  __shared__ double ws[8];
+  // fixed, grid-independent assignment: block b owns a contiguous slice
+  long long per = (n + RED_BLOCKS - 1) / RED_BLOCKS;
+  long long lo = (long long)blockIdx.x * per, hi = min(n, lo + per);
+  double s = 0.0;
+  for (long long i = lo + threadIdx.x; i < hi; i += blockDim.x) s += in[i];
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    for (int k = 0; k < (int)(blockDim.x >> 5); ++k) t += ws[k];
+    partial[blockIdx.x] = t;
+  }
+}
+__global__ void k_reduce_final(long long n, const double *partial, double *out2) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  double t = 0.0;
+  for (int k = 0; k < RED_BLOCKS; ++k) t += partial[k];
+  out2[0] = t;
+  out2[1] = (n > 0) ? t / (double)n : 0.0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// C-ABI
+// ---------------------------------------------------------------------------------------------
+static inline size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
+
+extern "C" int swarm_obs_field(swarm_t *s, const int32_t *row_of, const double src[3], const double box_length[3],
+                               double *hist, int32_t decay, double c0, double c1, double scale, int32_t clip,
+                               double *out, double *d_now, double *d_prev, void *stream) {
+  if (!s || !s->state_bound || !src || !box_length || !hist) { sw_set_error("bad arguments"); return SWARM_ERR_INVALID; }
+  if (decay < SWARM_DECAY_NONE || decay > SWARM_DECAY_INVERSE) { sw_set_error("unknown decay kind"); return SWARM_ERR_INVALID; }
+  SW_CUDA(cudaSetDevice(s->cfg.device));
+  const DevArrays &A = s->A;
+  if (A.n == 0) return SWARM_OK;
+  k_obs_field<<<sw_blocks(A.n, 256), 256, 0, (cudaStream_t)stream>>>(A.n, A.x[0], A.y[0], A.z[0], row_of, src[0], src[1], src[2],
+                                                                     box_length[0], box_length[1], box_length[2], hist, decay,
+                                                                     c0, c1, scale, clip, out, d_now, d_prev);
+  s->launches += 1;
+  SW_CUDA(cudaGetLastError());
+  return SWARM_OK;
+}
+
+extern "C" int swarm_obs_position(swarm_t *s, const int32_t *row_of, const double box_length[3], double *out, void *stream) {
+  if (!s || !s->state_bound || !box_length || !out) { sw_set_error("bad arguments"); return SWARM_ERR_INVALID; }
+  SW_CUDA(cudaSetDevice(s->cfg.device));
+  const DevArrays &A = s->A;
+  if (A.n == 0) return SWARM_OK;
+  k_obs_position<<<sw_blocks(A.n, 256), 256, 0, (cudaStream_t)stream>>>(A.n, A.x[0], A.y[0], A.z[0], row_of, box_length[0],
+                                                                        box_length[1], box_length[2], out);
+  s->launches += 1;
+  SW_CUDA(cudaGetLastError());
+  return SWARM_OK;
+}
+
+extern "C" int swarm_reduce_mean(swarm_t *s, const double *in, int64_t n, double *out2, void *stream) {
+  if (!s || n < 0 || !out2 || (n > 0 && !in)) { sw_set_error("bad arguments"); return SWARM_ERR_INVALID; }
+  SW_CUDA(cudaSetDevice(s->cfg.device));
+  if (!s->red_scratch) SW_CUDA(cudaMalloc((void **)&s->red_scratch, sizeof(double) * RED_BLOCKS));
+  cudaStream_t st = (cudaStream_t)stream;
+  k_reduce_partial<<<RED_BLOCKS, 256, 0, st>>>(n, in, s->red_scratch);
+  k_reduce_final<<<1, 32, 0, st>>>(n, s->red_scratch, out2);
+  s->launches += 2;
+  SW_CUDA(cudaGetLastError());
+  return SWARM_OK;
+}
+
+extern "C" int swarm_obs_vision(swarm_t *s, const int32_t *row_of, int64_t rows, double vision_range, double half_angle,
+                                int32_t n_cones, const double *radii, const int32_t *type_col, int32_t n_type_col,
+                                int32_t n_cols, double *out, void *stream) {
+  if (!s || !s->state_bound || !row_of || !radii || !type_col || !out) { sw_set_error("bad arguments"); return SWARM_ERR_INVALID; }
+  if (n_cones < 1 || n_cols < 1 || n_cones * n_cols > VIS_MAX_ACC) {
+    sw_set_error("n_cones * n_detected_types must be in 1..64"); return SWARM_ERR_INVALID;
+  }
+  if (!(vision_range > 0.0)) { sw_set_error("vision_range must be positive"); return SWARM_ERR_INVALID; }
+  SW_CUDA(cudaSetDevice(s->cfg.device));
+  const DevArrays &A = s->A;
+  const long long n = A.n;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (rows > 0) SW_CUDA(cudaMemsetAsync(out, 0, sizeof(double) * (size_t)rows * (size_t)n_cones * (size_t)n_cols, st));
+  if (n == 0 || rows == 0) return SWARM_OK;
+  long long ncell_max = 4 * n;
+  if (ncell_max < 4096) ncell_max = 4096;
+  if (ncell_max > (1LL << 24)) ncell_max = (1LL << 24);
+  const long long m = ncell_max + 1;
+  const int ntiles = (int)((m + SCAN_TILE - 1) / SCAN_TILE);
+  // carve the scratch buffer
+  size_t off = 0;
+  auto carve = [&](size_t bytes) { size_t o = off; off += align256(bytes); return o; };
+  size_t o_grid = carve(sizeof(VisGrid));
+  size_t o_count = carve(sizeof(int) * (size_t)m), o_start = carve(sizeof(int) * (size_t)m), o_fill = carve(sizeof(int) * (size_t)m);
+  size_t o_tiles = carve(sizeof(int) * (size_t)ntiles);
+  size_t o_cell = carve(sizeof(int) * (size_t)n), o_items = carve(sizeof(int) * (size_t)n), o_col = carve(sizeof(int) * (size_t)n);
+  size_t o_sx = carve(sizeof(double) * (size_t)n), o_sy = carve(sizeof(double) * (size_t)n);
+  size_t o_sz = carve(sizeof(double) * (size_t)n), o_sr = carve(sizeof(double) * (size_t)n);
+  if (s->vis_bytes < off) {
+    if (s->vis_buf) cudaFree(s->vis_buf);
+    s->vis_buf = nullptr; s->vis_bytes = 0;
+    SW_CUDA(cudaMalloc(&s->vis_buf, off));
+    s->vis_bytes = off;
+  }
+  char *base = (char *)s->vis_buf;
+  VisGrid *G = (VisGrid *)(base + o_grid);
+  int *count = (int *)(base + o_count), *start = (int *)(base + o_start), *fill = (int *)(base + o_fill);
+  int *tiles = (int *)(base + o_tiles), *cellid = (int *)(base + o_cell), *items = (int *)(base + o_items);
+  int *scol = (int *)(base + o_col);
+  double *sx = (double *)(base + o_sx), *sy = (double *)(base + o_sy), *sz = (double *)(base + o_sz), *sr = (double *)(base + o_sr);
+  const int T = 256, B = sw_blocks(n, T);
+  const int gb = B < 4 * s->num_sms ? B : 4 * s->num_sms;
+  k_vis_init<<<gb > 0 ? gb : 1, T, 0, st>>>(G, count, ncell_max);
+  k_vis_bbox<<<gb > 0 ? gb : 1, T, 0, st>>>(n, A.x[0], A.y[0], A.z[0], G);
+  k_vis_grid<<<1, 32, 0, st>>>(G, vision_range, ncell_max);
+  k_vis_count<<<B, T, 0, st>>>(n, A.x[0], A.y[0], A.z[0], G, cellid, count);
+  k_scan_tiles<<<ntiles, SCAN_T, 0, st>>>(m, count, start, tiles);
+  k_scan_sums<<<1, SCAN_T, 0, st>>>(ntiles, tiles);
+  k_scan_add<<<sw_blocks(m, T), T, 0, st>>>(m, start, tiles, fill);
+  k_vis_fill<<<B, T, 0, st>>>(n, cellid, fill, items);
+  k_vis_sortcell<<<sw_blocks(ncell_max, T), T, 0, st>>>(G, start, items);
+  k_vis_pack<<<B, T, 0, st>>>(n, items, A.x[0], A.y[0], A.z[0], radii, A.species, s->P, type_col, n_type_col, sx, sy, sz, sr, scol);
+  k_vis_cones<<<sw_blocks(n, 128), 128, 0, st>>>(n, items, row_of, G, start, sx, sy, sz, sr, scol, s->P.n_dims, A.theta, A.q0,
+                                                 A.q1, A.q2, A.q3, vision_range, half_angle, n_cones, n_cols, out);
+  s->launches += 11;
+  SW_CUDA(cudaGetLastError());
+  return SWARM_OK;
+}
