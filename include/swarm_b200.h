@@ -174,10 +174,11 @@ int swarm_obs_field(swarm_t *s, const int32_t *row_of_dev, const double src[3], 
 /* SubdividedVisionCones.compute_observable (observables/subdivided_vision_cones.py:83-258):
  * out[row, cone, col] over every particle j (raw unfolded differences, observer included),
  * col = type_col_dev[type_j] (or -1 = undetected), radius of the SEEN particle.
+ * dirs_dev = [3][n] observer directors, or NULL to use the bound orientation state.
  * out_dev = [rows][n_cones][n_cols], overwritten. */
 int swarm_obs_vision(swarm_t *s, const int32_t *row_of_dev, int64_t rows, double vision_range, double half_angle,
                      int32_t n_cones, const double *radii_dev, const int32_t *type_col_dev, int32_t n_type_col,
-                     int32_t n_cols, double *out_dev, void *stream);
+                     int32_t n_cols, const double *dirs_dev, double *out_dev, void *stream);
 
 /* PositionObservable (observables/position.py:32-60): out[row] = pos / box_length, [rows][3] */
 int swarm_obs_position(swarm_t *s, const int32_t *row_of_dev, const double box_length[3], double *out_dev, void *stream);

@@ -89,6 +89,8 @@ def lib():
         ]
         L.orc_vision_cones.restype = C.c_int64
         L.orc_num_threads.restype = C.c_int
+        L.orc_set_skin.argtypes = [C.c_double]
+        L.orc_last_verlet_builds.restype = C.c_int64
         L.orc_set_num_threads.argtypes = [C.c_int]
         _lib = L
     return _lib
@@ -269,6 +271,15 @@ class OracleSwarm:
             int(n_cones), _dp(radii), _ip(type_col), tmax, n_det, _dp(out),
         )
         return out
+
+
+def set_skin(skin):
+    """Verlet skin of mode 2 (cell_system.skin, espresso.py:269)."""
+    lib().orc_set_skin(float(skin))
+
+
+def last_verlet_builds():
+    return int(lib().orc_last_verlet_builds())
 
 
 def num_threads():

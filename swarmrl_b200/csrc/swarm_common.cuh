@@ -100,7 +100,7 @@ int sw_cuda_fail(cudaError_t e, const char *what);
   } while (0)
 
 // ---------------------------------------------------------------------------------------------
-// Philox4x64-10 (Salmon et al., SC'11).  Same layout as the oracle (swarm_oracle.c):
+// Philox4x64-10 (Salmon et al., SC'11).  Layout (documented in DESIGN.md, checked by the parity tests):
 // counter = (step, stream, 0, 0), key = (particle id, seed).
 // ---------------------------------------------------------------------------------------------
 __host__ __device__ __forceinline__ void sw_mulhilo(u64 a, u64 b, u64 &hi, u64 &lo) {

@@ -223,8 +223,9 @@ __global__ void __launch_bounds__(128) k_vis_cones(long long n, const int *items
                                                    const int *start, const double *sx, const double *sy,
                                                    const double *sz, const double *sr, const int *scol, int n_dims,
                                                    const double *theta, const double *q0, const double *q1,
-                                                   const double *q2, const double *q3, double range,
-                                                   double half_angle, int n_cones, int n_cols, double *out) {
+                                                   const double *q2, const double *q3, const double *dirs,
+                                                   double range, double half_angle, int n_cones, int n_cols,
+                                                   double *out) {
   long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= n) return;
   const int i = items[k];
@@ -235,7 +236,8 @@ __global__ void __launch_bounds__(128) k_vis_cones(long long n, const int *items
   for (int a = 0; a < nacc; ++a) acc[a] = 0.0;
   const double xi = sx[k], yi = sy[k], zi = sz[k];
   double ex, ey, ez;
-  if (n_dims == 2) { sincos(theta[i], &ey, &ex); ez = 0.0; }
+  if (dirs) { ex = dirs[i]; ey = dirs[n + i]; ez = dirs[2 * n + i]; }
+  else if (n_dims == 2) { sincos(theta[i], &ey, &ex); ez = 0.0; }
   else {
     double a = q0[i], b = q1[i], c = q2[i], d = q3[i];
     ex = 2 * (b * d + a * c); ey = 2 * (c * d - a * b); ez = a * a - b * b - c * c + d * d;
@@ -392,7 +394,7 @@ extern "C" int swarm_reduce_mean(swarm_t *s, const double *in, int64_t n, double
 
 extern "C" int swarm_obs_vision(swarm_t *s, const int32_t *row_of, int64_t rows, double vision_range, double half_angle,
                                 int32_t n_cones, const double *radii, const int32_t *type_col, int32_t n_type_col,
-                                int32_t n_cols, double *out, void *stream) {
+                                int32_t n_cols, const double *dirs, double *out, void *stream) {
   if (!s || !s->state_bound || !row_of || !radii || !type_col || !out) { sw_set_error("bad arguments"); return SWARM_ERR_INVALID; }
   if (n_cones < 1 || n_cols < 1 || n_cones * n_cols > VIS_MAX_ACC) {
     sw_set_error("n_cones * n_detected_types must be in 1..64"); return SWARM_ERR_INVALID;
@@ -443,7 +445,7 @@ extern "C" int swarm_obs_vision(swarm_t *s, const int32_t *row_of, int64_t rows,
   k_vis_sortcell<<<sw_blocks(ncell_max, T), T, 0, st>>>(G, start, items);
   k_vis_pack<<<B, T, 0, st>>>(n, items, A.x[0], A.y[0], A.z[0], radii, A.species, s->P, type_col, n_type_col, sx, sy, sz, sr, scol);
   k_vis_cones<<<sw_blocks(n, 128), 128, 0, st>>>(n, items, row_of, G, start, sx, sy, sz, sr, scol, s->P.n_dims, A.theta, A.q0,
-                                                 A.q1, A.q2, A.q3, vision_range, half_angle, n_cones, n_cols, out);
+                                                 A.q1, A.q2, A.q3, dirs, vision_range, half_angle, n_cones, n_cols, out);
   s->launches += 11;
   SW_CUDA(cudaGetLastError());
   return SWARM_OK;

@@ -297,12 +297,13 @@ class DeviceSwarm:
         cut = (lambda t: None if t is None else t[:n_rows])
         return cut(out), cut(dn), cut(dp)
 
-    def obs_vision(self, row_of, n_rows, vision_range, half_angle, n_cones, radii, type_col, n_cols):
+    def obs_vision(self, row_of, n_rows, vision_range, half_angle, n_cones, radii, type_col, n_cols, dirs=None):
         torch = self.torch
         out = torch.zeros((max(n_rows, 1), n_cones, n_cols), dtype=torch.float64, device=self.dev)
         _lib.check(self.lib.swarm_obs_vision(
             self.h, row_of.data_ptr(), int(n_rows), float(vision_range), float(half_angle), int(n_cones),
-            radii.data_ptr(), type_col.data_ptr(), int(type_col.numel()), int(n_cols), out.data_ptr(), self._stream()))
+            radii.data_ptr(), type_col.data_ptr(), int(type_col.numel()), int(n_cols),
+            dirs.data_ptr() if dirs is not None else None, out.data_ptr(), self._stream()))
         return out[:n_rows]
 
     def obs_position(self, row_of, n_rows, box_length):

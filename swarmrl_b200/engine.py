@@ -341,6 +341,9 @@ class SwarmEngine(Engine):
                 raise ValueError(
                     "It seems like you want to have a 2D simulation with colloids that point some amount in"
                     " Z-direction. Change something in your colloid setup.")
+            # the 2-D state is an angle: the director lies exactly in the plane from here on
+            init_direction = np.array([init_direction[0], init_direction[1], 0.0])
+            init_direction = init_direction / np.linalg.norm(init_direction)
         prop = (
             int(type_colloid),
             tuple(np.broadcast_to(np.asarray(gamma_t, dtype=float), (3,)).tolist()),
