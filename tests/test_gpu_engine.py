@@ -1,0 +1,268 @@
+"""
+GPU parity tests of the engine kernels (cell hash, Verlet lists, WCA forces, Brownian step, steepest
+descent, Philox noise) against the CPU oracle, through the C-ABI of libswarm_b200.so.
+
+Bars (BASELINE.json north_star): cell / neighbour lists bit-exact as integer sets; noise-free fp64
+trajectories within 1e-9 relative per step; Philox words bit-exact.
+"""
+import numpy as np
+import pytest
+
+from helpers import KT_300, jittered_lattice, make_pair, random_quats, rel_err, set_actions, species_for, wca_for
+
+pytestmark = pytest.mark.gpu
+
+
+def _swarm2d(n=1000, L=125.0, kT=0.0, seed=1234, radii=(1.0,), device_kw=None, periodic=True, walls=None):
+    rng = np.random.default_rng(seed)
+    sp, wca = species_for(list(radii)), wca_for(list(radii))
+    pos = jittered_lattice(n, L, 2, rng)
+    th = rng.uniform(0, 2 * np.pi, n)
+    sidx = (np.arange(n) % len(radii)).astype(np.int32)
+    o, d = make_pair(2, (L, L, L), periodic, 1e-3, kT, 42, sp, wca, pos, sidx, theta=th, device_kw=device_kw,
+                     walls=walls)
+    return o, d, sp
+
+
+def _swarm3d(n=512, L=40.0, kT=0.0, seed=99, device_kw=None, aniso=None):
+    rng = np.random.default_rng(seed)
+    sp, wca = species_for([1.0], aniso=aniso), wca_for([1.0])
+    pos = jittered_lattice(n, L, 3, rng)
+    q = random_quats(n, rng)
+    o, d = make_pair(3, (L, L, L), True, 1e-3, kT, 42, sp, wca, pos, np.zeros(n, dtype=np.int32), quat=q,
+                     device_kw=device_kw)
+    return o, d, sp
+
+
+def test_philox_gaussians_match_oracle():
+    from oracle import oracle
+
+    _, d, _ = _swarm2d(n=64)
+    for step, stream in ((0, 0), (7, 3), (2**40 + 5, 1)):
+        g = d.gaussians(64, step, stream).cpu().numpy()
+        ref = np.array([oracle.gaussians(42, i, step, stream) for i in range(64)])
+        # same Philox words; libm vs CUDA log/sincospi differ by a few ulp
+        assert np.max(np.abs(g - ref)) < 1e-13
+    big = d.gaussians(200000, 3, 0).cpu().numpy().ravel()
+    assert abs(big.mean()) < 5e-3 and abs(big.std() - 1.0) < 5e-3
+
+
+@pytest.mark.parametrize("nc", [(52, 52, 1), (7, 13, 1), (1, 1, 1)])
+def test_cell_hash_bit_exact(nc):
+    o, d, _ = _swarm2d(n=3000, L=125.0)
+    # unfold some positions by whole boxes: the hash must wrap them
+    o.x[::7] += 125.0; o.y[::5] -= 250.0
+    d.pos[0, ::7] += 125.0; d.pos[1, ::5] -= 250.0
+    assert np.array_equal(d.cell_index(nc), o.cell_index(nc))
+
+
+@pytest.mark.parametrize("persistent", [True, False])
+def test_neighbour_list_bit_exact_2d(persistent):
+    o, d, _ = _swarm2d(n=2000, L=100.0, radii=(1.0, 1.5), device_kw=dict(persistent=persistent, max_neighbors=32))
+    got = d.neighbors()
+    ref = o.pairs_within(skin=0.4)
+    assert got.shape == ref.shape and np.array_equal(got, ref)
+
+
+def test_neighbour_list_bit_exact_3d_and_nonperiodic():
+    o, d, _ = _swarm3d(n=1000, L=24.0)
+    assert np.array_equal(d.neighbors(), o.pairs_within(skin=0.4))
+    o, d, _ = _swarm2d(n=500, L=50.0, periodic=False)
+    assert np.array_equal(d.neighbors(), o.pairs_within(skin=0.4))
+
+
+def test_neighbour_list_edge_cases():
+    # empty swarm, single particle, tiny box (1-2 cells per axis)
+    from swarmrl_b200.device import DeviceSwarm
+
+    sp, wca = species_for([1.0]), wca_for([1.0])
+    d = DeviceSwarm(2, (10, 10, 10), True, 1e-3, 0.0, 1, sp, wca)
+    d.set_state(np.zeros((0, 3)), np.zeros(0, dtype=np.int32), theta=np.zeros(0))
+    assert d.neighbors().shape == (0, 2)
+    st = d.run_checked(5, 0)
+    assert st.steps_done == 0
+    d.set_state(np.array([[1.0, 2.0, 0.0]]), np.zeros(1, dtype=np.int32), theta=np.zeros(1))
+    assert d.neighbors().shape == (0, 2)
+    for L in (2.5, 5.0, 7.3):
+        rng = np.random.default_rng(3)
+        pos = np.zeros((6, 3)); pos[:, :2] = rng.uniform(0, L, (6, 2))
+        o, d = make_pair(2, (L, L, L), True, 1e-3, 0.0, 1, sp, wca, pos, np.zeros(6, dtype=np.int32),
+                         theta=np.zeros(6), device_kw=dict(max_neighbors=16))
+        assert np.array_equal(d.neighbors(), o.pairs_within(skin=0.4)), L
+
+
+def test_forces_match_oracle():
+    o, d, sp = _swarm2d(n=2000, L=80.0, radii=(1.0, 1.3))
+    n = o.n
+    set_actions(o, d, np.linspace(0, 3, n), np.zeros((n, 3)))
+    F = d.forces().cpu().numpy().T
+    ref = o.forces(mode=0)
+    assert np.abs(ref).max() > 1.0  # overlapping pairs exist
+    assert rel_err(F, ref) < 1e-12
+
+
+@pytest.mark.parametrize("persistent", [True, False])
+def test_noise_free_trajectory_2d_config2(persistent):
+    """BASELINE config 2: 1,000 colloids, WCA, 1,000 steps per slice, kT=0, <= 1e-9 relative per step."""
+    o, d, sp = _swarm2d(n=1000, L=125.0, device_kw=dict(persistent=persistent))
+    n = o.n
+    gt, gr = sp[0]["gamma_t"][0], sp[0]["gamma_r"][0]
+    set_actions(o, d, np.full(n, 5.0 * gt), np.tile([0, 0, gr * 4 * np.pi / 180], (n, 1)))
+    steps = 1000 if persistent else 200
+    o.bd_steps(0, steps, mode=2)
+    st = d.run_checked(steps, 0)
+    assert st.steps_done == steps and not st.overflow and st.persistent == int(persistent)
+    p, v, e = d.particle_data_host()
+    assert rel_err(p, o.pos) < 1e-9 and rel_err(e, o.directors, 1.0) < 1e-9
+    assert rel_err(v, o.velocities) < 1e-9
+    assert np.all(p[:, 2] == 0.0) and np.all(e[:, 2] == 0.0)
+
+
+def test_noise_free_trajectory_3d():
+    o, d, sp = _swarm3d(n=512, L=30.0)
+    n = o.n
+    gt, gr = sp[0]["gamma_t"][0], sp[0]["gamma_r"][0]
+    rng = np.random.default_rng(5)
+    set_actions(o, d, np.full(n, 5.0 * gt), rng.normal(size=(n, 3)) * gr)
+    o.bd_steps(0, 300, mode=2)
+    st = d.run_checked(300, 0)
+    assert st.steps_done == 300
+    p, v, e = d.particle_data_host()
+    assert rel_err(p, o.pos) < 1e-9 and rel_err(e, o.directors, 1.0) < 1e-9 and rel_err(v, o.velocities) < 1e-9
+    w = d.omega[:, :n].cpu().numpy().T
+    assert rel_err(w, o.omegas) < 1e-9
+
+
+def test_anisotropic_friction_3d_and_2d():
+    o, d, sp = _swarm3d(n=64, L=40.0, aniso=((1.0, 2.0, 3.0), (0.5, 0.7, 1.1)))
+    n = o.n
+    set_actions(o, d, np.full(n, 2.0), np.tile([0.3, -0.2, 1.0], (n, 1)))
+    o.bd_steps(0, 50, mode=0)
+    d.run_checked(50, 0)
+    p, v, e = d.particle_data_host()
+    assert rel_err(p, o.pos) < 1e-10 and rel_err(e, o.directors, 1.0) < 1e-10 and rel_err(v, o.velocities) < 1e-10
+
+
+def test_noisy_trajectory_same_streams():
+    """With identical Philox streams the noisy trajectory also agrees (short run: chaos amplifies ulps)."""
+    o, d, sp = _swarm2d(n=1000, L=125.0, kT=KT_300)
+    n = o.n
+    set_actions(o, d, np.full(n, 5.0 * sp[0]["gamma_t"][0]), np.zeros((n, 3)))
+    o.bd_steps(10, 100, mode=2)
+    st = d.run_checked(100, 10)
+    assert st.steps_done == 100
+    p, v, e = d.particle_data_host()
+    assert rel_err(p, o.pos) < 1e-9 and rel_err(e, o.directors, 1.0) < 1e-8
+    assert rel_err(v, o.velocities) < 1e-7
+    o3, d3, sp3 = _swarm3d(n=216, L=30.0, kT=KT_300)
+    o3.bd_steps(0, 50, mode=2)
+    d3.run_checked(50, 0)
+    p, v, e = d3.particle_data_host()
+    assert rel_err(p, o3.pos) < 1e-9 and rel_err(e, o3.directors, 1.0) < 1e-8
+
+
+def test_chunked_runs_equal_one_run():
+    """integrator.run(a); run(b) == run(a+b): the Philox counter is the global step index."""
+    _, d1, sp = _swarm2d(n=500, L=90.0, kT=KT_300)
+    _, d2, _ = _swarm2d(n=500, L=90.0, kT=KT_300)
+    f = np.full(500, 5.0 * sp[0]["gamma_t"][0])
+    set_actions(None, d1, f, np.zeros((500, 3)))
+    set_actions(None, d2, f, np.zeros((500, 3)))
+    d1.run_checked(60, 0)
+    for s0, k in ((0, 7), (7, 20), (27, 33)):
+        d2.run_checked(k, s0)
+    p1, _, e1 = d1.particle_data_host()
+    p2, _, e2 = d2.particle_data_host()
+    assert np.array_equal(p1, p2) and np.array_equal(e1, e2)
+
+
+def test_steepest_descent_relax_matches_oracle_and_removes_overlap():
+    rng = np.random.default_rng(11)
+    n, L = 400, 40.0
+    sp, wca = species_for([1.0]), wca_for([1.0])
+    pos = np.zeros((n, 3)); pos[:, :2] = rng.uniform(0, L, (n, 2))  # random => overlaps
+    o, d = make_pair(2, (L,) * 3, True, 1e-3, 0.0, 1, sp, wca, pos, np.zeros(n, dtype=np.int32),
+                     theta=rng.uniform(0, 6.28, n), device_kw=dict(max_neighbors=32))
+    o.sd_steps(200, 0.1, 0.1, mode=2)
+    st = d.relax_checked(200)
+    assert st.steps_done <= 200
+    p, _, _ = d.particle_data_host()
+    assert rel_err(p, o.pos) < 1e-8
+    o.sd_steps(800, 0.1, 0.1, mode=2)
+    d.relax_checked(800)
+    p, _, _ = d.particle_data_host()
+    dx = p[:, None, :2] - p[None, :, :2]
+    dx -= L * np.round(dx / L)
+    r = np.sqrt((dx**2).sum(-1)) + 10 * np.eye(n)
+    assert r.min() > 1.9
+
+
+def test_walls_keep_particles_inside():
+    """test_confining_walls.py:40-51 -- driven particles stay in the box (inequalities only)."""
+    walls = dict(sigma=[1.0 * 2 ** (-1 / 6)], eps=[1.0], cut=[1.0])
+    o, d, sp = _swarm2d(n=100, L=40.0, periodic=False, walls=walls)
+    n = o.n
+    set_actions(o, d, np.full(n, 20.0 * sp[0]["gamma_t"][0]), np.zeros((n, 3)))
+    o.bd_steps(0, 3000, mode=0)
+    d.run_checked(3000, 0)
+    p, _, _ = d.particle_data_host()
+    assert p[:, :2].min() > 0.0 and p[:, :2].max() < 40.0
+    assert rel_err(p, o.pos) < 1e-6
+
+
+def test_verlet_overflow_is_reported_and_recovered():
+    rng = np.random.default_rng(2)
+    n, L = 300, 12.0
+    sp, wca = species_for([1.0]), wca_for([1.0])
+    pos = np.zeros((n, 3)); pos[:, :2] = rng.uniform(0, L, (n, 2))
+    _, d = make_pair(2, (L,) * 3, True, 1e-3, 0.0, 1, sp, wca, pos, np.zeros(n, dtype=np.int32), theta=np.zeros(n),
+                     device_kw=dict(max_neighbors=2))
+    d.relax(10)
+    st = d.stats()
+    assert st.overflow == 1 and st.steps_done == 0
+    st = d.relax_checked(10)
+    assert st.overflow == 0 and st.capacity > 2
+
+
+def test_new_direction_2d_and_3d():
+    """espresso.py:1236-1249; test_espresso_2d.py:84-92."""
+    o, d, _ = _swarm2d(n=50)
+    rng = np.random.default_rng(8)
+    ang = rng.uniform(0, 2 * np.pi, 50)
+    nd = np.stack([np.cos(ang), np.sin(ang), np.zeros(50)], 1)
+    has = (np.arange(50) % 2).astype(np.int32)
+    d.set_new_directions_host(nd, has)
+    e0 = d.directors().cpu().numpy().T.copy()
+    d.apply_new_direction()
+    e1 = d.directors().cpu().numpy().T
+    assert np.allclose(e1[has == 1], nd[has == 1], atol=1e-12) and np.array_equal(e1[has == 0], e0[has == 0])
+    o3, d3, _ = _swarm3d(n=40)
+    v = rng.normal(size=(40, 3)); v /= np.linalg.norm(v, axis=1, keepdims=True)
+    d3.set_new_directions_host(v, np.ones(40, dtype=np.int32))
+    d3.apply_new_direction()
+    assert np.allclose(d3.directors().cpu().numpy().T, v, atol=1e-12)
+
+
+def test_batched_environments_are_independent():
+    """n_envs > 1: each block of n/n_envs particles is its own periodic box (BASELINE config 3)."""
+    E, m, L = 8, 32, 60.0
+    rng = np.random.default_rng(17)
+    sp, wca = species_for([1.0]), wca_for([1.0])
+    pos = np.concatenate([jittered_lattice(m, L, 2, rng) for _ in range(E)])
+    th = rng.uniform(0, 2 * np.pi, E * m)
+    from swarmrl_b200.device import DeviceSwarm
+    from oracle.oracle import OracleSwarm
+
+    d = DeviceSwarm(2, (L,) * 3, True, 1e-2, 0.0, 42, sp, wca, n_envs=E)
+    d.set_state(pos, np.zeros(E * m, dtype=np.int32), theta=th)
+    f = np.full(E * m, 5.0 * sp[0]["gamma_t"][0])
+    d.set_actions_host(f, np.zeros((E * m, 3)))
+    d.run_checked(400, 0)
+    p, _, _ = d.particle_data_host()
+    for e in range(E):
+        o = OracleSwarm(2, (L,) * 3, True, 1e-2, 0.0, 42, sp, wca)
+        sl = slice(e * m, (e + 1) * m)
+        o.set_state(pos[sl], np.zeros(m, dtype=np.int32), theta=th[sl])
+        o.f_swim[:] = f[sl]
+        o.bd_steps(0, 400, mode=0)
+        assert rel_err(p[sl], o.pos) < 1e-9, e

@@ -1,0 +1,171 @@
+"""
+GPU parity tests of the observable / reward kernels against the oracle and the golden vectors
+generated from the reference's own Python (oracle/make_golden.py), through the C-ABI.
+"""
+import numpy as np
+import pytest
+
+from helpers import jittered_lattice, make_pair, species_for, wca_for
+
+pytestmark = pytest.mark.gpu
+
+
+def _pair(n=3000, L=300.0, radii=(1.0, 1.0), seed=4):
+    rng = np.random.default_rng(seed)
+    sp, wca = species_for(list(radii)), wca_for(list(radii))
+    pos = jittered_lattice(n, L, 2, rng)
+    pos[::9, 0] += L  # unfolded coordinates: the reference takes raw differences
+    th = rng.uniform(0, 2 * np.pi, n)
+    sidx = (rng.uniform(size=n) < 0.3).astype(np.int32)
+    return make_pair(2, (L,) * 3, True, 1e-3, 0.0, 1, sp, wca, pos, sidx, theta=th), rng
+
+
+SPECIES8 = [dict(type=t, gamma_t=(1.0,) * 3, gamma_r=(1.0,) * 3, mass=1.0, rinertia=(1.0,) * 3) for t in range(8)]
+ZERO_WCA = dict(sigma=np.zeros((8, 8)), eps=np.zeros((8, 8)), cut=np.zeros((8, 8)))
+
+
+def _golden_swarm(pos, types, dirs=None):
+    from swarmrl_b200.device import DeviceSwarm
+
+    d = DeviceSwarm(2, (1.0, 1.0, 1.0), False, 1.0, 0.0, 0, SPECIES8, ZERO_WCA)
+    th = np.zeros(len(pos)) if dirs is None else np.arctan2(dirs[:, 1], dirs[:, 0])
+    d.set_state(pos, np.asarray(types, dtype=np.int32), theta=th)
+    return d
+
+
+@pytest.mark.parametrize("case", ["ref_unit", "rand64", "rand200_narrow", "rand150_wide"])
+def test_vision_cones_golden(golden, case):
+    """Fixtures produced by the reference's own SubdividedVisionCones (ref_unit is the literal case of
+    CI/unit_tests/observables/test_subdivided_vision_cone.py:17-53), replayed on the device."""
+    import torch
+
+    g = golden("vision_cones.npz")
+    pos, dirs, types = g[f"{case}/pos"], g[f"{case}/dirs"], g[f"{case}/types"]
+    d = _golden_swarm(pos, types, dirs)
+    det = [int(t) for t in g[f"{case}/detected_types"]]
+    tc = -np.ones(8, dtype=np.int32)
+    for c, t in enumerate(det):
+        tc[t] = c
+    row_of, rows = d.row_map(int(g[f"{case}/particle_type"]))
+    out = d.obs_vision(row_of, rows, float(g[f"{case}/vision_range"]), float(g[f"{case}/half_angle"]),
+                       int(g[f"{case}/n_cones"]), torch.from_numpy(g[f"{case}/radii"].astype(np.float64)).to(d.dev),
+                       torch.from_numpy(tc).to(d.dev), len(det)).cpu().numpy()
+    ref = g[f"{case}/obs"]
+    assert out.shape == ref.shape and np.max(np.abs(out - ref)) < 1e-12
+    if case == "ref_unit":
+        assert np.allclose(out[0], [[1.0, 0.0], [0.8, 0.75], [0.0, 0.0]], atol=1e-15)
+
+
+@pytest.mark.parametrize("n_cones,half_angle,rng_", [(5, np.pi / 2, 10.0), (3, np.pi, 25.0), (1, 0.3, 40.0)])
+def test_vision_cones_match_oracle(n_cones, half_angle, rng_):
+    import torch
+
+    (o, d), rng = _pair()
+    n = o.n
+    radii = rng.uniform(0.5, 2.0, n)
+    for want, det in ((0, [0, 1]), (1, [1])):
+        row_of, rows = d.row_map(want)
+        tc = -np.ones(2, dtype=np.int32)
+        for c, t in enumerate(det):
+            tc[t] = c
+        out = d.obs_vision(row_of, rows, rng_, half_angle, n_cones, torch.from_numpy(radii).to(d.dev),
+                           torch.from_numpy(tc).to(d.dev), len(det)).cpu().numpy()
+        ref = o.vision_cones(want, rng_, half_angle, n_cones, radii, det)
+        assert out.shape == ref.shape and ref.sum() > 0
+        # rim tests are strict inequalities on acos(): allow an ulp-level reassignment of one neighbour
+        bad = np.abs(out - ref) > 1e-9
+        assert bad.sum() <= 2, bad.sum()
+
+
+def test_field_observable_and_gradient_reward_match_oracle():
+    (o, d), rng = _pair(n=5000)
+    n = o.n
+    L = 300.0
+    import torch
+
+    src = (0.5, 0.4, 0.0)
+    hist_o = np.ascontiguousarray((o.pos / L).T.copy())
+    hist_d = torch.from_numpy(hist_o.copy()).to(d.dev)
+    # move, then evaluate
+    shift = rng.normal(size=(n, 3)) * 3.0
+    shift[:, 2] = 0.0
+    o.x += shift[:, 0]; o.y += shift[:, 1]
+    d.pos[:, :n] += torch.from_numpy(np.ascontiguousarray(shift.T)).to(d.dev)
+    row_of, rows = d.row_map(0)
+    dn, dp = o.field_distances(0, src, (L, L, L), hist_o)
+    out, gn, gp = d.obs_field(row_of, rows, src, (L, L, L), hist_d, decay=1, c0=1.0, c1=-1.0, scale=100.0, clip=True)
+    assert np.max(np.abs(gn.cpu().numpy() - dn)) < 1e-14 and np.max(np.abs(gp.cpu().numpy() - dp)) < 1e-14
+    ref = np.clip(100.0 * ((1 - dn) - (1 - dp)), 0, None)
+    assert np.max(np.abs(out.cpu().numpy() - ref)) < 1e-11
+    assert np.array_equal(hist_d.cpu().numpy()[:, o.ptype == 0], hist_o[:, o.ptype == 0])
+    # rows of the other type were left alone
+    assert np.array_equal(hist_d.cpu().numpy()[:, o.ptype == 1], (o.pos - shift)[o.ptype == 1].T / L)
+    # unclipped observable (ConcentrationField) and the other decay kinds
+    for kind, f in ((2, lambda x: 2.0 * np.exp(-0.5 * x)), (3, lambda x: 2.0 / (x + 0.5))):
+        h2 = torch.from_numpy(((o.pos - shift) / L).T.copy()).to(d.dev)
+        out, gn, gp = d.obs_field(row_of, rows, src, (L, L, L), h2, decay=kind, c0=2.0, c1=0.5, scale=3.0, clip=False)
+        ref = 3.0 * (f(gn.cpu().numpy()) - f(gp.cpu().numpy()))
+        assert np.max(np.abs(out.cpu().numpy() - ref)) < 1e-12
+
+
+@pytest.mark.parametrize("name,clip", [("gradient_sensing.npz", True), ("concentration_field.npz", False)])
+def test_field_sequences_golden(golden, name, clip):
+    """Sequences produced by the reference's GradientSensing / ConcentrationField (decay 1 - d)."""
+    import torch
+
+    g = golden(name)
+    traj, types, box, src = g["traj"], g["types"], g["box"], g["src"]
+    n = traj.shape[1]
+    d = _golden_swarm(traj[0], types)
+    hist = torch.from_numpy(np.ascontiguousarray((traj[0] / box).T)).to(d.dev)
+    row_of, rows = d.row_map(int(g["particle_type"]))
+    outs = []
+    for s in range(1, traj.shape[0]):
+        d.pos[:, :n] = torch.from_numpy(np.ascontiguousarray(traj[s].T)).to(d.dev)
+        out, _, _ = d.obs_field(row_of, rows, src / box, box, hist, decay=1, c0=1.0, c1=-1.0,
+                                scale=float(g["scale"]), clip=clip, want_dist=False)
+        outs.append(out.cpu().numpy().copy())
+    ref = g["rewards"] if clip else g["obs"][..., 0]
+    assert np.max(np.abs(np.array(outs) - ref)) < (1e-12 if clip else 1e-9)
+
+
+def test_gradient_sensing_reference_unit(golden):
+    """CI/unit_tests/tasks/test_gradient_sensing.py:70-113 known answers through the device kernel."""
+    import torch
+
+    g = golden("gradient_sensing_unit.npz")
+    p0, p1 = g["p0"], g["p1"]
+    d = _golden_swarm(p1, np.zeros(3, dtype=np.int32))
+    hist = torch.from_numpy(np.ascontiguousarray(p0.T.copy())).to(d.dev)
+    row_of, rows = d.row_map(0)
+    out, _, _ = d.obs_field(row_of, rows, (0.5, 0.5, 0.0), (1.0, 1.0, 1.0), hist, decay=1, c0=1.0, c1=-1.0, scale=1.0,
+                            clip=True)
+    r = out.cpu().numpy()
+    assert np.max(np.abs(r - g["rewards"])) < 1e-15 and r[1] == 0.0
+    assert np.array_equal(hist.cpu().numpy().T, p1)
+
+
+def test_position_golden(golden):
+    g = golden("position_director.npz")
+    d = _golden_swarm(g["pos"], g["types"], g["dirs"])
+    row_of, rows = d.row_map(1)
+    out = d.obs_position(row_of, rows, g["box"]).cpu().numpy()
+    assert np.max(np.abs(out - g["position_obs_type1"])) < 1e-15
+    e = d.directors().cpu().numpy().T
+    assert np.max(np.abs(e[g["types"] == 2] - g["director_obs_type2"])) < 1e-12
+
+
+def test_position_observable_and_mean_reduction():
+    (o, d), rng = _pair(n=4097)
+    row_of, rows = d.row_map(1)
+    out = d.obs_position(row_of, rows, (300.0, 300.0, 300.0)).cpu().numpy()
+    assert np.array_equal(out, o.pos[o.ptype == 1] / 300.0)
+    import torch
+
+    for m in (0, 1, 31, 100003):
+        v = rng.normal(size=m)
+        r = d.reduce_mean(torch.from_numpy(v).to(d.dev)).cpu().numpy()
+        assert abs(r[0] - v.sum()) < 1e-9 and (m == 0 or abs(r[1] - v.mean()) < 1e-12)
+    # deterministic: identical bits run to run
+    v = torch.from_numpy(rng.normal(size=50000)).to(d.dev)
+    assert np.array_equal(d.reduce_mean(v).cpu().numpy(), d.reduce_mean(v).cpu().numpy())
