@@ -1,0 +1,412 @@
+#!/usr/bin/env python
+"""
+bench.py -- headline benchmark of the SwarmRL rollout hot path on B200 (BASELINE.json metric:
+agent-steps/sec at 100k agents).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+Workload (BASELINE config 4, SURVEY.md 8d "C4"): one swarm of 100,000 active colloids, r = 1 um,
+periodic 2-D box L = 1772 um (phi = 0.10), dt = 1e-3 s, kT = 300 K, 100 integrator steps per action
+slice.  One bench "step" = one action slice of `SwarmEngine.integrate`:
+    manage_forces (write f_swim / ext torque of every agent)          espresso.py:1203-1249
+    integrator.run(100)  Brownian dynamics + WCA + Verlet lists + Philox   espresso.py:1304-1306
+    SubdividedVisionCones observable (range 10, half angle pi/2, 5 cones)  subdivided_vision_cones.py:83-258
+    GradientSensing reward + its mean                                      gradient_sensing.py:92-150, trainer.py:92-95
+value  = N * 100 * K / (device time of K slices), inputs resident in HBM.
+e2e    = the same slice through the host-buffer C-ABI (swarm_set_actions_host -> run -> observable ->
+         D2H of the observable and the reward mean), actions coming from pinned host memory.
+N > 1  : ensemble sharding -- every rank advances its own independent 100k-agent swarm (weak scaling,
+         no data-path collective; torch.distributed only for the barrier and the max-over-ranks time).
+--impl reference : ESPResSo is not installable here, so the reference arm times the CPU oracle
+         (oracle/swarm_oracle.c, OpenMP, all host threads) on a bounded sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import pathlib
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = pathlib.Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+N_AGENTS = 100_000
+BOX = 1772.0
+DT = 1e-3
+STEPS_PER_SLICE = 100
+KT = 300.0 / 293.0
+SEED = 42
+ETA = 0.2200
+VISION = dict(range=10.0, half_angle=np.pi / 2, n_cones=5)
+BYTES_PER_AGENT_STEP = 68  # 2-D steady-state step, read 44 B + write 24 B
+METRIC = "agent_steps_per_sec_100k_agents"
+UNIT = "agent-steps/s"
+
+
+def stokes(r):
+    return 6 * np.pi * ETA * r, 8 * np.pi * ETA * r**3
+
+
+def species_table():
+    gt, gr = stokes(1.0)
+    m = 1000.0 / 4.0453e-9 * 1e-18 * 4.0 / 3.0 * np.pi
+    return [dict(type=0, gamma_t=(gt,) * 3, gamma_r=(gr,) * 3, mass=m, rinertia=(0.4 * m,) * 3)]
+
+
+def wca_table():
+    s = 2.0 * 2 ** (-1 / 6)
+    return dict(sigma=np.array([[s]]), eps=np.array([[297.0 / 293.0]]), cut=np.array([[2.0]]))
+
+
+def initial_state(n, L, seed):
+    """Jittered square lattice (no overlaps at phi = 0.10), directors uniform on the circle."""
+    rng = np.random.default_rng(seed)
+    m = int(np.ceil(np.sqrt(n)))
+    a = L / m
+    idx = np.arange(n)
+    pos = np.zeros((n, 3))
+    pos[:, 0] = (idx % m + 0.5) * a
+    pos[:, 1] = (idx // m + 0.5) * a
+    pos[:, :2] += rng.uniform(-0.25 * a, 0.25 * a, (n, 2))
+    return pos, rng.uniform(0, 2 * np.pi, n)
+
+
+def action_sets(n, seed, n_sets=4):
+    """Random-policy actions from the 4 actions of the reference's RL tests (test_rl_trainers.py:36-46):
+    translate (f = gamma_t * 5 um/s), rotate CCW / CW (tau_z = +-gamma_r * 4 pi/180 rad/s ... scaled), none."""
+    gt, gr = stokes(1.0)
+    rng = np.random.default_rng(seed)
+    table_f = np.array([5.0 * gt, 0.0, 0.0, 0.0])
+    table_t = np.array([0.0, gr * 10.0, -gr * 10.0, 0.0])
+    out = []
+    for _ in range(n_sets):
+        a = rng.integers(0, 4, n)
+        tq = np.zeros((n, 3))
+        tq[:, 2] = table_t[a]
+        out.append((np.ascontiguousarray(table_f[a]), tq))
+    return out
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi SM clock / throttle reasons sampled while the timed region runs."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz, self._halt = index, [], set(), None, threading.Event()
+
+    def _q(self, fields):
+        try:
+            r = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={fields}", "--format=csv,noheader,nounits"],
+                               capture_output=True, text=True, timeout=5)
+            return [v.strip() for v in r.stdout.strip().split(",")]
+        except Exception:
+            return None
+
+    def run(self):
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap", "hw_power_brake_slowdown"]
+        q = "clocks.sm,clocks.max.sm," + ",".join("clocks_throttle_reasons." + n for n in names)
+        while not self._halt.is_set():
+            v = self._q(q)
+            if v and len(v) >= 2 + len(names):
+                try:
+                    self.samples.append(float(v[0]))
+                    self.max_mhz = float(v[1])
+                except ValueError:
+                    pass
+                for nme, val in zip(names, v[2:]):
+                    if val.lower().startswith("active"):
+                        self.reasons.add(nme)
+            self._halt.wait(0.05)
+
+    def stop(self):
+        self._halt.set()
+        self.join(timeout=6)
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# --------------------------------------------------------------------------------------------------
+# CPU arm: the oracle port of the reference path on the host cores (ESPResSo itself is unavailable)
+# --------------------------------------------------------------------------------------------------
+def cpu_slice_rate(sample_steps=40, observers=2000, threads=None):
+    """Times a bounded sample of the same workload with the CPU oracle and returns the agent-steps/s of
+    one full action slice: t_slice = 100 * t_step + t_vision(N observers) + t_reward, where t_step comes
+    from `sample_steps` BD steps of all 100k agents (Verlet lists, skin 0.4, Philox noise) and t_vision
+    from `observers` observers against all 100k particles (the reference's O(N^2) scan) scaled to N."""
+    from oracle import oracle
+    from oracle.oracle import OracleSwarm
+
+    if threads:
+        oracle.set_num_threads(threads)
+    cores = oracle.num_threads()
+    n = N_AGENTS
+    pos, th = initial_state(n, BOX, SEED)
+    o = OracleSwarm(2, (BOX,) * 3, True, DT, KT, SEED, species_table(), wca_table())
+    o.set_state(pos, np.zeros(n, dtype=np.int32), theta=th)
+    f, tq = action_sets(n, 7, 1)[0]
+    o.f_swim[:] = f
+    o.torque[2][:] = tq[:, 2]
+    o.bd_steps(0, 2, mode=2)  # warm
+    t0 = time.perf_counter()
+    o.bd_steps(2, sample_steps, mode=2)
+    t_step = (time.perf_counter() - t0) / sample_steps
+    # vision: only `observers` particles carry the observer type; everybody is seen
+    o.ptype = np.ones(n, dtype=np.int32)
+    o.ptype[:: n // observers] = 0
+    rows = int((o.ptype == 0).sum())
+    t0 = time.perf_counter()
+    o.vision_cones(0, VISION["range"], VISION["half_angle"], VISION["n_cones"], np.ones(n), [0, 1])
+    t_vis = (time.perf_counter() - t0) * n / rows
+    o.ptype = np.zeros(n, dtype=np.int32)
+    hist = np.ascontiguousarray((o.pos / BOX).T)
+    t0 = time.perf_counter()
+    dn, dp = o.field_distances(0, (0.5, 0.5, 0.0), (BOX,) * 3, hist)
+    float(np.clip(10.0 * ((1 - dn) - (1 - dp)), 0, None).mean())
+    t_rew = time.perf_counter() - t0
+    t_slice = STEPS_PER_SLICE * t_step + t_vis + t_rew
+    return dict(value=n * STEPS_PER_SLICE / t_slice, unit=UNIT, cores=cores, kind="port",
+                sample=f"{sample_steps} BD steps of all {n} agents + vision cones for {rows} observers (scaled to {n}) "
+                       f"+ 1 reward pass; t_step={t_step*1e3:.2f} ms, t_vision(N)={t_vis:.2f} s",
+                t_step_ms=t_step * 1e3, t_vision_s=t_vis, integrator_only=n / t_step)
+
+
+def config_dict(n_gpus):
+    return {"workload": "C4: 100,000-agent single swarm, 2-D periodic L=1772 (phi=0.10), WCA + Brownian dynamics "
+                        "kT=300K dt=1e-3, 100 steps/slice, vision cones (range 10, 5 cones) + gradient-sensing reward mean",
+            "n_agents": N_AGENTS, "steps_per_slice": STEPS_PER_SLICE,
+            "parallelism": "single GPU" if n_gpus == 1 else f"ensemble-sharded: {n_gpus} independent 100k swarms, no collective",
+            "l2": "working set (6.8 MB) is L2-resident; L2 flushed (256 MiB write) between timed slices, outside the events"}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    vals = []
+    for _ in range(max(1, args.warmup // 3)):
+        cpu_slice_rate(sample_steps=5, observers=500)
+    t_all = time.perf_counter()
+    last = None
+    for _ in range(args.steps):
+        last = cpu_slice_rate(sample_steps=20, observers=1000)
+        vals.append(last["value"])
+    v = float(np.mean(vals))
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": N_AGENTS * STEPS_PER_SLICE / v * 1e3, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config_dict(args.gpus),
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": last["cores"], "kind": "port", "sample": last["sample"]},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "note": "ESPResSo (the reference's physics backend) is not installable offline; this arm is the CPU oracle "
+                    "port of the same path, OpenMP over all host threads", "wall_s": time.perf_counter() - t_all}
+    print(json.dumps(line))
+
+
+# --------------------------------------------------------------------------------------------------
+# GPU arm
+# --------------------------------------------------------------------------------------------------
+class Rollout:
+    """One 100k-agent swarm on one GPU and the per-slice work of the rollout hot path."""
+
+    def __init__(self, device_index, seed, skin):
+        import torch
+        from swarmrl_b200.device import DeviceSwarm
+
+        self.torch = torch
+        n = N_AGENTS
+        pos, th = initial_state(n, BOX, seed)
+        self.d = d = DeviceSwarm(2, (BOX,) * 3, True, DT, KT, seed, species_table(), wca_table(), skin=skin,
+                                 device=device_index)
+        d.set_state(pos, np.zeros(n, dtype=np.int32), theta=th)
+        self.row_of, self.rows = d.row_map(0)
+        f64 = dict(dtype=torch.float64, device=d.dev)
+        self.radii = torch.ones(n, **f64)
+        self.type_col = torch.zeros(1, dtype=torch.int32, device=d.dev)
+        self.hist = (d.pos[:, :n] / BOX).contiguous()
+        sets = action_sets(n, 7 + seed)
+        # device-resident action sets (value) and pinned host copies (e2e)
+        self.act_dev = [(torch.from_numpy(f).to(d.dev), torch.from_numpy(np.ascontiguousarray(t.T)).to(d.dev)) for f, t in sets]
+        self.act_pin = [(torch.from_numpy(f).pin_memory(), torch.from_numpy(t).pin_memory()) for f, t in sets]
+        self.obs_pin = torch.empty((n, VISION["n_cones"], 1), dtype=torch.float64).pin_memory()
+        self.mean_pin = torch.empty(2, dtype=torch.float64).pin_memory()
+        self.step_idx = 0
+        self.flush_buf = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=d.dev)
+        self.run_ms = []
+        self.h2d = sum(f.numel() * 8 + t.numel() * 8 for f, t in self.act_pin[:1])
+        self.d2h = self.obs_pin.numel() * 8 + 16
+
+    def flush_l2(self):
+        self.flush_buf.fill_(1)
+
+    def _physics_and_obs(self, time_run):
+        d, torch = self.d, self.torch
+        if time_run:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+        d.run(STEPS_PER_SLICE, self.step_idx)
+        if time_run:
+            e1.record()
+            self.run_events.append((e0, e1))
+        self.step_idx += STEPS_PER_SLICE
+        obs = d.obs_vision(self.row_of, self.rows, VISION["range"], VISION["half_angle"], VISION["n_cones"], self.radii,
+                           self.type_col, 1)
+        rew, _, _ = d.obs_field(self.row_of, self.rows, (0.5, 0.5, 0.0), (BOX,) * 3, self.hist, decay=1, c0=1.0, c1=-1.0,
+                                scale=10.0, clip=True, want_dist=False)
+        mean = d.reduce_mean(rew)
+        return obs, mean
+
+    def slice_resident(self, k, time_run=False):
+        """manage_forces from device-resident actions -> run -> observable -> reward mean (all in HBM)."""
+        f, t = self.act_dev[k % len(self.act_dev)]
+        self.d.f_swim[: N_AGENTS].copy_(f)
+        self.d.torque[:, : N_AGENTS].copy_(t)
+        return self._physics_and_obs(time_run)
+
+    def slice_e2e(self, k):
+        """Same slice through the host-buffer C-ABI: pinned host actions in, observable + reward mean out."""
+        import ctypes as C
+        from swarmrl_b200 import _lib
+
+        f, t = self.act_pin[k % len(self.act_pin)]
+        d = self.d
+        _lib.check(d.lib.swarm_set_actions_host(d.h, C.c_void_p(f.data_ptr()), C.c_void_p(t.data_ptr()), d._stream()))
+        obs, mean = self._physics_and_obs(False)
+        self.obs_pin.copy_(obs, non_blocking=True)
+        self.mean_pin.copy_(mean, non_blocking=True)
+        self.torch.cuda.current_stream().synchronize()
+        return float(self.mean_pin[1])
+
+    run_events = []
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    from swarmrl_b200 import _lib
+
+    _lib.load()  # raises if the CUDA library is missing: there is no fallback
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (B200); there is no CPU fallback")
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    n_gpus = world
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    ro = Rollout(local, SEED + rank, args.skin)
+    K, W = args.steps, args.warmup
+    for k in range(W):
+        ro.slice_resident(k)
+    st = ro.d.stats()
+    if st.overflow or st.steps_done != STEPS_PER_SLICE:
+        raise SystemExit(f"warm-up run halted: steps_done={st.steps_done} overflow={st.overflow}")
+    launches0, rebuilds0 = st.launches, st.rebuilds
+
+    # ---- device-resident arm ---------------------------------------------------------------------
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    ro.run_events = []
+    barrier()
+    t_wall0 = time.perf_counter()
+    for k in range(K):
+        ro.flush_l2()
+        ev[k][0].record()
+        ro.slice_resident(W + k, time_run=True)
+        ev[k][1].record()
+    barrier()
+    t_wall = time.perf_counter() - t_wall0
+    st = ro.d.stats()
+    if st.overflow or st.steps_done != STEPS_PER_SLICE:
+        raise SystemExit(f"timed run halted: steps_done={st.steps_done} overflow={st.overflow}")
+    dev_ms = sum(a.elapsed_time(b) for a, b in ev)
+    run_ms = [a.elapsed_time(b) for a, b in ro.run_events]
+    launches = int(st.launches - launches0) + 2 * K  # + the two D2D action copies per slice (torch)
+    rebuilds = int(st.rebuilds - rebuilds0)
+
+    # ---- end-to-end arm (host buffers through the C-ABI) ---------------------------------------------
+    for k in range(min(W, 3)):
+        ro.slice_e2e(k)
+    ev2 = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    barrier()
+    for k in range(K):
+        ro.flush_l2()
+        ev2[k][0].record()
+        ro.slice_e2e(k)
+        ev2[k][1].record()
+    barrier()
+    e2e_ms = sum(a.elapsed_time(b) for a, b in ev2)
+    clocks = sampler.stop() if rank == 0 else None
+
+    t = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms, e2e_ms = float(t[0]), float(t[1])
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    units = N_AGENTS * STEPS_PER_SLICE * K * n_gpus
+    value = units / (dev_ms * 1e-3)
+    e2e = units / (e2e_ms * 1e-3)
+    peaks = {}
+    try:
+        peaks = json.loads((ROOT / "MEASURED_PEAKS.json").read_text())
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6554.6))
+    run_avg_ms = float(np.mean(run_ms))
+    achieved = N_AGENTS * STEPS_PER_SLICE * BYTES_PER_AGENT_STEP / (run_avg_ms * 1e-3) / 1e9
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": K, "warmup": W,
+            "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic", "config": dict(config_dict(n_gpus), skin=args.skin, rebuilds_per_slice=rebuilds / K,
+                                               persistent=bool(st.persistent)),
+            "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": ro.h2d, "d2h_bytes_per_step": ro.d2h,
+                    "ms_per_step": e2e_ms / K},
+            "gpu_launches": launches,
+            "roofline": {"bound": "hbm", "kernel": "k_persist<2,true> (one cooperative launch = 100 steps)",
+                         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                         "bytes_per_launch": N_AGENTS * STEPS_PER_SLICE * BYTES_PER_AGENT_STEP,
+                         "launch_ms": run_avg_ms, "share_of_step": run_avg_ms * K / dev_ms,
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback"},
+            "clocks": clocks, "wall_s_timed": t_wall}
+    if n_gpus == 1 and not args.no_cpu:
+        cb = cpu_slice_rate(sample_steps=args.cpu_steps, observers=2000)
+        line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--skin", type=float, default=0.4, help="Verlet skin (performance only; espresso.py:269 uses 0.4)")
+    ap.add_argument("--cpu-steps", type=int, default=100, help="BD steps of the cpu_baseline sample")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()
