@@ -178,18 +178,18 @@ def test_chunked_runs_equal_one_run():
 
 def test_steepest_descent_relax_matches_oracle_and_removes_overlap():
     rng = np.random.default_rng(11)
-    n, L = 400, 40.0
+    n, L = 400, 80.0  # phi = 0.2: random placement overlaps, and the overlaps can be relaxed away
     sp, wca = species_for([1.0]), wca_for([1.0])
-    pos = np.zeros((n, 3)); pos[:, :2] = rng.uniform(0, L, (n, 2))  # random => overlaps
+    pos = np.zeros((n, 3)); pos[:, :2] = rng.uniform(0, L, (n, 2))
     o, d = make_pair(2, (L,) * 3, True, 1e-3, 0.0, 1, sp, wca, pos, np.zeros(n, dtype=np.int32),
                      theta=rng.uniform(0, 6.28, n), device_kw=dict(max_neighbors=32))
-    o.sd_steps(200, 0.1, 0.1, mode=2)
-    st = d.relax_checked(200)
-    assert st.steps_done <= 200
+    o.sd_steps(50, 0.1, 0.1, mode=2)
+    st = d.relax_checked(50)
+    assert st.steps_done <= 50
     p, _, _ = d.particle_data_host()
     assert rel_err(p, o.pos) < 1e-8
-    o.sd_steps(800, 0.1, 0.1, mode=2)
-    d.relax_checked(800)
+    o.sd_steps(950, 0.1, 0.1, mode=2)
+    d.relax_checked(950)
     p, _, _ = d.particle_data_host()
     dx = p[:, None, :2] - p[None, :, :2]
     dx -= L * np.round(dx / L)
@@ -202,12 +202,14 @@ def test_walls_keep_particles_inside():
     walls = dict(sigma=[1.0 * 2 ** (-1 / 6)], eps=[1.0], cut=[1.0])
     o, d, sp = _swarm2d(n=100, L=40.0, periodic=False, walls=walls)
     n = o.n
-    set_actions(o, d, np.full(n, 20.0 * sp[0]["gamma_t"][0]), np.zeros((n, 3)))
-    o.bd_steps(0, 3000, mode=0)
-    d.run_checked(3000, 0)
+    set_actions(o, d, np.full(n, 5.0 * sp[0]["gamma_t"][0]), np.zeros((n, 3)))
+    o.bd_steps(0, 4000, mode=0)
+    d.run_checked(4000, 0)
     p, _, _ = d.particle_data_host()
-    assert p[:, :2].min() > 0.0 and p[:, :2].max() < 40.0
-    assert rel_err(p, o.pos) < 1e-6
+    assert rel_err(p, o.pos) < 1e-7
+    for q in (p, o.pos):
+        assert q[:, :2].min() > 0.0 and q[:, :2].max() < 40.0
+    assert (p[:, :2].min() < 1.0) or (p[:, :2].max() > 39.0)  # somebody is actually leaning on a wall
 
 
 def test_verlet_overflow_is_reported_and_recovered():
