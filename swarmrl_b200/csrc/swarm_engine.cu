@@ -23,6 +23,7 @@
 #include <mutex>
 
 #include "swarm_common.cuh"
+#include "swarm_math.cuh"
 
 #define SW_MAXCAP 128         // hard ceiling of the Verlet capacity
 #define SW_IDX_MASK 0x0FFFFFFF
@@ -242,7 +243,7 @@ __device__ __forceinline__ bool phase_step(const DevParams &P, const DevArrays &
     } else {
       const double gt1 = P.sp_gt[sp][1], gt2 = P.sp_gt[sp][2], gr0 = P.sp_gr[sp][0];
       double g[4] = {0.0, 0.0, 0.0, 0.0};
-      if (NOISE) sw_gaussians(P.seed, (u64)i, step, 0, g);
+      if (NOISE) swm_gaussians(P.seed, (u64)i, step, 0, g);
       double vx, vy;
       if (gt1 == gt2) {
         vx = F[0] / gt2; vy = F[1] / gt2;
@@ -269,8 +270,8 @@ __device__ __forceinline__ bool phase_step(const DevParams &P, const DevArrays &
         double gv[4] = {0, 0, 0, 0}, gw[4] = {0, 0, 0, 0};
         double sv = 0.0, sw = 0.0;
         if (NOISE) {
-          sw_gaussians(P.seed, (u64)i, step, 2, gv);
-          sw_gaussians(P.seed, (u64)i, step, 3, gw);
+          swm_gaussians(P.seed, (u64)i, step, 2, gv);
+          swm_gaussians(P.seed, (u64)i, step, 3, gw);
           sv = sqrt(kT / P.sp_mass[sp]);
           sw = sqrt(kT / P.sp_rin[sp][0]);
         }
@@ -300,7 +301,7 @@ __device__ __forceinline__ bool phase_step(const DevParams &P, const DevArrays &
     } else {
       const double *gt = P.sp_gt[sp], *gr = P.sp_gr[sp];
       double g[4] = {0.0, 0.0, 0.0, 0.0};
-      if (NOISE) sw_gaussians(P.seed, (u64)i, step, 0, g);
+      if (NOISE) swm_gaussians(P.seed, (u64)i, step, 0, g);
       const bool aniso = (gt[0] != gt[1] || gt[1] != gt[2]);
       double v[3];
       if (!aniso) {
@@ -341,7 +342,7 @@ __device__ __forceinline__ bool phase_step(const DevParams &P, const DevArrays &
       }
       if (NOISE) {
         double g1[4];
-        sw_gaussians(P.seed, (u64)i, step, 1, g1);
+        swm_gaussians(P.seed, (u64)i, step, 1, g1);
         double dr[3];
 #pragma unroll
         for (int b = 0; b < 3; ++b) dr[b] = sqrt(2.0 * kT * dt / gr[b]) * g1[b];
@@ -356,8 +357,8 @@ __device__ __forceinline__ bool phase_step(const DevParams &P, const DevArrays &
         double gv[4] = {0, 0, 0, 0}, gw[4] = {0, 0, 0, 0};
         double sv = 0.0;
         if (NOISE) {
-          sw_gaussians(P.seed, (u64)i, step, 2, gv);
-          sw_gaussians(P.seed, (u64)i, step, 3, gw);
+          swm_gaussians(P.seed, (u64)i, step, 2, gv);
+          swm_gaussians(P.seed, (u64)i, step, 3, gw);
           sv = sqrt(kT / P.sp_mass[sp]);
         }
         A.vx[i] = v[0] + sv * gv[0]; A.vy[i] = v[1] + sv * gv[1]; A.vz[i] = v[2] + sv * gv[2];
@@ -394,15 +395,15 @@ __global__ void __launch_bounds__(SW_THREADS) k_persist(const __grid_constant__ 
   Ctl *ctl = A.ctl;
   if (ldcg(&ctl->halted)) return;
   unsigned int epoch = 0;
-  const long long per_block = (A.n + gridDim.x - 1) / gridDim.x;
-  const long long lo = (long long)blockIdx.x * per_block;
-  const long long hi = (lo + per_block < A.n) ? lo + per_block : A.n;
+  // grid-stride ownership: thread t owns particles t, t + T, t + 2T, ... (balanced to one particle)
+  const long long lo = (long long)blockIdx.x * blockDim.x, hi = A.n;
+  const long long gstride = (long long)gridDim.x * blockDim.x;
   const bool leader = (blockIdx.x == 0 && threadIdx.x == 0);
 
   bool need = true;
   if (!R.force_rebuild) {
     bool moved = false;
-    for (long long i = lo + threadIdx.x; i < hi; i += blockDim.x) moved |= moved_since_build<DIM>(P, A, 0, i);
+    for (long long i = lo + threadIdx.x; i < hi; i += gstride) moved |= moved_since_build<DIM>(P, A, 0, i);
     if (moved) ctl->rebuild_flag[0] = 1;
     grid_barrier(&ctl->barrier, epoch);
     need = ldcg(&ctl->rebuild_flag[0]) != 0;
@@ -413,18 +414,18 @@ __global__ void __launch_bounds__(SW_THREADS) k_persist(const __grid_constant__ 
     const int cur = (int)(s & 1);
     if (s > 0) need = ldcg(&ctl->rebuild_flag[s % 3]) != 0;
     if (need) {
-      for (long long i = lo + threadIdx.x; i < hi; i += blockDim.x) phase_clear<DIM>(P, A, cur, i);
+      for (long long i = lo + threadIdx.x; i < hi; i += gstride) phase_clear<DIM>(P, A, cur, i);
       grid_barrier(&ctl->barrier, epoch);
-      for (long long i = lo + threadIdx.x; i < hi; i += blockDim.x) phase_insert(A, i);
+      for (long long i = lo + threadIdx.x; i < hi; i += gstride) phase_insert(A, i);
       grid_barrier(&ctl->barrier, epoch);
-      for (long long i = lo + threadIdx.x; i < hi; i += blockDim.x) phase_search<DIM>(P, A, cur, i);
+      for (long long i = lo + threadIdx.x; i < hi; i += gstride) phase_search<DIM>(P, A, cur, i);
       if (leader) ctl->rebuilds += 1;
       grid_barrier(&ctl->barrier, epoch);
       if (ldcg(&ctl->overflow)) break;  // uniform: every CTA reads the same value after the barrier
     }
     const bool last = (s == R.n_steps - 1);
     bool moved = false;
-    for (long long i = lo + threadIdx.x; i < hi; i += blockDim.x)
+    for (long long i = lo + threadIdx.x; i < hi; i += gstride)
       moved |= phase_step<DIM, NOISE>(P, A, R, cur, R.step0 + (u64)s, last, i);
     if (moved) ctl->rebuild_flag[(s + 1) % 3] = 1;
     if (leader) ctl->rebuild_flag[(s + 2) % 3] = 0;
@@ -432,10 +433,203 @@ __global__ void __launch_bounds__(SW_THREADS) k_persist(const __grid_constant__ 
   }
   // results live in buffer (s & 1); the caller's arrays are buffer 0
   if (s & 1) {
-    for (long long i = lo + threadIdx.x; i < hi; i += blockDim.x) {
+    for (long long i = lo + threadIdx.x; i < hi; i += gstride) {
       A.x[0][i] = ldcg(&A.x[1][i]); A.y[0][i] = ldcg(&A.y[1][i]);
       if (DIM == 3) A.z[0][i] = ldcg(&A.z[1][i]);
     }
+  }
+  if (leader) {
+    ctl->steps_done = s;
+    if (s < R.n_steps) ctl->halted = 1;
+    ctl->rebuild_flag[0] = 0; ctl->rebuild_flag[1] = 0; ctl->rebuild_flag[2] = 0;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Split grid barrier: arrive, do independent work, wait.  The Brownian step of particle i at step
+// s+1 needs its neighbours' positions after step s (a grid-wide dependency) but its NOISE depends on
+// (seed, i, s+1) only -- so the Philox + Box-Muller work of the next step, more than half of a
+// step's instructions, is issued between arrive and wait and hides the barrier's L2 round trips.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void grid_arrive(unsigned int *counter, unsigned int &epoch) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    epoch += gridDim.x;
+    __threadfence();
+    atomicAdd(counter, 1u);
+  }
+}
+__device__ __forceinline__ void grid_wait(unsigned int *counter, unsigned int epoch) {
+  if (threadIdx.x == 0) {
+    while (*((volatile unsigned int *)counter) < epoch) {
+    }
+    __threadfence();
+  }
+  __syncthreads();
+}
+
+#define SW_RES_NBR 4  // neighbour entries of the Verlet list kept in registers by the resident kernel
+
+// ---------------------------------------------------------------------------------------------
+// THE hot kernel of the 2-D rollout (BASELINE configs 2-4): cooperative persistent chunk of Brownian
+// steps with ONE PARTICLE PER THREAD, the particle's state (x, y, theta, rebuild reference, swim force,
+// torque, first Verlet entries) resident in registers for the whole chunk.  Per step a thread reads
+// only its neighbours' positions (L2, ld.cg) and writes its own new position for them; theta, v and
+// omega go to memory once, at the end of the chunk.  Requires grid * block >= n (all CTAs co-resident).
+// Arithmetic per particle is identical to phase_step<2, NOISE> (the oracle's orc_bd_steps).
+// ---------------------------------------------------------------------------------------------
+template <bool NOISE>
+__global__ void __launch_bounds__(SW_THREADS, 3) k_bd2d_resident(const __grid_constant__ DevParams P, DevArrays A, RunArgs R) {
+  Ctl *ctl = A.ctl;
+  if (ldcg(&ctl->halted)) return;
+  unsigned int epoch = 0;
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool act = i < A.n;
+  const bool leader = (i == 0);
+  double xi = 0.0, yi = 0.0, th = 0.0, xr = 0.0, yr = 0.0, fsw = 0.0, Tz = 0.0, fxe = 0.0, fye = 0.0;
+  int sp = 0, ti = 0;
+  if (act) {
+    xi = A.x[0][i]; yi = A.y[0][i]; th = A.theta[i];
+    xr = A.xr[i]; yr = A.yr[i];
+    fsw = A.f_swim[i]; Tz = A.tqz[i];
+    if (A.fex) { fxe = A.fex[i]; fye = A.fey[i]; }
+    sp = A.species[i]; ti = P.sp_type[sp];
+  }
+  const double lim2 = (0.5 * P.skin) * (0.5 * P.skin);
+  const double dt = P.dt, kT = P.kT;
+  const double gt1 = P.sp_gt[sp][1], gt2 = P.sp_gt[sp][2], gr0 = P.sp_gr[sp][0];
+  const bool iso = (gt1 == gt2);
+  const double sg_par = NOISE ? sqrt(2.0 * kT * dt / gt2) : 0.0;
+  const double sg_per = NOISE ? sqrt(2.0 * kT * dt / gt1) : 0.0;
+  const double sg_rot = NOISE ? sqrt(2.0 * kT * dt / gr0) : 0.0;
+
+  bool need = true;
+  if (!R.force_rebuild) {
+    if (act) {
+      double ddx = xi - xr, ddy = yi - yr;
+      if (!(ddx * ddx + ddy * ddy <= lim2)) ctl->rebuild_flag[0] = 1;
+    }
+    grid_barrier(&ctl->barrier, epoch);
+    need = ldcg(&ctl->rebuild_flag[0]) != 0;
+  }
+  double g0 = 0.0, g1 = 0.0, g3 = 0.0;
+  if (NOISE && act) swm_gaussians_xyt(P.seed, (u64)i, R.step0, g0, g1, g3);
+  int cnt = 0, nb[SW_RES_NBR];
+#pragma unroll
+  for (int k = 0; k < SW_RES_NBR; ++k) nb[k] = 0;
+  if (act && !need) {
+    cnt = A.nbr_cnt[i];
+#pragma unroll
+    for (int k = 0; k < SW_RES_NBR; ++k) if (k < cnt) nb[k] = A.nbr[(long long)k * A.n_pad + i];
+  }
+
+  long long s = 0;
+  for (; s < R.n_steps; ++s) {
+    const int cur = (int)(s & 1), nxt = cur ^ 1;
+    if (s > 0) need = ldcg(&ctl->rebuild_flag[s % 3]) != 0;
+    if (need) {
+      if (act) phase_clear<2>(P, A, cur, i);
+      grid_barrier(&ctl->barrier, epoch);
+      if (act) phase_insert(A, i);
+      grid_barrier(&ctl->barrier, epoch);
+      if (act) {
+        phase_search<2>(P, A, cur, i);
+        xr = xi; yr = yi;
+        cnt = A.nbr_cnt[i];
+#pragma unroll
+        for (int k = 0; k < SW_RES_NBR; ++k) if (k < cnt) nb[k] = A.nbr[(long long)k * A.n_pad + i];
+      }
+      if (leader) ctl->rebuilds += 1;
+      grid_barrier(&ctl->barrier, epoch);
+      if (ldcg(&ctl->overflow)) break;
+    }
+    const bool last = (s == R.n_steps - 1);
+    if (act) {
+      // ---- forces: WCA over the Verlet list (ascending j), walls, swim, external --------------
+      double Fx = 0.0, Fy = 0.0;
+#pragma unroll
+      for (int k = 0; k < SW_RES_NBR; ++k) {
+        if (k < cnt) {
+          const int en = nb[k];
+          const int j = en & SW_IDX_MASK, tj = en >> SW_TYPE_SHIFT;
+          double dx = sw_min_image(xi - ldcg(&A.x[cur][j]), P.box[0], P.inv_box[0], P.periodic[0]);
+          double dy = sw_min_image(yi - ldcg(&A.y[cur][j]), P.box[1], P.inv_box[1], P.periodic[1]);
+          double r2 = sw_r2(dx, dy, 0.0);
+          double cut = P.wca_cut[ti][tj];
+          if (r2 < __dmul_rn(cut, cut) && r2 > 0.0) {
+            double fac = sw_wca_factor(r2, P.wca_sigma[ti][tj], P.wca_eps[ti][tj]);
+            Fx += fac * dx; Fy += fac * dy;
+          }
+        }
+      }
+      for (int k = SW_RES_NBR; k < cnt; ++k) {
+        const int en = A.nbr[(long long)k * A.n_pad + i];
+        const int j = en & SW_IDX_MASK, tj = en >> SW_TYPE_SHIFT;
+        double dx = sw_min_image(xi - ldcg(&A.x[cur][j]), P.box[0], P.inv_box[0], P.periodic[0]);
+        double dy = sw_min_image(yi - ldcg(&A.y[cur][j]), P.box[1], P.inv_box[1], P.periodic[1]);
+        double r2 = sw_r2(dx, dy, 0.0);
+        double cut = P.wca_cut[ti][tj];
+        if (r2 < __dmul_rn(cut, cut) && r2 > 0.0) {
+          double fac = sw_wca_factor(r2, P.wca_sigma[ti][tj], P.wca_eps[ti][tj]);
+          Fx += fac * dx; Fy += fac * dy;
+        }
+      }
+      if (P.walls) {
+        const double cutw = P.wall_cut[ti];
+        if (xi < cutw && xi > 0.0) Fx += sw_wca_factor(xi * xi, P.wall_sigma[ti], P.wall_eps[ti]) * xi;
+        double d2 = P.box[0] - xi;
+        if (d2 < cutw && d2 > 0.0) Fx -= sw_wca_factor(d2 * d2, P.wall_sigma[ti], P.wall_eps[ti]) * d2;
+        if (yi < cutw && yi > 0.0) Fy += sw_wca_factor(yi * yi, P.wall_sigma[ti], P.wall_eps[ti]) * yi;
+        d2 = P.box[1] - yi;
+        if (d2 < cutw && d2 > 0.0) Fy -= sw_wca_factor(d2 * d2, P.wall_sigma[ti], P.wall_eps[ti]) * d2;
+      }
+      double ex, ey;
+      sincos(th, &ey, &ex);
+      Fx += fsw * ex; Fy += fsw * ey;
+      if (A.fex) { Fx += fxe; Fy += fye; }
+      // ---- Brownian update (phase_step<2>) ----------------------------------------------------
+      double vx, vy, xn, yn;
+      if (iso) {
+        vx = Fx / gt2; vy = Fy / gt2;
+        xn = xi + vx * dt; yn = yi + vy * dt;
+        if (NOISE) { xn += sg_par * g0; yn += sg_par * g1; }
+      } else {
+        double fpar = Fx * ex + Fy * ey, fper = -Fx * ey + Fy * ex;
+        double vpar = fpar / gt2, vper = fper / gt1;
+        vx = vpar * ex - vper * ey; vy = vpar * ey + vper * ex;
+        xn = xi + vx * dt; yn = yi + vy * dt;
+        if (NOISE) {
+          double spar = sg_par * g0, sper = sg_per * g1;
+          xn += spar * ex - sper * ey; yn += spar * ey + sper * ex;
+        }
+      }
+      const double w = Tz / gr0;
+      double thn = th + w * dt;
+      if (NOISE) thn += sg_rot * g3;
+      if (last) {
+        double gv[4] = {0, 0, 0, 0}, gw[4] = {0, 0, 0, 0};
+        double sv = 0.0, sw = 0.0;
+        if (NOISE) {
+          swm_gaussians(P.seed, (u64)i, R.step0 + (u64)s, 2, gv);
+          swm_gaussians(P.seed, (u64)i, R.step0 + (u64)s, 3, gw);
+          sv = sqrt(kT / P.sp_mass[sp]);
+          sw = sqrt(kT / P.sp_rin[sp][0]);
+        }
+        A.vx[i] = vx + sv * gv[0]; A.vy[i] = vy + sv * gv[1]; A.vz[i] = 0.0;
+        A.wx[i] = 0.0; A.wy[i] = 0.0; A.wz[i] = w + sw * gw[0];
+      }
+      xi = xn; yi = yn; th = thn;
+      A.x[nxt][i] = xn; A.y[nxt][i] = yn;
+      double ddx = xn - xr, ddy = yn - yr;
+      if ((ddx * ddx + ddy * ddy) > lim2) ctl->rebuild_flag[(s + 1) % 3] = 1;
+    }
+    if (leader) ctl->rebuild_flag[(s + 2) % 3] = 0;
+    grid_arrive(&ctl->barrier, epoch);
+    if (NOISE && act && !last) swm_gaussians_xyt(P.seed, (u64)i, R.step0 + (u64)(s + 1), g0, g1, g3);
+    grid_wait(&ctl->barrier, epoch);
+  }
+  if (act) {
+    A.x[0][i] = xi; A.y[0][i] = yi; A.theta[i] = th;
   }
   if (leader) {
     ctl->steps_done = s;
@@ -572,7 +766,7 @@ __global__ void k_gaussians(u64 seed, long long n, u64 step, u64 stream, double 
   long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   double g[4];
-  sw_gaussians(seed, (u64)i, step, stream, g);
+  swm_gaussians(seed, (u64)i, step, stream, g);
   out[4 * i + 0] = g[0]; out[4 * i + 1] = g[1]; out[4 * i + 2] = g[2]; out[4 * i + 3] = g[3];
 }
 
@@ -881,6 +1075,26 @@ static int sw_launch_persist(swarm *s, const RunArgs &R, cudaStream_t st) {
   return SWARM_OK;
 }
 
+// resident 2-D kernel: one particle per thread, every CTA co-resident
+template <bool NOISE>
+static int sw_launch_resident(swarm *s, const RunArgs &R, cudaStream_t st, bool *fits) {
+  auto kern = k_bd2d_resident<NOISE>;
+  int bpsm = 0;
+  SW_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bpsm, kern, SW_THREADS, 0));
+  const long long want = (s->A.n + SW_THREADS - 1) / SW_THREADS;
+  *fits = bpsm >= 1 && want <= (long long)s->num_sms * bpsm;
+  if (!*fits) return SWARM_OK;
+  s->coop_blocks_per_sm = bpsm;
+  SW_CUDA(cudaMemsetAsync(&s->A.ctl->barrier, 0, sizeof(unsigned int), st));
+  DevParams P = s->P;
+  DevArrays A = s->A;
+  RunArgs Rr = R;
+  void *args[] = {(void *)&P, (void *)&A, (void *)&Rr};
+  SW_CUDA(cudaLaunchCooperativeKernel((void *)kern, dim3((unsigned)want), dim3(SW_THREADS), args, 0, st));
+  s->launches += 1;
+  return SWARM_OK;
+}
+
 template <int DIM, bool NOISE>
 static int sw_launch_np(swarm *s, const RunArgs &R, cudaStream_t st) {
   const int T = SW_THREADS, B = sw_blocks(s->A.n > 0 ? s->A.n : 1, T);
@@ -921,7 +1135,13 @@ static int sw_run_common(swarm *s, RunArgs R, cudaStream_t st) {
     if (done > 0) Rc.force_rebuild = 0;
     // only the last sub-launch of a chunk materialises v / omega on its final step: handled by
     // Rc.n_steps bookkeeping -- earlier sub-launches also write them, harmlessly.
-    if (s->persistent) {
+    bool done_resident = false;
+    if (s->persistent && s->P.n_dims == 2 && R.mode == MODE_BD && !getenv("SWARM_B200_NO_RESIDENT")) {
+      rc = noise ? sw_launch_resident<true>(s, Rc, st, &done_resident) : sw_launch_resident<false>(s, Rc, st, &done_resident);
+      if (rc) return rc;
+    }
+    if (done_resident) {
+    } else if (s->persistent) {
       if (s->P.n_dims == 2) rc = noise ? sw_launch_persist<2, true>(s, Rc, st) : sw_launch_persist<2, false>(s, Rc, st);
       else rc = noise ? sw_launch_persist<3, true>(s, Rc, st) : sw_launch_persist<3, false>(s, Rc, st);
     } else {

@@ -40,7 +40,7 @@ for G in (74, 148, 296, 444):
     os.environ["SWARM_B200_GRID"] = str(G)
     from swarmrl_b200.device import DeviceSwarm
     pos, th = bench.initial_state(1000, 200.0, 1)
-    dd = DeviceSwarm(2, (200.0,) * 3, True, 1e-3, 0.0, 1, bench.species_table(), bench.wca_table(), skin=50.0)
+    dd = DeviceSwarm(2, (200.0,) * 3, True, 1e-3, 0.0, 1, bench.species_table(), bench.wca_table(), skin=5.0)
     dd.set_state(pos, np.zeros(1000, dtype=np.int32), theta=th)
     dd.run(1000, 0); torch.cuda.synchronize()
     a, b = ev(), ev(); a.record(); dd.run(4000, 1000); b.record(); torch.cuda.synchronize()
