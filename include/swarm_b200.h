@@ -138,6 +138,10 @@ int swarm_run(swarm_t *s, int64_t n_steps, uint64_t step0, void *stream);
 /* Synchronises `stream` and reports counters of the last run. */
 int swarm_sync_stats(swarm_t *s, void *stream, swarm_stats_t *out);
 
+/* Profiling hook: clock64 sums of the resident kernel's phases since the last call (all zero unless the
+ * library was built with -DSW_TIMING, `python -m swarmrl_b200.build --timing`); synchronises the device. */
+int swarm_debug_timing(swarm_t *s, int64_t out8[8]);
+
 /* Grow the Verlet capacity after an overflow (invalidates the current list). */
 int swarm_set_max_neighbors(swarm_t *s, int32_t max_neighbors);
 

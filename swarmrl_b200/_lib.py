@@ -11,7 +11,9 @@ import ctypes as C
 import pathlib
 
 PKG = pathlib.Path(__file__).resolve().parent
-LIB_PATH = PKG / "libswarm_b200.so"
+import os
+
+LIB_PATH = pathlib.Path(os.environ.get("SWARM_B200_LIB", PKG / "libswarm_b200.so"))
 
 MAX_SPECIES = 16
 MAX_TYPES = 8
@@ -79,6 +81,7 @@ SYMBOLS = {
     "swarm_run": (C.c_int, [_V, C.c_int64, C.c_uint64, _V]),
     "swarm_sync_stats": (C.c_int, [_V, _V, C.POINTER(Stats)]),
     "swarm_set_max_neighbors": (C.c_int, [_V, C.c_int32]),
+    "swarm_debug_timing": (C.c_int, [_V, C.POINTER(C.c_int64)]),
     "swarm_directors": (C.c_int, [_V, _V, _V, _V, _V]),
     "swarm_neighbors_dump": (C.c_int, [_V, _IP, C.c_int64, C.POINTER(C.c_int64)]),
     "swarm_cell_index": (C.c_int, [_V, C.POINTER(C.c_int32), _IP]),

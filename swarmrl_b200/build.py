@@ -16,7 +16,7 @@ PKG = pathlib.Path(__file__).resolve().parent
 CSRC = PKG / "csrc"
 LIB = PKG / "libswarm_b200.so"
 SOURCES = ["swarm_engine.cu", "swarm_obs.cu", "swarm_env.cu"]
-HEADERS = [CSRC / "swarm_common.cuh", PKG.parent / "include" / "swarm_b200.h"]
+HEADERS = [CSRC / "swarm_common.cuh", CSRC / "swarm_math.cuh", PKG.parent / "include" / "swarm_b200.h"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
@@ -41,7 +41,18 @@ def needs_build() -> bool:
     return any(d.stat().st_mtime > t for d in deps)
 
 
-def build(force: bool = False, verbose: bool = False) -> pathlib.Path:
+def build(force: bool = False, verbose: bool = False, timing: bool = False) -> pathlib.Path:
+    """timing=True builds libswarm_b200_timing.so with -DSW_TIMING (clock64 phase counters in the resident
+    kernel; select it with SWARM_B200_LIB=<path>) -- a profiling variant, never the default."""
+    if timing:
+        extra = [a for a in sys.argv if a.startswith("-D")]
+        tag = "".join(a[2:].lower() for a in extra)
+        out = PKG / f"libswarm_b200_timing{('_' + tag) if tag else ''}.so"
+        srcs = [str(CSRC / s) for s in SOURCES if (CSRC / s).exists()]
+        res = subprocess.run([_nvcc(), *NVCC_FLAGS, "-DSW_TIMING", *extra, "-o", str(out), *srcs], capture_output=True, text=True)
+        if res.returncode != 0:
+            raise RuntimeError("nvcc failed:\n" + res.stderr[-4000:])
+        return out
     if not force and not needs_build():
         return LIB
     srcs = [str(CSRC / s) for s in SOURCES if (CSRC / s).exists()]
@@ -56,5 +67,5 @@ def build(force: bool = False, verbose: bool = False) -> pathlib.Path:
 
 
 if __name__ == "__main__":
-    p = build(force="--force" in sys.argv, verbose=True)
+    p = build(force="--force" in sys.argv, verbose=True, timing="--timing" in sys.argv)
     print("built", p)

@@ -45,6 +45,11 @@ struct Ctl {
   int pad;
   long long steps_done;   // steps completed by the last launch sequence
   long long rebuilds;
+  long long tprof[8];         // SW_TIMING builds: clock64 sums of the resident kernel's phases (CTA 0, thread 0)
+  unsigned long long bar64;
+  unsigned long long pad1[15];   // keep the release word on its own 128-byte line
+  unsigned long long rel64;      // published by the last arriver: same encoding as bar64
+  unsigned long long pad2[15];  // resident kernel's barrier: low 32 bits arrivals, high 32 bits CTAs with a mover
 };
 
 struct DevArrays {

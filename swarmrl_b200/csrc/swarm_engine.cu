@@ -451,23 +451,44 @@ __global__ void __launch_bounds__(SW_THREADS) k_persist(const __grid_constant__ 
 // (seed, i, s+1) only -- so the Philox + Box-Muller work of the next step, more than half of a
 // step's instructions, is issued between arrive and wait and hides the barrier's L2 round trips.
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ void grid_arrive(unsigned int *counter, unsigned int &epoch) {
-  __syncthreads();
+// 64-bit counter: low word = arrivals, high word = number of CTA-steps that reported a particle beyond
+// skin/2 (the Verlet rebuild criterion travels with the barrier instead of costing another L2 round trip).
+// red.release / ld.acquire at gpu scope: no fence.sc (what __threadfence() is) on the critical path.
+// Centralised barrier with a separate release word: arrivals are atomics on `bar64`; the LAST arriver
+// publishes the final counter value to `rel64` (own 128-byte line) and everybody polls only that word,
+// so the polling traffic never queues in front of the arrivals at the L2 slice.
+__device__ __forceinline__ void grid_arrive64(unsigned long long *counter, unsigned int &epoch, bool cta_moved) {
   if (threadIdx.x == 0) {
     epoch += gridDim.x;
-    __threadfence();
-    atomicAdd(counter, 1u);
+    const unsigned long long inc = 1ULL | (cta_moved ? (1ULL << 32) : 0ULL);
+    unsigned long long old;
+    asm volatile("atom.acq_rel.gpu.global.add.u64 %0, [%1], %2;" : "=l"(old) : "l"(counter), "l"(inc) : "memory");
+    if ((unsigned int)old + 1u == epoch) {
+      const unsigned long long fin = old + inc;
+      asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(counter + 16), "l"(fin) : "memory");
+    }
   }
 }
-__device__ __forceinline__ void grid_wait(unsigned int *counter, unsigned int epoch) {
-  if (threadIdx.x == 0) {
-    while (*((volatile unsigned int *)counter) < epoch) {
-    }
-    __threadfence();
+__device__ __forceinline__ unsigned long long grid_poll64(unsigned long long *counter, unsigned int epoch) {
+  unsigned long long v;
+  for (;;) {
+    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(counter + 16) : "memory");
+    if ((unsigned int)v >= epoch) break;
+#ifdef SW_POLL_SLEEP
+    __nanosleep(SW_POLL_SLEEP);
+#endif
   }
+  return v;
+}
+// full barrier on the same counter (rebuild phases)
+__device__ __forceinline__ void grid_barrier64(unsigned long long *counter, unsigned int &epoch) {
+  __syncthreads();
+  grid_arrive64(counter, epoch, false);
+  if (threadIdx.x == 0) grid_poll64(counter, epoch);
   __syncthreads();
 }
 
+#define SW_RES_MAXT 768  // resident kernel: at most 768 threads per SM (<= 85 registers each)
 #define SW_RES_NBR 4  // neighbour entries of the Verlet list kept in registers by the resident kernel
 
 // ---------------------------------------------------------------------------------------------
@@ -479,7 +500,7 @@ __device__ __forceinline__ void grid_wait(unsigned int *counter, unsigned int ep
 // Arithmetic per particle is identical to phase_step<2, NOISE> (the oracle's orc_bd_steps).
 // ---------------------------------------------------------------------------------------------
 template <bool NOISE>
-__global__ void __launch_bounds__(SW_THREADS, 3) k_bd2d_resident(const __grid_constant__ DevParams P, DevArrays A, RunArgs R) {
+__global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_resident(const __grid_constant__ DevParams P, DevArrays A, RunArgs R) {
   Ctl *ctl = A.ctl;
   if (ldcg(&ctl->halted)) return;
   unsigned int epoch = 0;
@@ -499,61 +520,90 @@ __global__ void __launch_bounds__(SW_THREADS, 3) k_bd2d_resident(const __grid_co
   const double dt = P.dt, kT = P.kT;
   const double gt1 = P.sp_gt[sp][1], gt2 = P.sp_gt[sp][2], gr0 = P.sp_gr[sp][0];
   const bool iso = (gt1 == gt2);
+  // divisions by the friction coefficients: reciprocal once per launch + one residual correction per use
+  const double r_gt1 = swm_rcp(gt1), r_gt2 = swm_rcp(gt2), r_gr0 = swm_rcp(gr0);
   const double sg_par = NOISE ? sqrt(2.0 * kT * dt / gt2) : 0.0;
   const double sg_per = NOISE ? sqrt(2.0 * kT * dt / gt1) : 0.0;
   const double sg_rot = NOISE ? sqrt(2.0 * kT * dt / gr0) : 0.0;
 
+  __shared__ int s_need;
+  unsigned int movers_seen = 0;  // thread 0: high word of the barrier counter at the last poll
   bool need = true;
   if (!R.force_rebuild) {
+    bool moved = false;
     if (act) {
       double ddx = xi - xr, ddy = yi - yr;
-      if (!(ddx * ddx + ddy * ddy <= lim2)) ctl->rebuild_flag[0] = 1;
+      moved = !(ddx * ddx + ddy * ddy <= lim2);
     }
-    grid_barrier(&ctl->barrier, epoch);
-    need = ldcg(&ctl->rebuild_flag[0]) != 0;
+    const int any = __syncthreads_or(moved);
+    grid_arrive64(&ctl->bar64, epoch, any != 0);
+    if (threadIdx.x == 0) {
+      const unsigned int mv = (unsigned int)(grid_poll64(&ctl->bar64, epoch) >> 32);
+      s_need = (mv != movers_seen);
+      movers_seen = mv;
+    }
+    __syncthreads();
+    need = s_need != 0;
   }
   double g0 = 0.0, g1 = 0.0, g3 = 0.0;
   if (NOISE && act) swm_gaussians_xyt(P.seed, (u64)i, R.step0, g0, g1, g3);
   int cnt = 0, nb[SW_RES_NBR];
+  const int self_entry = act ? (int)i : 0;
 #pragma unroll
-  for (int k = 0; k < SW_RES_NBR; ++k) nb[k] = 0;
+  for (int k = 0; k < SW_RES_NBR; ++k) nb[k] = self_entry;
   if (act && !need) {
     cnt = A.nbr_cnt[i];
 #pragma unroll
-    for (int k = 0; k < SW_RES_NBR; ++k) if (k < cnt) nb[k] = A.nbr[(long long)k * A.n_pad + i];
+    for (int k = 0; k < SW_RES_NBR; ++k) nb[k] = (k < cnt) ? A.nbr[(long long)k * A.n_pad + i] : self_entry;
   }
 
+#ifdef SW_TIMING
+  long long tp[6] = {0, 0, 0, 0, 0, 0}, tc = clock64();
+#define SW_TICK(slot) do { if (leader) { long long t_ = clock64(); tp[slot] += t_ - tc; tc = t_; } } while (0)
+#else
+#define SW_TICK(slot) do { } while (0)
+#endif
   long long s = 0;
   for (; s < R.n_steps; ++s) {
     const int cur = (int)(s & 1), nxt = cur ^ 1;
-    if (s > 0) need = ldcg(&ctl->rebuild_flag[s % 3]) != 0;
     if (need) {
       if (act) phase_clear<2>(P, A, cur, i);
-      grid_barrier(&ctl->barrier, epoch);
+      grid_barrier64(&ctl->bar64, epoch);
       if (act) phase_insert(A, i);
-      grid_barrier(&ctl->barrier, epoch);
+      grid_barrier64(&ctl->bar64, epoch);
       if (act) {
         phase_search<2>(P, A, cur, i);
         xr = xi; yr = yi;
         cnt = A.nbr_cnt[i];
 #pragma unroll
-        for (int k = 0; k < SW_RES_NBR; ++k) if (k < cnt) nb[k] = A.nbr[(long long)k * A.n_pad + i];
+        for (int k = 0; k < SW_RES_NBR; ++k) nb[k] = (k < cnt) ? A.nbr[(long long)k * A.n_pad + i] : self_entry;
       }
       if (leader) ctl->rebuilds += 1;
-      grid_barrier(&ctl->barrier, epoch);
+      grid_barrier64(&ctl->bar64, epoch);
       if (ldcg(&ctl->overflow)) break;
     }
+    SW_TICK(0);
     const bool last = (s == R.n_steps - 1);
+    bool moved = false;
     if (act) {
       // ---- forces: WCA over the Verlet list (ascending j), walls, swim, external --------------
+      // the register-resident entries are loaded unconditionally (unused slots point at the particle
+      // itself) so the L2 round trips overlap each other and the sincos below
+      double xj[SW_RES_NBR], yj[SW_RES_NBR];
+#pragma unroll
+      for (int k = 0; k < SW_RES_NBR; ++k) {
+        const int j = nb[k] & SW_IDX_MASK;
+        xj[k] = ldcg(&A.x[cur][j]); yj[k] = ldcg(&A.y[cur][j]);
+      }
+      double ex, ey;
+      sincos(th, &ey, &ex);
       double Fx = 0.0, Fy = 0.0;
 #pragma unroll
       for (int k = 0; k < SW_RES_NBR; ++k) {
         if (k < cnt) {
-          const int en = nb[k];
-          const int j = en & SW_IDX_MASK, tj = en >> SW_TYPE_SHIFT;
-          double dx = sw_min_image(xi - ldcg(&A.x[cur][j]), P.box[0], P.inv_box[0], P.periodic[0]);
-          double dy = sw_min_image(yi - ldcg(&A.y[cur][j]), P.box[1], P.inv_box[1], P.periodic[1]);
+          const int tj = nb[k] >> SW_TYPE_SHIFT;
+          double dx = sw_min_image(xi - xj[k], P.box[0], P.inv_box[0], P.periodic[0]);
+          double dy = sw_min_image(yi - yj[k], P.box[1], P.inv_box[1], P.periodic[1]);
           double r2 = sw_r2(dx, dy, 0.0);
           double cut = P.wca_cut[ti][tj];
           if (r2 < __dmul_rn(cut, cut) && r2 > 0.0) {
@@ -583,19 +633,17 @@ __global__ void __launch_bounds__(SW_THREADS, 3) k_bd2d_resident(const __grid_co
         d2 = P.box[1] - yi;
         if (d2 < cutw && d2 > 0.0) Fy -= sw_wca_factor(d2 * d2, P.wall_sigma[ti], P.wall_eps[ti]) * d2;
       }
-      double ex, ey;
-      sincos(th, &ey, &ex);
       Fx += fsw * ex; Fy += fsw * ey;
       if (A.fex) { Fx += fxe; Fy += fye; }
       // ---- Brownian update (phase_step<2>) ----------------------------------------------------
       double vx, vy, xn, yn;
       if (iso) {
-        vx = Fx / gt2; vy = Fy / gt2;
+        vx = swm_div_r(Fx, gt2, r_gt2); vy = swm_div_r(Fy, gt2, r_gt2);
         xn = xi + vx * dt; yn = yi + vy * dt;
         if (NOISE) { xn += sg_par * g0; yn += sg_par * g1; }
       } else {
         double fpar = Fx * ex + Fy * ey, fper = -Fx * ey + Fy * ex;
-        double vpar = fpar / gt2, vper = fper / gt1;
+        double vpar = swm_div_r(fpar, gt2, r_gt2), vper = swm_div_r(fper, gt1, r_gt1);
         vx = vpar * ex - vper * ey; vy = vpar * ey + vper * ex;
         xn = xi + vx * dt; yn = yi + vy * dt;
         if (NOISE) {
@@ -603,7 +651,7 @@ __global__ void __launch_bounds__(SW_THREADS, 3) k_bd2d_resident(const __grid_co
           xn += spar * ex - sper * ey; yn += spar * ey + sper * ex;
         }
       }
-      const double w = Tz / gr0;
+      const double w = swm_div_r(Tz, gr0, r_gr0);
       double thn = th + w * dt;
       if (NOISE) thn += sg_rot * g3;
       if (last) {
@@ -621,13 +669,27 @@ __global__ void __launch_bounds__(SW_THREADS, 3) k_bd2d_resident(const __grid_co
       xi = xn; yi = yn; th = thn;
       A.x[nxt][i] = xn; A.y[nxt][i] = yn;
       double ddx = xn - xr, ddy = yn - yr;
-      if ((ddx * ddx + ddy * ddy) > lim2) ctl->rebuild_flag[(s + 1) % 3] = 1;
+      moved = (ddx * ddx + ddy * ddy) > lim2;
     }
-    if (leader) ctl->rebuild_flag[(s + 2) % 3] = 0;
-    grid_arrive(&ctl->barrier, epoch);
+    SW_TICK(1);
+    const int any = __syncthreads_or(moved);
+    SW_TICK(2);
+    grid_arrive64(&ctl->bar64, epoch, any != 0);
+    SW_TICK(3);
     if (NOISE && act && !last) swm_gaussians_xyt(P.seed, (u64)i, R.step0 + (u64)(s + 1), g0, g1, g3);
-    grid_wait(&ctl->barrier, epoch);
+    SW_TICK(4);
+    if (threadIdx.x == 0) {
+      const unsigned int mv = (unsigned int)(grid_poll64(&ctl->bar64, epoch) >> 32);
+      s_need = (mv != movers_seen);
+      movers_seen = mv;
+    }
+    __syncthreads();
+    need = s_need != 0;
+    SW_TICK(5);
   }
+#ifdef SW_TIMING
+  if (leader) for (int k = 0; k < 6; ++k) ctl->tprof[k] += tp[k];
+#endif
   if (act) {
     A.x[0][i] = xi; A.y[0][i] = yi; A.theta[i] = th;
   }
@@ -1079,18 +1141,26 @@ static int sw_launch_persist(swarm *s, const RunArgs &R, cudaStream_t st) {
 template <bool NOISE>
 static int sw_launch_resident(swarm *s, const RunArgs &R, cudaStream_t st, bool *fits) {
   auto kern = k_bd2d_resident<NOISE>;
+  // one CTA per SM (or fewer, larger ones): the grid barrier sees <= num_sms arrivals and the
+  // particles are spread over the SMs to within one warp
+  int threads = (int)(((s->A.n + (long long)s->num_sms * 32 - 1) / ((long long)s->num_sms * 32)) * 32);
+  if (threads < 128) threads = 128;
+  const char *envt = getenv("SWARM_B200_RES_THREADS");
+  if (envt) { int t = atoi(envt); if (t >= 32 && t <= SW_RES_MAXT && t % 32 == 0) threads = t; }
+  *fits = threads <= SW_RES_MAXT;
+  if (!*fits) return SWARM_OK;
   int bpsm = 0;
-  SW_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bpsm, kern, SW_THREADS, 0));
-  const long long want = (s->A.n + SW_THREADS - 1) / SW_THREADS;
+  SW_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bpsm, kern, threads, 0));
+  const long long want = (s->A.n + threads - 1) / threads;
   *fits = bpsm >= 1 && want <= (long long)s->num_sms * bpsm;
   if (!*fits) return SWARM_OK;
   s->coop_blocks_per_sm = bpsm;
-  SW_CUDA(cudaMemsetAsync(&s->A.ctl->barrier, 0, sizeof(unsigned int), st));
+  SW_CUDA(cudaMemsetAsync(&s->A.ctl->bar64, 0, sizeof(unsigned long long) * 32, st));
   DevParams P = s->P;
   DevArrays A = s->A;
   RunArgs Rr = R;
   void *args[] = {(void *)&P, (void *)&A, (void *)&Rr};
-  SW_CUDA(cudaLaunchCooperativeKernel((void *)kern, dim3((unsigned)want), dim3(SW_THREADS), args, 0, st));
+  SW_CUDA(cudaLaunchCooperativeKernel((void *)kern, dim3((unsigned)want), dim3(threads), args, 0, st));
   s->launches += 1;
   return SWARM_OK;
 }
@@ -1184,6 +1254,17 @@ extern "C" int swarm_sync_stats(swarm_t *s, void *stream, swarm_stats_t *out) {
   out->capacity = s->A.cap;
   out->persistent = s->persistent ? 1 : 0;
   if (s->ctl_host->overflow) s->list_valid = false;
+  return SWARM_OK;
+}
+
+extern "C" int swarm_debug_timing(swarm_t *s, int64_t out8[8]) {
+  if (!s || !out8) return SWARM_ERR_INVALID;
+  SW_CUDA(cudaSetDevice(s->cfg.device));
+  SW_CUDA(cudaDeviceSynchronize());
+  long long t[8];
+  SW_CUDA(cudaMemcpy(t, s->A.ctl->tprof, sizeof(t), cudaMemcpyDeviceToHost));
+  SW_CUDA(cudaMemset(s->A.ctl->tprof, 0, sizeof(t)));
+  for (int k = 0; k < 8; ++k) out8[k] = t[k];
   return SWARM_OK;
 }
 

@@ -9,36 +9,69 @@
 #pragma once
 #include "swarm_common.cuh"
 
-// 64 x 64 -> 128 bit product from four 32 x 32 -> 64 partial products (IMAD.WIDE.U32 with a 64-bit
-// addend); nvcc's separate mul.hi.u64 / mul.lo.u64 recompute the partial products.
-__device__ __forceinline__ void swm_mulhilo(u64 a, u64 b, u64 &hi, u64 &lo) {
-  const unsigned a0 = (unsigned)a, a1 = (unsigned)(a >> 32), b0 = (unsigned)b, b1 = (unsigned)(b >> 32);
-  const u64 t = (u64)a0 * b0;
-  const u64 u = (u64)a1 * b0 + (t >> 32);
-  const u64 v = (u64)a0 * b1 + (unsigned)u;
-  hi = (u64)a1 * b1 + (u >> 32) + (v >> 32);
-  lo = (v << 32) | (unsigned)t;
+// Polynomial coefficients live in constant memory: a DFMA takes a c[bank][offset] operand directly,
+// whereas a 64-bit immediate costs two extra moves per coefficient (measured: 140 UMOV per step).
+static __constant__ double SWM_LOG[11] = {0.6666666666666666, 0.4, 0.2857142857142857, 0.2222222222222222,
+                                          0.18181818181818182, 0.15384615384615385, 0.13333333333333333,
+                                          0.11764705882352941, 0.10526315789473684, 0.09523809523809523,
+                                          0.08695652173913043};
+static __constant__ double SWM_SIN[9] = {6.283185307179586, -41.34170224039976, 81.60524927607506, -76.70585975306139,
+                                         42.058693944897655, -15.09464257682299, 3.819952584848282,
+                                         -0.7181223017785006, 0.10422916220813984};
+static __constant__ double SWM_COS[10] = {1.0, -19.739208802178716, 64.9393940226683, -85.45681720669373,
+                                          60.24464137187666, -26.4262567833744, 7.903536371318469,
+                                          -1.714390711088672, 0.28200596845579123, -0.03638284114254567};
+static __constant__ double SWM_K[4] = {0.99999999999999988897769753748 /* 1 - 2^-53 */, 0.6931471805599453 /* ln2 hi */,
+                                       2.3190468138462996e-17 /* ln2 lo */, 0.5};
+
+// nvcc's mul.hi.u64 + mul.lo.u64 pair is the shortest SASS for the Philox multiply (measured against a
+// shared-partial-product IMAD.WIDE version and a PTX carry chain: 248 vs 336 vs 256 instructions).
+__device__ __forceinline__ void swm_philox4x64_10(u64 c0, u64 c1, u64 c2, u64 c3, u64 k0, u64 k1, u64 out[4]) {
+  sw_philox4x64_10(c0, c1, c2, c3, k0, k1, out);
 }
 
-__device__ __forceinline__ void swm_philox4x64_10(u64 c0, u64 c1, u64 c2, u64 c3, u64 k0, u64 k1, u64 out[4]) {
-  const u64 M0 = 0xD2E7470EE14C6C93ULL, M1 = 0xCA5A826395121157ULL;
-  const u64 W0 = 0x9E3779B97F4A7C15ULL, W1 = 0xBB67AE8584CAA73BULL;
-#pragma unroll
-  for (int r = 0; r < 10; ++r) {
-    u64 hi0, lo0, hi1, lo1;
-    swm_mulhilo(M0, c0, hi0, lo0);
-    swm_mulhilo(M1, c2, hi1, lo1);
-    const u64 n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
-    c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
-    k0 += W0; k1 += W1;
-  }
-  out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+// 1/d and sqrt(x) for normal positive arguments: MUFU seed + Newton steps, no special-case branches.
+__device__ __forceinline__ double swm_rcp(double d) {
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
+  double e = fma(-d, r, 1.0);   // seed: ~2^-20 relative
+  r = fma(r, e, r);
+  e = fma(-d, r, 1.0);
+  r = fma(r, e, r);
+  e = fma(-d, r, 1.0);
+  return fma(r, e, r);
+}
+// n / d, correctly rounded except in rare double-rounding cases (<= 1 ulp always)
+__device__ __forceinline__ double swm_div(double n, double d) {
+  const double r = swm_rcp(d);
+  double q = n * r;
+  const double rem = fma(-d, q, n);
+  return fma(rem, r, q);
+}
+// n * (1/d) with a residual correction, r = swm_rcp(d) precomputed
+__device__ __forceinline__ double swm_div_r(double n, double d, double r) {
+  double q = n * r;
+  const double rem = fma(-d, q, n);
+  return fma(rem, r, q);
+}
+__device__ __forceinline__ double swm_sqrt(double x) {
+  double r;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+  double g = x * r, h = 0.5 * r;
+  double e = fma(-h, g, 0.5);
+  g = fma(g, e, g); h = fma(h, e, h);
+  e = fma(-h, g, 0.5);
+  g = fma(g, e, g); h = fma(h, e, h);
+  e = fma(-h, g, 0.5);
+  g = fma(g, e, g); h = fma(h, e, h);
+  const double d = fma(-g, g, x);
+  return fma(d, h, g);
 }
 
 // u = ((r >> 12) + 1/2) 2^-52, bit-identical to sw_u01 / the oracle's u01, without an int->double convert
 __device__ __forceinline__ double swm_u01(u64 r) {
   const double d = __longlong_as_double((long long)((r >> 12) | 0x3FF0000000000000ULL));  // [1, 2)
-  return d - 0.99999999999999988897769753748;  // 1 - 2^-53 (exact); the difference is exact
+  return d - SWM_K[0];  // 1 - 2^-53 (exact); the difference is exact
 }
 
 // log(u), u in (0, 1) normal
@@ -50,23 +83,15 @@ __device__ __forceinline__ double swm_log01(double u) {
   if (hi >= 0x3FF6A09F) { hi -= 0x00100000; e += 1; }  // m >= ~sqrt(2): halve
   const double m = __hiloint2double(hi, lo);
   const double f = m - 1.0;
-  const double s = f / (2.0 + f);
+  const double s = swm_div(f, 2.0 + f);
   const double z = s * s;
-  double p = 0.08695652173913043;
-  p = fma(p, z, 0.09523809523809523);
-  p = fma(p, z, 0.10526315789473684);
-  p = fma(p, z, 0.11764705882352941);
-  p = fma(p, z, 0.13333333333333333);
-  p = fma(p, z, 0.15384615384615385);
-  p = fma(p, z, 0.18181818181818182);
-  p = fma(p, z, 0.2222222222222222);
-  p = fma(p, z, 0.2857142857142857);
-  p = fma(p, z, 0.4);
-  p = fma(p, z, 0.6666666666666666);
+  double p = SWM_LOG[10];
+#pragma unroll
+  for (int k = 9; k >= 0; --k) p = fma(p, z, SWM_LOG[k]);
   // log m = 2 s + s z p ;  log u = e ln2 + log m
   const double ed = (double)e;
-  const double r = fma(s * z, p, fma(ed, 2.3190468138462996e-17, 0.0));
-  return fma(ed, 0.6931471805599453, fma(2.0, s, r));
+  const double r = fma(s * z, p, ed * SWM_K[2]);
+  return fma(ed, SWM_K[1], fma(2.0, s, r));
 }
 
 // (sin, cos)(2 pi u) for the Philox word r, u = ((r >> 12) + 1/2) 2^-52
@@ -77,26 +102,13 @@ __device__ __forceinline__ void swm_sincos2pi(u64 r, double &sn, double &cs) {
   const double u = swm_u01(r);
   const double t = fma((double)q, -0.25, u);
   const double z = t * t;
-  double ps = 0.10422916220813984;
-  ps = fma(ps, z, -0.7181223017785006);
-  ps = fma(ps, z, 3.819952584848282);
-  ps = fma(ps, z, -15.09464257682299);
-  ps = fma(ps, z, 42.058693944897655);
-  ps = fma(ps, z, -76.70585975306139);
-  ps = fma(ps, z, 81.60524927607506);
-  ps = fma(ps, z, -41.34170224039976);
-  ps = fma(ps, z, 6.283185307179586);
+  double ps = SWM_SIN[8];
+#pragma unroll
+  for (int k = 7; k >= 0; --k) ps = fma(ps, z, SWM_SIN[k]);
   ps *= t;
-  double pc = -0.03638284114254567;
-  pc = fma(pc, z, 0.28200596845579123);
-  pc = fma(pc, z, -1.714390711088672);
-  pc = fma(pc, z, 7.903536371318469);
-  pc = fma(pc, z, -26.4262567833744);
-  pc = fma(pc, z, 60.24464137187666);
-  pc = fma(pc, z, -85.45681720669373);
-  pc = fma(pc, z, 64.9393940226683);
-  pc = fma(pc, z, -19.739208802178716);
-  pc = fma(pc, z, 1.0);
+  double pc = SWM_COS[9];
+#pragma unroll
+  for (int k = 8; k >= 0; --k) pc = fma(pc, z, SWM_COS[k]);
   // quadrant: angle = q pi/2 + 2 pi t
   const bool swap = q & 1u;
   double s0 = swap ? pc : ps, c0 = swap ? ps : pc;
@@ -110,8 +122,8 @@ __device__ __forceinline__ void swm_sincos2pi(u64 r, double &sn, double &cs) {
 __device__ __forceinline__ void swm_gaussians_xyt(u64 seed, u64 id, u64 step, double &g0, double &g1, double &g3) {
   u64 r[4];
   swm_philox4x64_10(step, 0ULL, 0ULL, 0ULL, id, seed, r);
-  const double m0 = sqrt(-2.0 * swm_log01(swm_u01(r[0])));
-  const double m1 = sqrt(-2.0 * swm_log01(swm_u01(r[2])));
+  const double m0 = swm_sqrt(-2.0 * swm_log01(swm_u01(r[0])));
+  const double m1 = swm_sqrt(-2.0 * swm_log01(swm_u01(r[2])));
   double s0, c0, s1, c1;
   swm_sincos2pi(r[1], s0, c0);
   swm_sincos2pi(r[3], s1, c1);
@@ -122,8 +134,8 @@ __device__ __forceinline__ void swm_gaussians_xyt(u64 seed, u64 id, u64 step, do
 __device__ __forceinline__ void swm_gaussians(u64 seed, u64 id, u64 step, u64 stream, double g[4]) {
   u64 r[4];
   swm_philox4x64_10(step, stream, 0ULL, 0ULL, id, seed, r);
-  const double m0 = sqrt(-2.0 * swm_log01(swm_u01(r[0])));
-  const double m1 = sqrt(-2.0 * swm_log01(swm_u01(r[2])));
+  const double m0 = swm_sqrt(-2.0 * swm_log01(swm_u01(r[0])));
+  const double m1 = swm_sqrt(-2.0 * swm_log01(swm_u01(r[2])));
   double s0, c0, s1, c1;
   swm_sincos2pi(r[1], s0, c0);
   swm_sincos2pi(r[3], s1, c1);
