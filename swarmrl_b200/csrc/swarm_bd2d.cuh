@@ -1,0 +1,247 @@
+// swarm_bd2d.cuh -- k_bd2d_resident, THE hot kernel of the 2-D rollout (BASELINE configs 2-4).
+// Included by swarm_engine.cu after the rebuild phases and the grid barrier.
+//
+// Cooperative persistent chunk of Brownian steps, ONE PARTICLE PER THREAD, one CTA per SM.  A particle's
+// state (x, y, theta, director, rebuild reference, swim force, torque, first Verlet entries) stays in
+// registers for the whole chunk; per step a thread reads only its neighbours' positions (L2, ld.cg) and
+// writes its own new position for them.  theta, v and omega go to memory once, at the end.
+//
+// Per step the only grid-wide dependency is "neighbours' positions after step s".  Everything else of
+// step s+1 -- the Philox + Box-Muller noise (seed, i, s+1), the director sincos(theta_{s+1}), the wall
+// and swim forces -- depends on the particle alone and is issued BETWEEN barrier arrive and barrier
+// wait, so that work (about 3/4 of a step's instructions) hides the barrier's L2 round trips.  Warp 0
+// of every CTA owns no particles: its lane 0 does the arrive / poll, so no particle warp sits behind it.
+//
+// Arithmetic per particle is identical to phase_step<2, NOISE> (the oracle's orc_bd_steps), except
+// that F / gamma is computed as a reciprocal multiply with one residual correction (<= 1 ulp).
+#pragma once
+
+#ifdef SW_TIMING
+#define SW_TICK(slot) do { if (prof) { long long t_ = clock64(); tp[slot] += t_ - tc; tc = t_; } } while (0)
+#else
+#define SW_TICK(slot) do { } while (0)
+#endif
+
+// pair force of one Verlet entry on particle (xi, yi) of type ti
+__device__ __forceinline__ void bd2d_pair(const DevParams &P, double xi, double yi, int ti, int tj, double xj, double yj,
+                                          double &Fx, double &Fy) {
+  double dx = sw_min_image(xi - xj, P.box[0], P.inv_box[0], P.periodic[0]);
+  double dy = sw_min_image(yi - yj, P.box[1], P.inv_box[1], P.periodic[1]);
+  double r2 = sw_r2(dx, dy, 0.0);
+  double cut = P.wca_cut[ti][tj];
+  if (r2 < __dmul_rn(cut, cut) && r2 > 0.0) {
+    double fac = sw_wca_factor(r2, P.wca_sigma[ti][tj], P.wca_eps[ti][tj]);
+    Fx += fac * dx; Fy += fac * dy;
+  }
+}
+
+// forces that depend on the particle alone: walls + swim + external (added AFTER the pair forces,
+// in the oracle's order: walls, swim, external)
+struct Bd2dSelf { double wx, wy, sx, sy; };
+__device__ __forceinline__ Bd2dSelf bd2d_self_forces(const DevParams &P, int ti, double xi, double yi, double ex, double ey,
+                                                    double fsw) {
+  Bd2dSelf o;
+  o.wx = 0.0; o.wy = 0.0;
+  if (P.walls) {
+    const double cutw = P.wall_cut[ti];
+    // two separate accumulations per axis, in the oracle's order (lower wall, upper wall)
+    if (xi < cutw && xi > 0.0) o.wx += sw_wca_factor(xi * xi, P.wall_sigma[ti], P.wall_eps[ti]) * xi;
+    double d2 = P.box[0] - xi;
+    if (d2 < cutw && d2 > 0.0) o.wx -= sw_wca_factor(d2 * d2, P.wall_sigma[ti], P.wall_eps[ti]) * d2;
+    if (yi < cutw && yi > 0.0) o.wy += sw_wca_factor(yi * yi, P.wall_sigma[ti], P.wall_eps[ti]) * yi;
+    d2 = P.box[1] - yi;
+    if (d2 < cutw && d2 > 0.0) o.wy -= sw_wca_factor(d2 * d2, P.wall_sigma[ti], P.wall_eps[ti]) * d2;
+  }
+  o.sx = fsw * ex; o.sy = fsw * ey;
+  return o;
+}
+
+template <bool NOISE>
+__global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_resident(const __grid_constant__ DevParams P, DevArrays A, RunArgs R) {
+  Ctl *ctl = A.ctl;
+  if (ldcg(&ctl->halted)) return;
+  unsigned int epoch = 0;
+  const int ptid = (int)threadIdx.x - 32;  // warp 0 is the barrier warp
+  const long long i = (long long)blockIdx.x * (blockDim.x - 32) + ptid;
+  const bool act = ptid >= 0 && i < A.n;
+  const bool leader = act && i == 0;
+  double xi = 0.0, yi = 0.0, th = 0.0, xr = 0.0, yr = 0.0, fsw = 0.0, Tz = 0.0, fxe = 0.0, fye = 0.0;
+  int sp = 0, ti = 0;
+  if (act) {
+    xi = A.x[0][i]; yi = A.y[0][i]; th = A.theta[i];
+    xr = A.xr[i]; yr = A.yr[i];
+    fsw = A.f_swim[i]; Tz = A.tqz[i];
+    if (A.fex) { fxe = A.fex[i]; fye = A.fey[i]; }
+    sp = A.species[i]; ti = P.sp_type[sp];
+  }
+  const double lim2 = (0.5 * P.skin) * (0.5 * P.skin);
+  const double dt = P.dt, kT = P.kT;
+  const double gt1 = P.sp_gt[sp][1], gt2 = P.sp_gt[sp][2], gr0 = P.sp_gr[sp][0];
+  const bool iso = (gt1 == gt2);
+  const double r_gt1 = swm_rcp(gt1), r_gt2 = swm_rcp(gt2), r_gr0 = swm_rcp(gr0);
+  const double sg_par = NOISE ? sqrt(2.0 * kT * dt / gt2) : 0.0;
+  const double sg_per = NOISE ? sqrt(2.0 * kT * dt / gt1) : 0.0;
+  const double sg_rot = NOISE ? sqrt(2.0 * kT * dt / gr0) : 0.0;
+  const double w = swm_div_r(Tz, gr0, r_gr0);  // omega_z: the torque is constant over the chunk
+
+  __shared__ int s_need;
+  unsigned int movers_seen = 0;  // thread 0: high word of the barrier counter at the last poll
+  bool need = true;
+  if (!R.force_rebuild) {
+    bool moved = false;
+    if (act) {
+      double ddx = xi - xr, ddy = yi - yr;
+      moved = !(ddx * ddx + ddy * ddy <= lim2);
+    }
+    const int any = __syncthreads_or(moved);
+    grid_arrive64(&ctl->bar64, epoch, any != 0);
+    if (threadIdx.x == 0) {
+      const unsigned int mv = (unsigned int)(grid_poll64(&ctl->bar64, epoch) >> 32);
+      s_need = (mv != movers_seen);
+      movers_seen = mv;
+    }
+    __syncthreads();
+    need = s_need != 0;
+  }
+  // particle-local inputs of the first step
+  double g0 = 0.0, g1 = 0.0, g3 = 0.0, ex = 1.0, ey = 0.0;
+  Bd2dSelf sf = {0.0, 0.0, 0.0, 0.0};
+  if (act) {
+    sincos(th, &ey, &ex);
+    sf = bd2d_self_forces(P, ti, xi, yi, ex, ey, fsw);
+    if (NOISE) swm_gaussians_xyt(P.seed, (u64)i, R.step0, g0, g1, g3);
+  }
+  int cnt = 0, nb[SW_RES_NBR];
+  const int self_entry = act ? (int)i : 0;
+#pragma unroll
+  for (int k = 0; k < SW_RES_NBR; ++k) nb[k] = self_entry;
+  if (act && !need) {
+    cnt = A.nbr_cnt[i];
+#pragma unroll
+    for (int k = 0; k < SW_RES_NBR; ++k) nb[k] = (k < cnt) ? A.nbr[(long long)k * A.n_pad + i] : self_entry;
+  }
+  double vx_l = 0.0, vy_l = 0.0;  // velocity of the most recent step (materialised after the loop)
+#ifdef SW_TIMING
+  long long tp[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tc = clock64();
+  const bool prof = (blockIdx.x == 0) && (threadIdx.x == 32 || threadIdx.x == 0);
+#endif
+
+  long long s = 0;
+  for (; s < R.n_steps; ++s) {
+    const int cur = (int)(s & 1), nxt = cur ^ 1;
+    if (need) {
+      if (act) phase_clear<2>(P, A, cur, i);
+      grid_barrier64(&ctl->bar64, epoch);
+      if (act) phase_insert(A, i);
+      grid_barrier64(&ctl->bar64, epoch);
+      if (act) {
+        phase_search<2>(P, A, cur, i);
+        xr = xi; yr = yi;
+        cnt = A.nbr_cnt[i];
+#pragma unroll
+        for (int k = 0; k < SW_RES_NBR; ++k) nb[k] = (k < cnt) ? A.nbr[(long long)k * A.n_pad + i] : self_entry;
+      }
+      if (leader) ctl->rebuilds += 1;
+      grid_barrier64(&ctl->bar64, epoch);
+      if (ldcg(&ctl->overflow)) break;  // uniform: every CTA reads the same value after the barrier
+    }
+    SW_TICK(0);
+    const bool last = (s == R.n_steps - 1);
+    bool moved = false;
+    if (act) {
+      // ---- the part that needs the neighbours: WCA over the Verlet list (ascending j) ------------
+      // register-resident entries are loaded unconditionally (unused slots point at the particle
+      // itself) so the L2 round trips overlap
+      double xj[SW_RES_NBR], yj[SW_RES_NBR];
+#pragma unroll
+      for (int k = 0; k < SW_RES_NBR; ++k) {
+        const int j = nb[k] & SW_IDX_MASK;
+        xj[k] = ldcg(&A.x[cur][j]); yj[k] = ldcg(&A.y[cur][j]);
+      }
+      double Fx = 0.0, Fy = 0.0;
+#pragma unroll
+      for (int k = 0; k < SW_RES_NBR; ++k)
+        if (k < cnt) bd2d_pair(P, xi, yi, ti, nb[k] >> SW_TYPE_SHIFT, xj[k], yj[k], Fx, Fy);
+      for (int k = SW_RES_NBR; k < cnt; ++k) {
+        const int en = A.nbr[(long long)k * A.n_pad + i];
+        const int j = en & SW_IDX_MASK;
+        bd2d_pair(P, xi, yi, ti, en >> SW_TYPE_SHIFT, ldcg(&A.x[cur][j]), ldcg(&A.y[cur][j]), Fx, Fy);
+      }
+      Fx += sf.wx; Fy += sf.wy;
+      Fx += sf.sx; Fy += sf.sy;
+      if (A.fex) { Fx += fxe; Fy += fye; }
+      // ---- Brownian update (phase_step<2>) ------------------------------------------------------
+      double xn, yn;
+      if (iso) {
+        vx_l = swm_div_r(Fx, gt2, r_gt2); vy_l = swm_div_r(Fy, gt2, r_gt2);
+        xn = xi + vx_l * dt; yn = yi + vy_l * dt;
+        if (NOISE) { xn += sg_par * g0; yn += sg_par * g1; }
+      } else {
+        double fpar = Fx * ex + Fy * ey, fper = -Fx * ey + Fy * ex;
+        double vpar = swm_div_r(fpar, gt2, r_gt2), vper = swm_div_r(fper, gt1, r_gt1);
+        vx_l = vpar * ex - vper * ey; vy_l = vpar * ey + vper * ex;
+        xn = xi + vx_l * dt; yn = yi + vy_l * dt;
+        if (NOISE) {
+          double spar = sg_par * g0, sper = sg_per * g1;
+          xn += spar * ex - sper * ey; yn += spar * ey + sper * ex;
+        }
+      }
+      double thn = th + w * dt;
+      if (NOISE) thn += sg_rot * g3;
+      xi = xn; yi = yn; th = thn;
+      A.x[nxt][i] = xn; A.y[nxt][i] = yn;
+      double ddx = xn - xr, ddy = yn - yr;
+      moved = (ddx * ddx + ddy * ddy) > lim2;
+    }
+    SW_TICK(1);
+    const int any = __syncthreads_or(moved);
+    SW_TICK(2);
+    if (threadIdx.x < 32) {
+      // ---- barrier warp: arrive, then poll; publishes the rebuild decision -----------------------
+      grid_arrive64(&ctl->bar64, epoch, any != 0);
+      SW_TICK(6);
+      if (threadIdx.x == 0) {
+        const unsigned int mv = (unsigned int)(grid_poll64(&ctl->bar64, epoch) >> 32);
+        s_need = (mv != movers_seen);
+        movers_seen = mv;
+      }
+      SW_TICK(7);
+    } else if (act && !last) {
+      // ---- particle-local work of step s+1, overlapping the barrier ------------------------------
+      sincos(th, &ey, &ex);
+      sf = bd2d_self_forces(P, ti, xi, yi, ex, ey, fsw);
+      if (NOISE) swm_gaussians_xyt(P.seed, (u64)i, R.step0 + (u64)(s + 1), g0, g1, g3);
+    }
+    SW_TICK(4);
+    __syncthreads();
+    need = s_need != 0;
+    SW_TICK(5);
+  }
+#ifdef SW_TIMING
+  if (prof) {
+    if (threadIdx.x == 0) { ctl->tprof[6] += tp[6]; ctl->tprof[7] += tp[7]; }
+    else for (int k = 0; k < 6; ++k) ctl->tprof[k] += tp[k];
+  }
+#endif
+  if (act) {
+    A.x[0][i] = xi; A.y[0][i] = yi; A.theta[i] = th;
+    if (s > 0) {
+      // v and omega of the last completed step (stochastic parts: streams 2 and 3)
+      double gv[4] = {0, 0, 0, 0}, gw[4] = {0, 0, 0, 0};
+      double sv = 0.0, sw = 0.0;
+      if (NOISE) {
+        swm_gaussians(P.seed, (u64)i, R.step0 + (u64)(s - 1), 2, gv);
+        swm_gaussians(P.seed, (u64)i, R.step0 + (u64)(s - 1), 3, gw);
+        sv = sqrt(kT / P.sp_mass[sp]);
+        sw = sqrt(kT / P.sp_rin[sp][0]);
+      }
+      A.vx[i] = vx_l + sv * gv[0]; A.vy[i] = vy_l + sv * gv[1]; A.vz[i] = 0.0;
+      A.wx[i] = 0.0; A.wy[i] = 0.0; A.wz[i] = w + sw * gw[0];
+    }
+  }
+  if (leader) {
+    ctl->steps_done = s;
+    if (s < R.n_steps) ctl->halted = 1;
+    ctl->rebuild_flag[0] = 0; ctl->rebuild_flag[1] = 0; ctl->rebuild_flag[2] = 0;
+  }
+}

@@ -491,214 +491,7 @@ __device__ __forceinline__ void grid_barrier64(unsigned long long *counter, unsi
 #define SW_RES_MAXT 768  // resident kernel: at most 768 threads per SM (<= 85 registers each)
 #define SW_RES_NBR 4  // neighbour entries of the Verlet list kept in registers by the resident kernel
 
-// ---------------------------------------------------------------------------------------------
-// THE hot kernel of the 2-D rollout (BASELINE configs 2-4): cooperative persistent chunk of Brownian
-// steps with ONE PARTICLE PER THREAD, the particle's state (x, y, theta, rebuild reference, swim force,
-// torque, first Verlet entries) resident in registers for the whole chunk.  Per step a thread reads
-// only its neighbours' positions (L2, ld.cg) and writes its own new position for them; theta, v and
-// omega go to memory once, at the end of the chunk.  Requires grid * block >= n (all CTAs co-resident).
-// Arithmetic per particle is identical to phase_step<2, NOISE> (the oracle's orc_bd_steps).
-// ---------------------------------------------------------------------------------------------
-template <bool NOISE>
-__global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_resident(const __grid_constant__ DevParams P, DevArrays A, RunArgs R) {
-  Ctl *ctl = A.ctl;
-  if (ldcg(&ctl->halted)) return;
-  unsigned int epoch = 0;
-  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  const bool act = i < A.n;
-  const bool leader = (i == 0);
-  double xi = 0.0, yi = 0.0, th = 0.0, xr = 0.0, yr = 0.0, fsw = 0.0, Tz = 0.0, fxe = 0.0, fye = 0.0;
-  int sp = 0, ti = 0;
-  if (act) {
-    xi = A.x[0][i]; yi = A.y[0][i]; th = A.theta[i];
-    xr = A.xr[i]; yr = A.yr[i];
-    fsw = A.f_swim[i]; Tz = A.tqz[i];
-    if (A.fex) { fxe = A.fex[i]; fye = A.fey[i]; }
-    sp = A.species[i]; ti = P.sp_type[sp];
-  }
-  const double lim2 = (0.5 * P.skin) * (0.5 * P.skin);
-  const double dt = P.dt, kT = P.kT;
-  const double gt1 = P.sp_gt[sp][1], gt2 = P.sp_gt[sp][2], gr0 = P.sp_gr[sp][0];
-  const bool iso = (gt1 == gt2);
-  // divisions by the friction coefficients: reciprocal once per launch + one residual correction per use
-  const double r_gt1 = swm_rcp(gt1), r_gt2 = swm_rcp(gt2), r_gr0 = swm_rcp(gr0);
-  const double sg_par = NOISE ? sqrt(2.0 * kT * dt / gt2) : 0.0;
-  const double sg_per = NOISE ? sqrt(2.0 * kT * dt / gt1) : 0.0;
-  const double sg_rot = NOISE ? sqrt(2.0 * kT * dt / gr0) : 0.0;
-
-  __shared__ int s_need;
-  unsigned int movers_seen = 0;  // thread 0: high word of the barrier counter at the last poll
-  bool need = true;
-  if (!R.force_rebuild) {
-    bool moved = false;
-    if (act) {
-      double ddx = xi - xr, ddy = yi - yr;
-      moved = !(ddx * ddx + ddy * ddy <= lim2);
-    }
-    const int any = __syncthreads_or(moved);
-    grid_arrive64(&ctl->bar64, epoch, any != 0);
-    if (threadIdx.x == 0) {
-      const unsigned int mv = (unsigned int)(grid_poll64(&ctl->bar64, epoch) >> 32);
-      s_need = (mv != movers_seen);
-      movers_seen = mv;
-    }
-    __syncthreads();
-    need = s_need != 0;
-  }
-  double g0 = 0.0, g1 = 0.0, g3 = 0.0;
-  if (NOISE && act) swm_gaussians_xyt(P.seed, (u64)i, R.step0, g0, g1, g3);
-  int cnt = 0, nb[SW_RES_NBR];
-  const int self_entry = act ? (int)i : 0;
-#pragma unroll
-  for (int k = 0; k < SW_RES_NBR; ++k) nb[k] = self_entry;
-  if (act && !need) {
-    cnt = A.nbr_cnt[i];
-#pragma unroll
-    for (int k = 0; k < SW_RES_NBR; ++k) nb[k] = (k < cnt) ? A.nbr[(long long)k * A.n_pad + i] : self_entry;
-  }
-
-#ifdef SW_TIMING
-  long long tp[6] = {0, 0, 0, 0, 0, 0}, tc = clock64();
-#define SW_TICK(slot) do { if (leader) { long long t_ = clock64(); tp[slot] += t_ - tc; tc = t_; } } while (0)
-#else
-#define SW_TICK(slot) do { } while (0)
-#endif
-  long long s = 0;
-  for (; s < R.n_steps; ++s) {
-    const int cur = (int)(s & 1), nxt = cur ^ 1;
-    if (need) {
-      if (act) phase_clear<2>(P, A, cur, i);
-      grid_barrier64(&ctl->bar64, epoch);
-      if (act) phase_insert(A, i);
-      grid_barrier64(&ctl->bar64, epoch);
-      if (act) {
-        phase_search<2>(P, A, cur, i);
-        xr = xi; yr = yi;
-        cnt = A.nbr_cnt[i];
-#pragma unroll
-        for (int k = 0; k < SW_RES_NBR; ++k) nb[k] = (k < cnt) ? A.nbr[(long long)k * A.n_pad + i] : self_entry;
-      }
-      if (leader) ctl->rebuilds += 1;
-      grid_barrier64(&ctl->bar64, epoch);
-      if (ldcg(&ctl->overflow)) break;
-    }
-    SW_TICK(0);
-    const bool last = (s == R.n_steps - 1);
-    bool moved = false;
-    if (act) {
-      // ---- forces: WCA over the Verlet list (ascending j), walls, swim, external --------------
-      // the register-resident entries are loaded unconditionally (unused slots point at the particle
-      // itself) so the L2 round trips overlap each other and the sincos below
-      double xj[SW_RES_NBR], yj[SW_RES_NBR];
-#pragma unroll
-      for (int k = 0; k < SW_RES_NBR; ++k) {
-        const int j = nb[k] & SW_IDX_MASK;
-        xj[k] = ldcg(&A.x[cur][j]); yj[k] = ldcg(&A.y[cur][j]);
-      }
-      double ex, ey;
-      sincos(th, &ey, &ex);
-      double Fx = 0.0, Fy = 0.0;
-#pragma unroll
-      for (int k = 0; k < SW_RES_NBR; ++k) {
-        if (k < cnt) {
-          const int tj = nb[k] >> SW_TYPE_SHIFT;
-          double dx = sw_min_image(xi - xj[k], P.box[0], P.inv_box[0], P.periodic[0]);
-          double dy = sw_min_image(yi - yj[k], P.box[1], P.inv_box[1], P.periodic[1]);
-          double r2 = sw_r2(dx, dy, 0.0);
-          double cut = P.wca_cut[ti][tj];
-          if (r2 < __dmul_rn(cut, cut) && r2 > 0.0) {
-            double fac = sw_wca_factor(r2, P.wca_sigma[ti][tj], P.wca_eps[ti][tj]);
-            Fx += fac * dx; Fy += fac * dy;
-          }
-        }
-      }
-      for (int k = SW_RES_NBR; k < cnt; ++k) {
-        const int en = A.nbr[(long long)k * A.n_pad + i];
-        const int j = en & SW_IDX_MASK, tj = en >> SW_TYPE_SHIFT;
-        double dx = sw_min_image(xi - ldcg(&A.x[cur][j]), P.box[0], P.inv_box[0], P.periodic[0]);
-        double dy = sw_min_image(yi - ldcg(&A.y[cur][j]), P.box[1], P.inv_box[1], P.periodic[1]);
-        double r2 = sw_r2(dx, dy, 0.0);
-        double cut = P.wca_cut[ti][tj];
-        if (r2 < __dmul_rn(cut, cut) && r2 > 0.0) {
-          double fac = sw_wca_factor(r2, P.wca_sigma[ti][tj], P.wca_eps[ti][tj]);
-          Fx += fac * dx; Fy += fac * dy;
-        }
-      }
-      if (P.walls) {
-        const double cutw = P.wall_cut[ti];
-        if (xi < cutw && xi > 0.0) Fx += sw_wca_factor(xi * xi, P.wall_sigma[ti], P.wall_eps[ti]) * xi;
-        double d2 = P.box[0] - xi;
-        if (d2 < cutw && d2 > 0.0) Fx -= sw_wca_factor(d2 * d2, P.wall_sigma[ti], P.wall_eps[ti]) * d2;
-        if (yi < cutw && yi > 0.0) Fy += sw_wca_factor(yi * yi, P.wall_sigma[ti], P.wall_eps[ti]) * yi;
-        d2 = P.box[1] - yi;
-        if (d2 < cutw && d2 > 0.0) Fy -= sw_wca_factor(d2 * d2, P.wall_sigma[ti], P.wall_eps[ti]) * d2;
-      }
-      Fx += fsw * ex; Fy += fsw * ey;
-      if (A.fex) { Fx += fxe; Fy += fye; }
-      // ---- Brownian update (phase_step<2>) ----------------------------------------------------
-      double vx, vy, xn, yn;
-      if (iso) {
-        vx = swm_div_r(Fx, gt2, r_gt2); vy = swm_div_r(Fy, gt2, r_gt2);
-        xn = xi + vx * dt; yn = yi + vy * dt;
-        if (NOISE) { xn += sg_par * g0; yn += sg_par * g1; }
-      } else {
-        double fpar = Fx * ex + Fy * ey, fper = -Fx * ey + Fy * ex;
-        double vpar = swm_div_r(fpar, gt2, r_gt2), vper = swm_div_r(fper, gt1, r_gt1);
-        vx = vpar * ex - vper * ey; vy = vpar * ey + vper * ex;
-        xn = xi + vx * dt; yn = yi + vy * dt;
-        if (NOISE) {
-          double spar = sg_par * g0, sper = sg_per * g1;
-          xn += spar * ex - sper * ey; yn += spar * ey + sper * ex;
-        }
-      }
-      const double w = swm_div_r(Tz, gr0, r_gr0);
-      double thn = th + w * dt;
-      if (NOISE) thn += sg_rot * g3;
-      if (last) {
-        double gv[4] = {0, 0, 0, 0}, gw[4] = {0, 0, 0, 0};
-        double sv = 0.0, sw = 0.0;
-        if (NOISE) {
-          swm_gaussians(P.seed, (u64)i, R.step0 + (u64)s, 2, gv);
-          swm_gaussians(P.seed, (u64)i, R.step0 + (u64)s, 3, gw);
-          sv = sqrt(kT / P.sp_mass[sp]);
-          sw = sqrt(kT / P.sp_rin[sp][0]);
-        }
-        A.vx[i] = vx + sv * gv[0]; A.vy[i] = vy + sv * gv[1]; A.vz[i] = 0.0;
-        A.wx[i] = 0.0; A.wy[i] = 0.0; A.wz[i] = w + sw * gw[0];
-      }
-      xi = xn; yi = yn; th = thn;
-      A.x[nxt][i] = xn; A.y[nxt][i] = yn;
-      double ddx = xn - xr, ddy = yn - yr;
-      moved = (ddx * ddx + ddy * ddy) > lim2;
-    }
-    SW_TICK(1);
-    const int any = __syncthreads_or(moved);
-    SW_TICK(2);
-    grid_arrive64(&ctl->bar64, epoch, any != 0);
-    SW_TICK(3);
-    if (NOISE && act && !last) swm_gaussians_xyt(P.seed, (u64)i, R.step0 + (u64)(s + 1), g0, g1, g3);
-    SW_TICK(4);
-    if (threadIdx.x == 0) {
-      const unsigned int mv = (unsigned int)(grid_poll64(&ctl->bar64, epoch) >> 32);
-      s_need = (mv != movers_seen);
-      movers_seen = mv;
-    }
-    __syncthreads();
-    need = s_need != 0;
-    SW_TICK(5);
-  }
-#ifdef SW_TIMING
-  if (leader) for (int k = 0; k < 6; ++k) ctl->tprof[k] += tp[k];
-#endif
-  if (act) {
-    A.x[0][i] = xi; A.y[0][i] = yi; A.theta[i] = th;
-  }
-  if (leader) {
-    ctl->steps_done = s;
-    if (s < R.n_steps) ctl->halted = 1;
-    ctl->rebuild_flag[0] = 0; ctl->rebuild_flag[1] = 0; ctl->rebuild_flag[2] = 0;
-  }
-}
+#include "swarm_bd2d.cuh"  // k_bd2d_resident: the hot kernel of the 2-D rollout
 
 // ---------------------------------------------------------------------------------------------
 // one-launch-per-phase variant (SWARM_FLAG_NO_PERSISTENT): same device functions, kernel
@@ -1143,15 +936,16 @@ static int sw_launch_resident(swarm *s, const RunArgs &R, cudaStream_t st, bool 
   auto kern = k_bd2d_resident<NOISE>;
   // one CTA per SM (or fewer, larger ones): the grid barrier sees <= num_sms arrivals and the
   // particles are spread over the SMs to within one warp
-  int threads = (int)(((s->A.n + (long long)s->num_sms * 32 - 1) / ((long long)s->num_sms * 32)) * 32);
-  if (threads < 128) threads = 128;
+  // + 32: warp 0 of every CTA is the barrier warp and owns no particles
+  int threads = 32 + (int)(((s->A.n + (long long)s->num_sms * 32 - 1) / ((long long)s->num_sms * 32)) * 32);
+  if (threads < 160) threads = 160;
   const char *envt = getenv("SWARM_B200_RES_THREADS");
-  if (envt) { int t = atoi(envt); if (t >= 32 && t <= SW_RES_MAXT && t % 32 == 0) threads = t; }
+  if (envt) { int t = atoi(envt); if (t >= 64 && t <= SW_RES_MAXT && t % 32 == 0) threads = t; }
   *fits = threads <= SW_RES_MAXT;
   if (!*fits) return SWARM_OK;
   int bpsm = 0;
   SW_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bpsm, kern, threads, 0));
-  const long long want = (s->A.n + threads - 1) / threads;
+  const long long want = (s->A.n + (threads - 32) - 1) / (threads - 32);
   *fits = bpsm >= 1 && want <= (long long)s->num_sms * bpsm;
   if (!*fits) return SWARM_OK;
   s->coop_blocks_per_sm = bpsm;

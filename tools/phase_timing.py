@@ -7,7 +7,7 @@ import bench
 from swarmrl_b200 import _lib
 from swarmrl_b200.device import DeviceSwarm
 
-NAMES = ["loop_head+rebuild", "force+update", "cta_sync_or", "arrive(red.release)", "noise(next step)", "poll+cta_sync"]
+NAMES = ["head+rebuild", "pairs+update", "cta_sync_or", "-", "local work s+1 (noise, sincos)", "wait final sync", "ctrl: arrive", "ctrl: poll"]
 
 def prof(d, steps, label):
     out = (C.c_int64 * 8)()
@@ -15,7 +15,7 @@ def prof(d, steps, label):
     a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True)
     a.record(); d.run(steps, steps); b.record(); torch.cuda.synchronize()
     _lib.check(d.lib.swarm_debug_timing(d.h, out))
-    cyc = np.array(list(out)[:6], dtype=float) / steps
+    cyc = np.array(list(out)[:8], dtype=float) / steps
     print(json.dumps({"case": label, "us_per_step": a.elapsed_time(b) / steps * 1e3, "cycles_per_step": dict(zip(NAMES, cyc.round(0).tolist())),
                       "sum_cycles": float(cyc.sum())}))
 
