@@ -45,6 +45,9 @@ SEED = 42
 ETA = 0.2200
 VISION = dict(range=10.0, half_angle=np.pi / 2, n_cones=5)
 BYTES_PER_AGENT_STEP = 68  # 2-D steady-state step, read 44 B + write 24 B
+# dram__bytes_read.sum + dram__bytes_write.sum of one k_bd2d_resident launch (100 steps), from the ncu --set full
+# capture profiles/r01_k_bd2d_resident.ncu-rep (10.70 MB + 0.12 MB): the state is register / L2 resident
+NCU_DRAM_BYTES_PER_LAUNCH = 10.82e6
 METRIC = "agent_steps_per_sec_100k_agents"
 UNIT = "agent-steps/s"
 
@@ -378,8 +381,8 @@ def run_ours(args):
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": ro.h2d, "d2h_bytes_per_step": ro.d2h,
                     "ms_per_step": e2e_ms / K},
             "gpu_launches": launches,
-            "roofline": {"bound": "hbm", "kernel": "k_persist<2,true> (one cooperative launch = 100 steps)",
-                         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+            "roofline": {"bound": "hbm", "kernel": "k_bd2d_resident<true> (one cooperative launch = 100 Brownian steps of 100k agents)",
+                         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": NCU_DRAM_BYTES_PER_LAUNCH,
                          "bytes_per_launch": N_AGENTS * STEPS_PER_SLICE * BYTES_PER_AGENT_STEP,
                          "launch_ms": run_avg_ms, "share_of_step": run_avg_ms * K / dev_ms,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback"},
@@ -398,7 +401,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--skin", type=float, default=0.4, help="Verlet skin (performance only; espresso.py:269 uses 0.4)")
+    ap.add_argument("--skin", type=float, default=2.0, help="Verlet skin (performance only; espresso.py:269 uses 0.4)")
     ap.add_argument("--cpu-steps", type=int, default=100, help="BD steps of the cpu_baseline sample")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()

@@ -62,8 +62,9 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_resident(const __grid_c
   if (ldcg(&ctl->halted)) return;
   unsigned int epoch = 0;
   const int ptid = (int)threadIdx.x - 32;  // warp 0 is the barrier warp
-  const long long i = (long long)blockIdx.x * (blockDim.x - 32) + ptid;
-  const bool act = ptid >= 0 && i < A.n;
+  const int ppc = R.particles_per_cta;     // particles are spread evenly over the CTAs (one CTA per SM)
+  const long long i = (long long)blockIdx.x * ppc + ptid;
+  const bool act = ptid >= 0 && ptid < ppc && i < A.n;
   const bool leader = act && i == 0;
   double xi = 0.0, yi = 0.0, th = 0.0, xr = 0.0, yr = 0.0, fsw = 0.0, Tz = 0.0, fxe = 0.0, fye = 0.0;
   int sp = 0, ti = 0;

@@ -38,6 +38,7 @@ struct RunArgs {
   int mode;
   int force_rebuild;
   double sd_gamma, sd_maxd;
+  int particles_per_cta;  // resident kernel only
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -936,16 +937,18 @@ static int sw_launch_resident(swarm *s, const RunArgs &R, cudaStream_t st, bool 
   auto kern = k_bd2d_resident<NOISE>;
   // one CTA per SM (or fewer, larger ones): the grid barrier sees <= num_sms arrivals and the
   // particles are spread over the SMs to within one warp
-  // + 32: warp 0 of every CTA is the barrier warp and owns no particles
-  int threads = 32 + (int)(((s->A.n + (long long)s->num_sms * 32 - 1) / ((long long)s->num_sms * 32)) * 32);
-  if (threads < 160) threads = 160;
+  // one CTA per SM, the particles spread evenly over them; + 32: warp 0 of every CTA is the barrier warp
+  long long ctas = s->num_sms;
+  if (s->A.n < ctas * 128) ctas = (s->A.n + 127) / 128;   // small swarms: at least 4 particle warps per CTA
+  int ppc = (int)((s->A.n + ctas - 1) / ctas);
+  int threads = 32 + ((ppc + 31) / 32) * 32;
   const char *envt = getenv("SWARM_B200_RES_THREADS");
-  if (envt) { int t = atoi(envt); if (t >= 64 && t <= SW_RES_MAXT && t % 32 == 0) threads = t; }
+  if (envt) { int t = atoi(envt); if (t >= 64 && t <= SW_RES_MAXT && t % 32 == 0) { threads = t; ppc = t - 32; } }
   *fits = threads <= SW_RES_MAXT;
   if (!*fits) return SWARM_OK;
   int bpsm = 0;
   SW_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bpsm, kern, threads, 0));
-  const long long want = (s->A.n + (threads - 32) - 1) / (threads - 32);
+  const long long want = (s->A.n + ppc - 1) / ppc;
   *fits = bpsm >= 1 && want <= (long long)s->num_sms * bpsm;
   if (!*fits) return SWARM_OK;
   s->coop_blocks_per_sm = bpsm;
@@ -953,6 +956,7 @@ static int sw_launch_resident(swarm *s, const RunArgs &R, cudaStream_t st, bool 
   DevParams P = s->P;
   DevArrays A = s->A;
   RunArgs Rr = R;
+  Rr.particles_per_cta = ppc;
   void *args[] = {(void *)&P, (void *)&A, (void *)&Rr};
   SW_CUDA(cudaLaunchCooperativeKernel((void *)kern, dim3((unsigned)want), dim3(threads), args, 0, st));
   s->launches += 1;
