@@ -47,6 +47,7 @@ typedef enum {
 } swarm_status_t;
 
 typedef struct swarm swarm_t;
+typedef enum { SWARM_DECAY_NONE = 0, SWARM_DECAY_LINEAR = 1, SWARM_DECAY_EXP = 2, SWARM_DECAY_INVERSE = 3 } swarm_decay_t;
 
 /* espresso.py:143-152 (n_dims, seed), :267-270 (box, time_step, skin, periodicity),
  * :1170-1186 (kT, thermostat seed). */
@@ -161,8 +162,59 @@ int swarm_forces(swarm_t *s, double *fx_dev, double *fy_dev, double *fz_dev, voi
 int swarm_philox_host(const uint64_t ctr[4], const uint64_t key[2], uint64_t out[4]);
 int swarm_gaussians(swarm_t *s, int64_t n, uint64_t step, uint64_t stream_id, double *out4n_dev, void *stream);
 
+/* Scratch capacity: later swarm_bind_state calls with n <= n_max keep the library's scratch (Verlet
+ * lists, cell links) instead of reallocating it -- the domain-decomposed swarm re-binds after every
+ * halo exchange.  Call before swarm_bind_state. */
+int swarm_reserve(swarm_t *s, int64_t n_max);
+
+/* Philox key id of every slot (int64 [n], device).  The reference's thermostat keys its noise by the
+ * particle id (espresso.py:1180-1186); slot index == id unless a sub-domain of a larger swarm is bound.
+ * Reset to NULL (slot index) by swarm_bind_state. */
+int swarm_bind_ids(swarm_t *s, const int64_t *gid_dev);
+
+/* ---- domain decomposition (no reference counterpart, ESPResSo runs single-rank) ---
+ * Slab decomposition along x of a 2-D periodic swarm.  Local frame of a rank: owned slab
+ * [halo, halo + slab_w), kept region [0, slab_w + 2 halo); the local swarm_t is created with
+ * box = (slab_w + 2 halo, L_y, .), periodic = (0, 1, 0).  Exchange buffers are SoA records of
+ * (x, y, theta, f_swim, tqz, gid, species, image, aux...) doubles behind an 8-byte record count. */
+#define SWARM_DD_MAX_AUX 4
+typedef struct {
+  double slab_w;
+  double halo;
+  int32_t n_aux;             /* user channels that travel with a particle (observable histories) */
+  int32_t cap;               /* record capacity of one exchange buffer */
+  int32_t image_shift_left;  /* added to the periodic image count of records sent left (-1 on rank 0) */
+  int32_t image_shift_right; /* ... sent right (+1 on the last rank) */
+} swarm_dd_geom_t;
+
+typedef struct {
+  double *x, *y, *theta, *f_swim, *tqz;
+  int64_t *gid;
+  int32_t *species, *image, *owned;
+  double *aux[SWARM_DD_MAX_AUX];
+} swarm_dd_arrays_t;
+
+/* doubles per exchange buffer for this geometry */
+int64_t swarm_dd_buffer_doubles(const swarm_dd_geom_t *g);
+/* owned particles within `halo` of a slab face (or beyond it: migrants) -> send buffers, x already in
+ * the receiver's frame */
+int swarm_dd_pack(swarm_t *s, const swarm_dd_geom_t *g, int64_t n, const swarm_dd_arrays_t *loc, double *send_left_dev,
+                  double *send_right_dev, void *stream);
+/* new local set = old owned + both received buffers, restricted to the kept region; owned recomputed.
+ * counts8_dev: [0] new n, [1] owned, [2] error bits (1 buffer overflow, 2 a particle outran the halo,
+ * 4 local capacity exceeded). */
+int swarm_dd_merge(swarm_t *s, const swarm_dd_geom_t *g, int64_t n_old, const swarm_dd_arrays_t *old_loc,
+                   const double *recv_left_dev, const double *recv_right_dev, int64_t cap_new,
+                   const swarm_dd_arrays_t *new_loc, int32_t *counts8_dev, void *stream);
+
+/* swarm_obs_field for the owned particles of a sub-domain, on global unfolded coordinates
+ * x_global = x_local + x_offset + image * box_x; history (p_prev) in aux channels 0, 1; out_dev[n],
+ * 0 for ghosts.  init_only = 1 just seeds the history. */
+int swarm_dd_obs_field(swarm_t *s, int64_t n, const swarm_dd_arrays_t *loc, double x_offset, double box_x,
+                       const double src[3], const double box_length[2], int32_t decay, double c0, double c1,
+                       double scale, int32_t clip_nonneg, int32_t init_only, double *out_dev, void *stream);
+
 /* ---- observables / tasks -------------------------------------------------------------- */
-typedef enum { SWARM_DECAY_NONE = 0, SWARM_DECAY_LINEAR = 1, SWARM_DECAY_EXP = 2, SWARM_DECAY_INVERSE = 3 } swarm_decay_t;
 
 /* ConcentrationField.compute_observable (observables/concentration_field.py:84-138) and
  * GradientSensing.__call__ (tasks/searching/gradient_sensing.py:92-150):

@@ -63,6 +63,18 @@ class Stats(C.Structure):
     ]
 
 
+DD_MAX_AUX = 4
+
+
+class DDGeom(C.Structure):
+    _fields_ = [("slab_w", C.c_double), ("halo", C.c_double), ("n_aux", C.c_int32), ("cap", C.c_int32),
+                ("image_shift_left", C.c_int32), ("image_shift_right", C.c_int32)]
+
+
+class DDArrays(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in "x y theta f_swim tqz gid species image owned".split()] + [("aux", C.c_void_p * DD_MAX_AUX)]
+
+
 # every symbol include/swarm_b200.h declares: (name, restype, argtypes)
 _V = C.c_void_p
 SYMBOLS = {
@@ -76,6 +88,14 @@ SYMBOLS = {
     "swarm_set_thermostat": (C.c_int, [_V, C.c_double, C.c_uint64]),
     "swarm_bind_state": (C.c_int, [_V, C.c_int64, C.POINTER(StateDev)]),
     "swarm_bind_actions": (C.c_int, [_V, C.POINTER(ActionsDev)]),
+    "swarm_reserve": (C.c_int, [_V, C.c_int64]),
+    "swarm_bind_ids": (C.c_int, [_V, _V]),
+    "swarm_dd_buffer_doubles": (C.c_int64, [C.POINTER(DDGeom)]),
+    "swarm_dd_pack": (C.c_int, [_V, C.POINTER(DDGeom), C.c_int64, C.POINTER(DDArrays), _V, _V, _V]),
+    "swarm_dd_merge": (C.c_int, [_V, C.POINTER(DDGeom), C.c_int64, C.POINTER(DDArrays), _V, _V, C.c_int64,
+                                 C.POINTER(DDArrays), _V, _V]),
+    "swarm_dd_obs_field": (C.c_int, [_V, C.c_int64, C.POINTER(DDArrays), C.c_double, C.c_double, _DP, _DP, C.c_int32,
+                                     C.c_double, C.c_double, C.c_double, C.c_int32, C.c_int32, _V, _V]),
     "swarm_apply_new_direction": (C.c_int, [_V, _V]),
     "swarm_relax": (C.c_int, [_V, C.c_int64, C.c_double, C.c_double, _V]),
     "swarm_run": (C.c_int, [_V, C.c_int64, C.c_uint64, _V]),

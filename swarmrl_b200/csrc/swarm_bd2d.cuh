@@ -68,7 +68,9 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_resident(const __grid_c
   const bool leader = act && i == 0;
   double xi = 0.0, yi = 0.0, th = 0.0, xr = 0.0, yr = 0.0, fsw = 0.0, Tz = 0.0, fxe = 0.0, fye = 0.0;
   int sp = 0, ti = 0;
+  u64 pid = 0;
   if (act) {
+    pid = sw_pid(A, i);
     xi = A.x[0][i]; yi = A.y[0][i]; th = A.theta[i];
     xr = A.xr[i]; yr = A.yr[i];
     fsw = A.f_swim[i]; Tz = A.tqz[i];
@@ -110,7 +112,7 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_resident(const __grid_c
   if (act) {
     sincos(th, &ey, &ex);
     sf = bd2d_self_forces(P, ti, xi, yi, ex, ey, fsw);
-    if (NOISE) swm_gaussians_xyt(P.seed, (u64)i, R.step0, g0, g1, g3);
+    if (NOISE) swm_gaussians_xyt(P.seed, pid, R.step0, g0, g1, g3);
   }
   int cnt = 0, nb[SW_RES_NBR];
   const int self_entry = act ? (int)i : 0;
@@ -211,7 +213,7 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_resident(const __grid_c
       // ---- particle-local work of step s+1, overlapping the barrier ------------------------------
       sincos(th, &ey, &ex);
       sf = bd2d_self_forces(P, ti, xi, yi, ex, ey, fsw);
-      if (NOISE) swm_gaussians_xyt(P.seed, (u64)i, R.step0 + (u64)(s + 1), g0, g1, g3);
+      if (NOISE) swm_gaussians_xyt(P.seed, pid, R.step0 + (u64)(s + 1), g0, g1, g3);
     }
     SW_TICK(4);
     __syncthreads();
@@ -231,8 +233,8 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_resident(const __grid_c
       double gv[4] = {0, 0, 0, 0}, gw[4] = {0, 0, 0, 0};
       double sv = 0.0, sw = 0.0;
       if (NOISE) {
-        swm_gaussians(P.seed, (u64)i, R.step0 + (u64)(s - 1), 2, gv);
-        swm_gaussians(P.seed, (u64)i, R.step0 + (u64)(s - 1), 3, gw);
+        swm_gaussians(P.seed, pid, R.step0 + (u64)(s - 1), 2, gv);
+        swm_gaussians(P.seed, pid, R.step0 + (u64)(s - 1), 3, gw);
         sv = sqrt(kT / P.sp_mass[sp]);
         sw = sqrt(kT / P.sp_rin[sp][0]);
       }

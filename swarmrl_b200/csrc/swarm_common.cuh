@@ -60,12 +60,16 @@ struct DevArrays {
   double *vx, *vy, *vz, *wx, *wy, *wz;
   double *f_swim, *tqx, *tqy, *tqz, *fex, *fey, *fez;
   const int *species;
+  const long long *gid;       // Philox id of every slot (domain decomposition); NULL => the slot index
   double *xr, *yr, *zr;        // positions at the last Verlet rebuild
   int *head, *next, *cellof;   // linked cells
   int *nbr, *nbr_cnt;          // Verlet list: nbr[k * n_pad + i], k < cap
   int cap;
   Ctl *ctl;
 };
+
+// Philox key id of slot i: the global particle id when the slots hold a sub-domain of a larger swarm
+__device__ __forceinline__ u64 sw_pid(const DevArrays &A, long long i) { return A.gid ? (u64)A.gid[i] : (u64)i; }
 
 // ---------------------------------------------------------------------------------------------
 // host handle
@@ -84,6 +88,8 @@ struct swarm {
   int coop_blocks_per_sm = 0;
   bool persistent = true;
   long long ncell_alloc = 0;
+  long long n_reserved = 0;   // scratch capacity in particles (swarm_reserve); bind_state reuses it
+  const long long *gid = nullptr;
   // scratch owned by the library
   std::vector<void *> owned;
   double *zeros = nullptr;  // n zeros (for unbound optional arrays)

@@ -1,0 +1,214 @@
+// swarm_dd.cu -- slab domain decomposition of ONE large periodic 2-D swarm over several GPUs
+// (BASELINE config 5).  The reference has no counterpart: SwarmRL drives a
+// single-rank ESPResSo (swarmrl/engine/espresso.py:193,1304-1306).
+//
+// Communication-avoiding scheme: rank g owns the slab x in [g W, (g+1) W) and
+// keeps, in a LOCAL frame where the slab is [H, H + W), every particle with 0 <= x_loc < W + 2H.  The
+// ghosts in the two halos are integrated REDUNDANTLY by the same Brownian kernel as the owned
+// particles -- their noise is keyed by the global particle id (swarm_bind_ids), so a ghost follows
+// bit-for-bit the random path its owner computes -- and the halos are re-shipped only every k steps,
+// with H >= k (r_cut + margin): an error entering at the outer halo edge travels at most r_cut + 2
+// max-displacements per step and never reaches the slab between two exchanges.
+//
+// One exchange = k_dd_pack (owned particles inside the two send bands -> fixed-capacity SoA record
+// buffers with the record count in their first 8 bytes), NCCL send/recv of the two buffers (host side,
+// torch.distributed), k_dd_merge (old owned + the two received buffers -> the other half of the
+// ping-pong state, owned flag recomputed).  Migration needs nothing extra: a particle that left the
+// slab lies in a send band, the receiver finds it inside its own slab and owns it from then on.
+#include "swarm_common.cuh"
+
+#define DD_FIXED 8  // x, y, theta, f_swim, tqz, gid, species, image
+
+struct DdArrays {
+  double *x, *y, *theta, *f_swim, *tqz;
+  long long *gid;
+  int *species, *image, *owned;
+  double *aux[SWARM_DD_MAX_AUX];
+};
+
+static DdArrays dd_arrays(const swarm_dd_arrays_t *a) {
+  DdArrays d;
+  d.x = a->x; d.y = a->y; d.theta = a->theta; d.f_swim = a->f_swim; d.tqz = a->tqz;
+  d.gid = (long long *)a->gid; d.species = a->species; d.image = a->image; d.owned = a->owned;
+  for (int c = 0; c < SWARM_DD_MAX_AUX; ++c) d.aux[c] = a->aux[c];
+  return d;
+}
+
+// warp-aggregated append: returns the slot of this lane (or -1 when !want)
+__device__ __forceinline__ long long dd_append(unsigned long long *counter, bool want) {
+  const unsigned m = __ballot_sync(0xFFFFFFFFu, want);
+  if (!m) return -1;
+  const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+  unsigned long long base = 0;
+  if (lane == leader) base = atomicAdd(counter, (unsigned long long)__popc(m));
+  base = __shfl_sync(0xFFFFFFFFu, base, leader);
+  return want ? (long long)(base + __popc(m & ((1u << lane) - 1u))) : -1;
+}
+
+__device__ __forceinline__ void dd_store(double *buf, long long cap, int n_aux, long long j, const DdArrays &L, long long i,
+                                         double x_new, int image_new) {
+  double *r = buf + 1;
+  r[0 * cap + j] = x_new;
+  r[1 * cap + j] = L.y[i];
+  r[2 * cap + j] = L.theta[i];
+  r[3 * cap + j] = L.f_swim[i];
+  r[4 * cap + j] = L.tqz[i];
+  r[5 * cap + j] = (double)L.gid[i];
+  r[6 * cap + j] = (double)L.species[i];
+  r[7 * cap + j] = (double)image_new;
+  for (int c = 0; c < n_aux; ++c) r[(DD_FIXED + c) * cap + j] = L.aux[c][i];
+}
+
+__global__ void k_dd_pack(swarm_dd_geom_t G, long long n, DdArrays L, double *send_left, double *send_right) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool act = i < n && L.owned[i] != 0;
+  const double x = act ? L.x[i] : 0.0;
+  const bool to_l = act && x < 2.0 * G.halo;   // within H of the left face, or already beyond it
+  const bool to_r = act && x >= G.slab_w;      // within H of the right face (H + W - H), or beyond
+  long long j = dd_append((unsigned long long *)send_left, to_l);
+  if (to_l && j < G.cap) dd_store(send_left, G.cap, G.n_aux, j, L, i, x + G.slab_w, L.image[i] + G.image_shift_left);
+  j = dd_append((unsigned long long *)send_right, to_r);
+  if (to_r && j < G.cap) dd_store(send_right, G.cap, G.n_aux, j, L, i, x - G.slab_w, L.image[i] + G.image_shift_right);
+}
+
+// t < n_old: old local slot t (kept when owned); then the records of recv_left, then of recv_right
+__global__ void k_dd_merge(swarm_dd_geom_t G, long long n_old, DdArrays O, const double *recv_left, const double *recv_right,
+                           long long cap_new, DdArrays N, int *counts) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const unsigned long long cl = *(const unsigned long long *)recv_left, cr = *(const unsigned long long *)recv_right;
+  if (t == 0 && (cl > (unsigned long long)G.cap || cr > (unsigned long long)G.cap)) atomicOr(&counts[2], 1);
+  const long long nl = cl > (unsigned long long)G.cap ? G.cap : (long long)cl;
+  const long long nr = cr > (unsigned long long)G.cap ? G.cap : (long long)cr;
+  const double *rec = nullptr;
+  long long j = -1;
+  bool cand = false;
+  double x = 0.0;
+  if (t < n_old) {
+    cand = O.owned[t] != 0;
+    if (cand) x = O.x[t];
+  } else if (t < n_old + nl) {
+    rec = recv_left + 1; j = t - n_old; cand = true; x = rec[j];
+  } else if (t < n_old + nl + nr) {
+    rec = recv_right + 1; j = t - n_old - nl; cand = true; x = rec[j];
+  }
+  const bool keep = cand && x >= 0.0 && x < G.slab_w + 2.0 * G.halo;
+  if (cand && !keep && !rec) atomicOr(&counts[2], 2);  // an owned particle outran the halo: k or H too small
+  const long long o = dd_append((unsigned long long *)(counts + 4), keep);
+  if (!keep) return;
+  if (o >= cap_new) { atomicOr(&counts[2], 4); return; }
+  const int own = (x >= G.halo && x < G.halo + G.slab_w) ? 1 : 0;
+  if (own) atomicAdd(&counts[1], 1);
+  N.x[o] = x;
+  N.owned[o] = own;
+  if (!rec) {
+    N.y[o] = O.y[t]; N.theta[o] = O.theta[t]; N.f_swim[o] = O.f_swim[t]; N.tqz[o] = O.tqz[t];
+    N.gid[o] = O.gid[t]; N.species[o] = O.species[t]; N.image[o] = O.image[t];
+    for (int c = 0; c < G.n_aux; ++c) N.aux[c][o] = O.aux[c][t];
+  } else {
+    const long long cap = G.cap;
+    N.y[o] = rec[1 * cap + j]; N.theta[o] = rec[2 * cap + j]; N.f_swim[o] = rec[3 * cap + j]; N.tqz[o] = rec[4 * cap + j];
+    N.gid[o] = (long long)rec[5 * cap + j]; N.species[o] = (int)rec[6 * cap + j]; N.image[o] = (int)rec[7 * cap + j];
+    for (int c = 0; c < G.n_aux; ++c) N.aux[c][o] = rec[(DD_FIXED + c) * cap + j];
+  }
+}
+
+__global__ void k_dd_finish(int *counts) {
+  const unsigned long long n = *(unsigned long long *)(counts + 4);
+  counts[0] = (int)n;
+}
+
+static int dd_check(const swarm_dd_geom_t *g) {
+  if (!g || g->n_aux < 0 || g->n_aux > SWARM_DD_MAX_AUX || g->cap < 1 || !(g->slab_w > 0.0) || !(g->halo >= 0.0)) {
+    sw_set_error("bad domain-decomposition geometry"); return SWARM_ERR_INVALID;
+  }
+  if (g->slab_w < 2.0 * g->halo) { sw_set_error("slab narrower than two halos: use fewer ranks or a smaller halo"); return SWARM_ERR_INVALID; }
+  return SWARM_OK;
+}
+
+extern "C" int64_t swarm_dd_buffer_doubles(const swarm_dd_geom_t *g) {
+  if (!g) return -1;
+  return 1 + (int64_t)(DD_FIXED + g->n_aux) * g->cap;
+}
+
+extern "C" int swarm_dd_pack(swarm_t *s, const swarm_dd_geom_t *g, int64_t n, const swarm_dd_arrays_t *loc, double *send_left_dev,
+                             double *send_right_dev, void *stream) {
+  if (!s || !loc || !send_left_dev || !send_right_dev || n < 0) { sw_set_error("bad arguments"); return SWARM_ERR_INVALID; }
+  int rc = dd_check(g);
+  if (rc) return rc;
+  SW_CUDA(cudaSetDevice(s->cfg.device));
+  cudaStream_t st = (cudaStream_t)stream;
+  SW_CUDA(cudaMemsetAsync(send_left_dev, 0, 8, st));
+  SW_CUDA(cudaMemsetAsync(send_right_dev, 0, 8, st));
+  if (n > 0) {
+    k_dd_pack<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(*g, n, dd_arrays(loc), send_left_dev, send_right_dev);
+    s->launches += 1;
+  }
+  SW_CUDA(cudaGetLastError());
+  return SWARM_OK;
+}
+
+extern "C" int swarm_dd_merge(swarm_t *s, const swarm_dd_geom_t *g, int64_t n_old, const swarm_dd_arrays_t *old_loc,
+                              const double *recv_left_dev, const double *recv_right_dev, int64_t cap_new,
+                              const swarm_dd_arrays_t *new_loc, int32_t *counts8_dev, void *stream) {
+  if (!s || !old_loc || !new_loc || !recv_left_dev || !recv_right_dev || !counts8_dev || n_old < 0 || cap_new < 1) {
+    sw_set_error("bad arguments"); return SWARM_ERR_INVALID;
+  }
+  int rc = dd_check(g);
+  if (rc) return rc;
+  SW_CUDA(cudaSetDevice(s->cfg.device));
+  cudaStream_t st = (cudaStream_t)stream;
+  SW_CUDA(cudaMemsetAsync(counts8_dev, 0, 8 * sizeof(int), st));
+  const long long total = n_old + 2LL * g->cap;
+  k_dd_merge<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(*g, n_old, dd_arrays(old_loc), recv_left_dev, recv_right_dev, cap_new,
+                                                             dd_arrays(new_loc), counts8_dev);
+  k_dd_finish<<<1, 1, 0, st>>>(counts8_dev);
+  s->launches += 2;
+  SW_CUDA(cudaGetLastError());
+  return SWARM_OK;
+}
+
+// ConcentrationField / GradientSensing of the owned particles on their GLOBAL unfolded coordinates
+// (observables/concentration_field.py:84-138, tasks/searching/gradient_sensing.py:92-150).  The history
+// p_prev = (x, y)/box_length travels with the particle in aux channels 0 and 1.  out[i] = 0 for ghosts.
+__device__ __forceinline__ double dd_decay(int kind, double c0, double c1, double d) {
+  switch (kind) {
+    case SWARM_DECAY_LINEAR: return c0 + c1 * d;
+    case SWARM_DECAY_EXP: return c0 * exp(-c1 * d);
+    case SWARM_DECAY_INVERSE: return c0 / (d + c1);
+    default: return d;
+  }
+}
+
+__global__ void k_dd_obs_field(long long n, DdArrays L, double x_off, double box_x, double s0, double s1, double s2, double b0,
+                               double b1, int decay, double c0, double c1, double scale, int clip, int init_only, double *out) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  if (!L.owned[i]) { out[i] = 0.0; return; }
+  const double xg = L.x[i] + x_off + (double)L.image[i] * box_x;
+  const double p0 = xg / b0, p1 = L.y[i] / b1;
+  const double h0 = L.aux[0][i], h1 = L.aux[1][i];
+  L.aux[0][i] = p0; L.aux[1][i] = p1;
+  if (init_only) { out[i] = 0.0; return; }
+  const double dn = sqrt((s0 - p0) * (s0 - p0) + (s1 - p1) * (s1 - p1) + s2 * s2);
+  const double dp = sqrt((s0 - h0) * (s0 - h0) + (s1 - h1) * (s1 - h1) + s2 * s2);
+  double v = scale * (dd_decay(decay, c0, c1, dn) - dd_decay(decay, c0, c1, dp));
+  if (clip && !(v > 0.0)) v = 0.0;
+  out[i] = v;
+}
+
+extern "C" int swarm_dd_obs_field(swarm_t *s, int64_t n, const swarm_dd_arrays_t *loc, double x_offset, double box_x,
+                                  const double src[3], const double box_length[2], int32_t decay, double c0, double c1,
+                                  double scale, int32_t clip_nonneg, int32_t init_only, double *out_dev, void *stream) {
+  if (!s || !loc || !src || !box_length || !out_dev || n < 0 || !loc->aux[0] || !loc->aux[1]) {
+    sw_set_error("bad arguments (the history needs aux channels 0 and 1)"); return SWARM_ERR_INVALID;
+  }
+  if (decay < SWARM_DECAY_NONE || decay > SWARM_DECAY_INVERSE) { sw_set_error("unknown decay kind"); return SWARM_ERR_INVALID; }
+  SW_CUDA(cudaSetDevice(s->cfg.device));
+  if (n == 0) return SWARM_OK;
+  k_dd_obs_field<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(n, dd_arrays(loc), x_offset, box_x, src[0], src[1],
+                                                                               src[2], box_length[0], box_length[1], decay, c0, c1,
+                                                                               scale, clip_nonneg, init_only, out_dev);
+  s->launches += 1;
+  SW_CUDA(cudaGetLastError());
+  return SWARM_OK;
+}

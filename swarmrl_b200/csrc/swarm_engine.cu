@@ -222,6 +222,7 @@ __device__ __forceinline__ bool phase_step(const DevParams &P, const DevArrays &
                                            bool last, long long i) {
   const int nxt = cur ^ 1;
   const int sp = A.species[i];
+  const u64 pid = sw_pid(A, i);
   const int ti = P.sp_type[sp];
   double xi = ldcg(&A.x[cur][i]), yi = ldcg(&A.y[cur][i]);
   double zi = (DIM == 3) ? ldcg(&A.z[cur][i]) : 0.0;
@@ -244,7 +245,7 @@ __device__ __forceinline__ bool phase_step(const DevParams &P, const DevArrays &
     } else {
       const double gt1 = P.sp_gt[sp][1], gt2 = P.sp_gt[sp][2], gr0 = P.sp_gr[sp][0];
       double g[4] = {0.0, 0.0, 0.0, 0.0};
-      if (NOISE) swm_gaussians(P.seed, (u64)i, step, 0, g);
+      if (NOISE) swm_gaussians(P.seed, pid, step, 0, g);
       double vx, vy;
       if (gt1 == gt2) {
         vx = F[0] / gt2; vy = F[1] / gt2;
@@ -271,8 +272,8 @@ __device__ __forceinline__ bool phase_step(const DevParams &P, const DevArrays &
         double gv[4] = {0, 0, 0, 0}, gw[4] = {0, 0, 0, 0};
         double sv = 0.0, sw = 0.0;
         if (NOISE) {
-          swm_gaussians(P.seed, (u64)i, step, 2, gv);
-          swm_gaussians(P.seed, (u64)i, step, 3, gw);
+          swm_gaussians(P.seed, pid, step, 2, gv);
+          swm_gaussians(P.seed, pid, step, 3, gw);
           sv = sqrt(kT / P.sp_mass[sp]);
           sw = sqrt(kT / P.sp_rin[sp][0]);
         }
@@ -302,7 +303,7 @@ __device__ __forceinline__ bool phase_step(const DevParams &P, const DevArrays &
     } else {
       const double *gt = P.sp_gt[sp], *gr = P.sp_gr[sp];
       double g[4] = {0.0, 0.0, 0.0, 0.0};
-      if (NOISE) swm_gaussians(P.seed, (u64)i, step, 0, g);
+      if (NOISE) swm_gaussians(P.seed, pid, step, 0, g);
       const bool aniso = (gt[0] != gt[1] || gt[1] != gt[2]);
       double v[3];
       if (!aniso) {
@@ -343,7 +344,7 @@ __device__ __forceinline__ bool phase_step(const DevParams &P, const DevArrays &
       }
       if (NOISE) {
         double g1[4];
-        swm_gaussians(P.seed, (u64)i, step, 1, g1);
+        swm_gaussians(P.seed, pid, step, 1, g1);
         double dr[3];
 #pragma unroll
         for (int b = 0; b < 3; ++b) dr[b] = sqrt(2.0 * kT * dt / gr[b]) * g1[b];
@@ -358,8 +359,8 @@ __device__ __forceinline__ bool phase_step(const DevParams &P, const DevArrays &
         double gv[4] = {0, 0, 0, 0}, gw[4] = {0, 0, 0, 0};
         double sv = 0.0;
         if (NOISE) {
-          swm_gaussians(P.seed, (u64)i, step, 2, gv);
-          swm_gaussians(P.seed, (u64)i, step, 3, gw);
+          swm_gaussians(P.seed, pid, step, 2, gv);
+          swm_gaussians(P.seed, pid, step, 3, gw);
           sv = sqrt(kT / P.sp_mass[sp]);
         }
         A.vx[i] = v[0] + sv * gv[0]; A.vy[i] = v[1] + sv * gv[1]; A.vz[i] = v[2] + sv * gv[2];
@@ -804,40 +805,53 @@ extern "C" int swarm_bind_state(swarm_t *s, int64_t n, const swarm_state_dev_t *
   if (s->P.n_dims == 2 && !st->theta) { sw_set_error("theta must be bound in 2-D"); return SWARM_ERR_INVALID; }
   if (s->P.n_dims == 3 && (!st->q0 || !st->q1 || !st->q2 || !st->q3)) { sw_set_error("q0..q3 must be bound in 3-D"); return SWARM_ERR_INVALID; }
   SW_CUDA(cudaSetDevice(s->cfg.device));
-  // (re)allocate library scratch
-  Ctl *ctl = s->A.ctl;
-  int cap = s->A.cap;
-  for (void *p : s->owned) if (p != (void *)ctl) cudaFree(p);
-  s->owned.clear();
-  s->owned.push_back(ctl);
+  // (re)allocate library scratch -- unless a previous bind / swarm_reserve already holds enough of it
+  long long need = n > s->n_reserved ? n : s->n_reserved;
+  long long need_pad = ((need + 31) / 32) * 32;
+  if (need_pad == 0) need_pad = 32;
   DevArrays &A = s->A;
-  memset(&A, 0, sizeof(A));
-  A.ctl = ctl; A.cap = cap;
+  const bool reuse = s->state_bound && A.x[1] && A.n_pad == need_pad;
+  if (!reuse) {
+    Ctl *ctl = s->A.ctl;
+    int cap = s->A.cap;
+    for (void *p : s->owned) if (p != (void *)ctl) cudaFree(p);
+    s->owned.clear();
+    s->owned.push_back(ctl);
+    memset(&A, 0, sizeof(A));
+    A.ctl = ctl; A.cap = cap;
+    A.n_pad = need_pad;
+  }
   A.n = n;
-  A.n_pad = ((n + 31) / 32) * 32;
-  if (A.n_pad == 0) A.n_pad = 32;
   s->st = *st;
   A.x[0] = st->x; A.y[0] = st->y; A.z[0] = st->z;
   A.theta = st->theta; A.q0 = st->q0; A.q1 = st->q1; A.q2 = st->q2; A.q3 = st->q3;
   A.vx = st->vx; A.vy = st->vy; A.vz = st->vz; A.wx = st->wx; A.wy = st->wy; A.wz = st->wz;
   A.species = st->species;
+  A.gid = nullptr;
   s->P.env_size = (int)(n / s->P.n_envs);
   if (s->P.env_size < 1) s->P.env_size = 1;
-  size_t nb = sizeof(double) * (size_t)A.n_pad;
-  int rc;
-  if ((rc = sw_alloc(s, (void **)&A.x[1], nb))) return rc;
-  if ((rc = sw_alloc(s, (void **)&A.y[1], nb))) return rc;
-  if ((rc = sw_alloc(s, (void **)&A.z[1], nb))) return rc;
-  if ((rc = sw_alloc(s, (void **)&A.xr, nb))) return rc;
-  if ((rc = sw_alloc(s, (void **)&A.yr, nb))) return rc;
-  if ((rc = sw_alloc(s, (void **)&A.zr, nb))) return rc;
-  if ((rc = sw_alloc(s, (void **)&s->zeros, nb))) return rc;
-  if ((rc = sw_alloc(s, (void **)&A.next, sizeof(int) * (size_t)A.n_pad, 0xFF))) return rc;
-  if ((rc = sw_alloc(s, (void **)&A.cellof, sizeof(int) * (size_t)A.n_pad))) return rc;
-  if ((rc = sw_alloc(s, (void **)&A.nbr_cnt, sizeof(int) * (size_t)A.n_pad))) return rc;
-  if ((rc = sw_alloc(s, (void **)&A.nbr, sizeof(int) * (size_t)A.n_pad * (size_t)A.cap))) return rc;
-  A.head = nullptr;
-  s->ncell_alloc = 0;
+  if (!reuse) {
+    size_t nb = sizeof(double) * (size_t)A.n_pad;
+    int rc;
+    if ((rc = sw_alloc(s, (void **)&A.x[1], nb))) return rc;
+    if ((rc = sw_alloc(s, (void **)&A.y[1], nb))) return rc;
+    if ((rc = sw_alloc(s, (void **)&A.z[1], nb))) return rc;
+    if ((rc = sw_alloc(s, (void **)&A.xr, nb))) return rc;
+    if ((rc = sw_alloc(s, (void **)&A.yr, nb))) return rc;
+    if ((rc = sw_alloc(s, (void **)&A.zr, nb))) return rc;
+    if ((rc = sw_alloc(s, (void **)&s->zeros, nb))) return rc;
+    if ((rc = sw_alloc(s, (void **)&A.next, sizeof(int) * (size_t)A.n_pad, 0xFF))) return rc;
+    if ((rc = sw_alloc(s, (void **)&A.cellof, sizeof(int) * (size_t)A.n_pad))) return rc;
+    if ((rc = sw_alloc(s, (void **)&A.nbr_cnt, sizeof(int) * (size_t)A.n_pad))) return rc;
+    if ((rc = sw_alloc(s, (void **)&A.nbr, sizeof(int) * (size_t)A.n_pad * (size_t)A.cap))) return rc;
+    A.head = nullptr;
+    s->ncell_alloc = 0;
+  } else {
+    // same scratch, different particles: the linked cells of the previous occupants are stale
+    SW_CUDA(cudaMemsetAsync(A.next, 0xFF, sizeof(int) * (size_t)A.n_pad, 0));
+    SW_CUDA(cudaMemsetAsync(A.cellof, 0, sizeof(int) * (size_t)A.n_pad, 0));
+    if (A.head) SW_CUDA(cudaMemsetAsync(A.head, 0xFF, sizeof(int) * (size_t)s->ncell_alloc, 0));
+  }
   // default actions: zeros
   A.f_swim = s->zeros; A.tqx = s->zeros; A.tqy = s->zeros; A.tqz = s->zeros;
   A.fex = nullptr; A.fey = nullptr; A.fez = nullptr;
@@ -857,6 +871,20 @@ extern "C" int swarm_bind_actions(swarm_t *s, const swarm_actions_dev_t *act) {
   A.f_swim = act->f_swim; A.tqx = act->tqx; A.tqy = act->tqy; A.tqz = act->tqz;
   A.fex = act->fex; A.fey = act->fey; A.fez = act->fez;
   s->actions_bound = true;
+  return SWARM_OK;
+}
+
+extern "C" int swarm_reserve(swarm_t *s, int64_t n_max) {
+  if (!s || n_max < 0) { sw_set_error("bad arguments"); return SWARM_ERR_INVALID; }
+  if (n_max >= (1LL << SW_TYPE_SHIFT)) { sw_set_error("n_max must be < 2^28 particles per handle"); return SWARM_ERR_INVALID; }
+  s->n_reserved = n_max;
+  return SWARM_OK;
+}
+
+extern "C" int swarm_bind_ids(swarm_t *s, const int64_t *gid_dev) {
+  if (!s) return SWARM_ERR_INVALID;
+  if (!s->state_bound) { sw_set_error("bind the state first"); return SWARM_ERR_STATE; }
+  s->A.gid = (const long long *)gid_dev;
   return SWARM_OK;
 }
 

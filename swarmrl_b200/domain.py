@@ -1,0 +1,317 @@
+"""
+One large periodic 2-D swarm, slab-decomposed along x over the GPUs of a node (BASELINE config 5,
+SURVEY.md 8(e).2).  The reference has no counterpart -- SwarmRL drives a single-rank ESPResSo
+(swarmrl/engine/espresso.py:193,1304-1306) -- so the contract is: same trajectories as the single-GPU
+engine (and the oracle) on the same inputs, to the tolerance north_star states (1e-9 relative per
+step, noise-free; identical noise because Philox is keyed by the global particle id).
+
+Scheme: every rank keeps its slab plus two halos of width H and integrates the
+ghosts redundantly with the same kernel; halos are re-shipped (and ownership migrates) only every
+`exchange_every` = k steps, H = k * r_cut * (1 + margin).  Per exchange: k_dd_pack -> two NCCL
+send/recv pairs over NVLink (torch.distributed) -> k_dd_merge -> re-bind.  No per-step collective.
+
+`slab_plan` and `select_local` are pure host logic (tested on CPU, gloo world_size 2);
+`DomainSwarm` needs the CUDA library and a device -- there is no CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+
+import numpy as np
+
+from . import _lib
+
+
+def slab_plan(box_x, world, rank, exchange_every, max_cut, margin=0.25):
+    """Geometry of rank `rank`'s slab.  Raises ValueError when the slabs are narrower than two halos."""
+    world, rank, k = int(world), int(rank), int(exchange_every)
+    if world < 1 or not (0 <= rank < world):
+        raise ValueError("rank must lie in [0, world)")
+    if k < 1:
+        raise ValueError("exchange_every must be >= 1")
+    if not (max_cut > 0.0 and box_x > 0.0 and margin >= 0.0):
+        raise ValueError("box_x, max_cut must be positive and margin non-negative")
+    w = float(box_x) / world
+    h = k * float(max_cut) * (1.0 + float(margin))
+    if w < 2.0 * h:
+        raise ValueError(f"slab width {w:g} < 2 halos of {h:g}: lower exchange_every or the number of ranks")
+    return {
+        "world": world, "rank": rank, "k": k, "box_x": float(box_x), "slab_w": w, "halo": h, "x0": rank * w,
+        "left": (rank - 1) % world, "right": (rank + 1) % world,
+        "image_shift_left": -1 if rank == 0 else 0,
+        "image_shift_right": 1 if rank == world - 1 else 0,
+        # local frame: x_global = x_local + x_offset + image * box_x
+        "x_offset": rank * w - h,
+    }
+
+
+def select_local(x_global, plan):
+    """Initial scatter: which particles (and which periodic image of each) rank `plan['rank']` keeps.
+
+    Returns (index, x_local, image, owned) -- index into the global arrays, x in the local frame where
+    the slab is [H, H + W), the periodic image count such that
+    x_global = x_local + x_offset + image * box_x, and the ownership flag.
+    """
+    x = np.asarray(x_global, dtype=np.float64)
+    L, w, h, x0 = plan["box_x"], plan["slab_w"], plan["halo"], plan["x0"]
+    img = np.floor(x / L)
+    xf = x - img * L
+    idx, xl, im = [], [], []
+    for m in (-1, 0, 1):
+        cand = xf - x0 + h + m * L
+        sel = np.nonzero((cand >= 0.0) & (cand < w + 2.0 * h))[0]
+        idx.append(sel)
+        xl.append(cand[sel])
+        im.append(img[sel] - m)
+    idx = np.concatenate(idx)
+    xl = np.concatenate(xl)
+    im = np.concatenate(im).astype(np.int32)
+    order = np.argsort(idx, kind="stable")
+    idx, xl, im = idx[order], xl[order], im[order]
+    owned = ((xl >= h) & (xl < h + w)).astype(np.int32)
+    return idx.astype(np.int64), xl, im, owned
+
+
+def unfold_global(x_local, image, plan):
+    """x_global of local-frame coordinates (inverse of select_local)."""
+    return np.asarray(x_local) + plan["x_offset"] + np.asarray(image, dtype=np.float64) * plan["box_x"]
+
+
+class _Transport:
+    """Moves the two exchange buffers to the slab neighbours: NCCL device-to-device over NVLink when the
+    process group is nccl, host-staged for gloo (single-GPU tests), a local swap when world == 1."""
+
+    def __init__(self, plan, group=None):
+        self.plan = plan
+        self.group = group
+        self.world = plan["world"]
+        if self.world > 1:
+            import torch.distributed as dist
+
+            self.dist = dist
+            self.backend = dist.get_backend(group)
+
+    def exchange(self, send_l, send_r, recv_l, recv_r):
+        if self.world == 1:
+            recv_r.copy_(send_l)   # what goes out through my left face enters through my right face
+            recv_l.copy_(send_r)
+            return
+        dist, p = self.dist, self.plan
+        if self.backend == "nccl":
+            # posting order matters when left == right (world 2): the peer's first send is its send_l,
+            # which reaches me through my RIGHT face
+            ops = [dist.P2POp(dist.isend, send_l, p["left"], self.group), dist.P2POp(dist.isend, send_r, p["right"], self.group),
+                   dist.P2POp(dist.irecv, recv_r, p["right"], self.group), dist.P2POp(dist.irecv, recv_l, p["left"], self.group)]
+            for r in dist.batch_isend_irecv(ops):
+                r.wait()
+            return
+        sl, sr = send_l.cpu(), send_r.cpu()
+        rl, rr = sl.new_empty(sl.shape), sr.new_empty(sr.shape)
+        reqs = [dist.isend(sl, p["left"], group=self.group, tag=1), dist.isend(sr, p["right"], group=self.group, tag=2),
+                dist.irecv(rr, p["right"], group=self.group, tag=1), dist.irecv(rl, p["left"], group=self.group, tag=2)]
+        for r in reqs:
+            r.wait()
+        recv_l.copy_(rl)
+        recv_r.copy_(rr)
+
+    def all_reduce_sum(self, t):
+        if self.world > 1:
+            if self.backend == "nccl":
+                self.dist.all_reduce(t, group=self.group)
+            else:
+                c = t.cpu()
+                self.dist.all_reduce(c, group=self.group)
+                t.copy_(c)
+        return t
+
+
+_F64 = ("x", "y", "theta", "f_swim", "tqz")
+
+
+class DomainSwarm:
+    """This rank's slab (+ halos) of a periodic 2-D swarm; see the module docstring."""
+
+    def __init__(self, box, dt, kT, seed, species, wca, *, exchange_every=8, margin=0.25, skin=0.4, world=1, rank=0,
+                 group=None, device=None, n_aux=2, max_neighbors=0, capacity_factor=1.3, persistent=True):
+        from .device import DeviceSwarm
+
+        self.max_cut = float(np.max(np.asarray(wca["cut"], dtype=np.float64)))
+        self.plan = slab_plan(box[0], world, rank, exchange_every, self.max_cut, margin)
+        if not (0 <= n_aux <= _lib.DD_MAX_AUX):
+            raise ValueError("n_aux must lie in [0, 4]")
+        p = self.plan
+        self.box = (float(box[0]), float(box[1]))
+        self.n_aux = int(n_aux)
+        self.capacity_factor = float(capacity_factor)
+        local_box = (p["slab_w"] + 2.0 * p["halo"], self.box[1], self.box[1])
+        self.sw = DeviceSwarm(2, local_box, (False, True, False), dt, kT, seed, species, wca, skin=skin,
+                              max_neighbors=max_neighbors, persistent=persistent, device=device)
+        self.torch, self.dev, self.lib, self.h = self.sw.torch, self.sw.dev, self.sw.lib, self.sw.h
+        self.transport = _Transport(p, group)
+        self.n = 0
+        self.n_owned = 0
+        self.since_exchange = 0
+        self.exchanges = 0
+        self.cur = 0
+
+    # ---------------------------------------------------------------- storage
+    def _alloc(self, cap, buf_cap):
+        torch = self.torch
+        f64 = dict(dtype=torch.float64, device=self.dev)
+        self.cap = int(cap)
+        self.sets = []
+        for _ in range(2):   # ping-pong halves: merge reads one, writes the other
+            s = {k: torch.zeros(self.cap, **f64) for k in _F64}
+            s["gid"] = torch.zeros(self.cap, dtype=torch.int64, device=self.dev)
+            for k in ("species", "image", "owned"):
+                s[k] = torch.zeros(self.cap, dtype=torch.int32, device=self.dev)
+            s["aux"] = [torch.zeros(self.cap, **f64) for _ in range(self.n_aux)]
+            self.sets.append(s)
+        self.zeros = torch.zeros(self.cap, **f64)
+        self.vel = torch.zeros((3, self.cap), **f64)
+        self.omega = torch.zeros((3, self.cap), **f64)
+        self.geom = _lib.DDGeom(self.plan["slab_w"], self.plan["halo"], self.n_aux, int(buf_cap),
+                                self.plan["image_shift_left"], self.plan["image_shift_right"])
+        nd = int(self.lib.swarm_dd_buffer_doubles(C.byref(self.geom)))
+        self.bufs = {k: torch.zeros(nd, **f64) for k in ("send_l", "send_r", "recv_l", "recv_r")}
+        self.counts = torch.zeros(8, dtype=torch.int32, device=self.dev)
+        self.counts_host = torch.zeros(8, dtype=torch.int32).pin_memory()
+        self.out = torch.zeros(self.cap, **f64)
+        _lib.check(self.lib.swarm_reserve(self.h, self.cap))
+
+    def _dd(self, s):
+        a = _lib.DDArrays()
+        for k in _F64 + ("gid", "species", "image", "owned"):
+            setattr(a, k, s[k].data_ptr())
+        for c in range(self.n_aux):
+            a.aux[c] = s["aux"][c].data_ptr()
+        return a
+
+    def _bind(self):
+        s = self.sets[self.cur]
+        st = _lib.StateDev()
+        st.x, st.y, st.z, st.theta = s["x"].data_ptr(), s["y"].data_ptr(), self.zeros.data_ptr(), s["theta"].data_ptr()
+        st.vx, st.vy, st.vz = (self.vel[a].data_ptr() for a in range(3))
+        st.wx, st.wy, st.wz = (self.omega[a].data_ptr() for a in range(3))
+        st.species = s["species"].data_ptr()
+        _lib.check(self.lib.swarm_bind_state(self.h, self.n, C.byref(st)))
+        act = _lib.ActionsDev()
+        act.f_swim, act.tqx, act.tqy, act.tqz = s["f_swim"].data_ptr(), self.zeros.data_ptr(), self.zeros.data_ptr(), s["tqz"].data_ptr()
+        _lib.check(self.lib.swarm_bind_actions(self.h, C.byref(act)))
+        _lib.check(self.lib.swarm_bind_ids(self.h, s["gid"].data_ptr()))
+        self.sw.n = self.n
+
+    @property
+    def local(self):
+        return self.sets[self.cur]
+
+    # ------------------------------------------------------------------ setup
+    def scatter(self, pos_global, theta_global, species_global=None, capacity=None, buffer_capacity=None):
+        """Every rank passes the same global arrays (host, particle index == global id) and keeps its part."""
+        torch = self.torch
+        pos = np.asarray(pos_global, dtype=np.float64)
+        n_glob = pos.shape[0]
+        idx, xl, im, owned = select_local(pos[:, 0], self.plan)
+        p = self.plan
+        frac = (p["slab_w"] + 2.0 * p["halo"]) / p["box_x"]
+        cap = capacity or int(max(len(idx), frac * n_glob) * self.capacity_factor) + 1024
+        bcap = buffer_capacity or int(max(1.0, 2.0 * p["halo"] / p["box_x"] * n_glob) * 2.0) + 1024
+        self._alloc(cap, bcap)
+        n = len(idx)
+        s = self.sets[0]
+        up = lambda a, dt: torch.from_numpy(np.ascontiguousarray(a, dtype=dt)).to(self.dev)
+        s["x"][:n] = up(xl, np.float64)
+        s["y"][:n] = up(pos[idx, 1], np.float64)
+        s["theta"][:n] = up(np.asarray(theta_global, dtype=np.float64)[idx], np.float64)
+        s["gid"][:n] = up(idx, np.int64)
+        sp = np.zeros(n_glob, dtype=np.int32) if species_global is None else np.asarray(species_global, dtype=np.int32)
+        s["species"][:n] = up(sp[idx], np.int32)
+        s["image"][:n] = up(im, np.int32)
+        s["owned"][:n] = up(owned, np.int32)
+        self.n_global = n_glob
+        self.cur, self.n, self.n_owned = 0, n, int(owned.sum())
+        self.since_exchange = 0
+        self._bind()
+
+    def set_actions_global(self, f_swim_dev, tqz_dev):
+        """manage_forces (espresso.py:1227-1235) from device arrays indexed by global id; ghosts included,
+        because they are integrated redundantly."""
+        s, n = self.local, self.n
+        g = s["gid"][:n]
+        s["f_swim"][:n] = f_swim_dev[g]
+        s["tqz"][:n] = tqz_dev[g]
+
+    def _stream(self):
+        return self.sw._stream()
+
+    # --------------------------------------------------------------- exchange
+    def exchange(self):
+        """halo refresh + migration; one device->host read of 8 ints."""
+        b, g = self.bufs, self.geom
+        old, new = self.sets[self.cur], self.sets[self.cur ^ 1]
+        a_old, a_new = self._dd(old), self._dd(new)
+        _lib.check(self.lib.swarm_dd_pack(self.h, C.byref(g), self.n, C.byref(a_old), b["send_l"].data_ptr(),
+                                          b["send_r"].data_ptr(), self._stream()))
+        self.transport.exchange(b["send_l"], b["send_r"], b["recv_l"], b["recv_r"])
+        _lib.check(self.lib.swarm_dd_merge(self.h, C.byref(g), self.n, C.byref(a_old), b["recv_l"].data_ptr(),
+                                           b["recv_r"].data_ptr(), self.cap, C.byref(a_new), self.counts.data_ptr(),
+                                           self._stream()))
+        self.counts_host.copy_(self.counts, non_blocking=True)
+        self.torch.cuda.current_stream(self.dev).synchronize()
+        n_new, n_owned, err = (int(v) for v in self.counts_host[:3])
+        if err:
+            why = [m for bit, m in ((1, "exchange buffer overflow"), (2, "an owned particle outran the halo"),
+                                    (4, "local capacity exceeded")) if err & bit]
+            raise OverflowError("domain exchange failed: " + ", ".join(why))
+        self.cur ^= 1
+        self.n, self.n_owned = n_new, n_owned
+        self.since_exchange = 0
+        self.exchanges += 1
+        self._bind()
+
+    # ------------------------------------------------------------ integration
+    def run(self, n_steps, step0):
+        """integrator.run(n_steps) (espresso.py:1304-1306) on the decomposed swarm."""
+        done, k = 0, self.plan["k"]
+        while done < n_steps:
+            if self.since_exchange >= k:
+                self.exchange()
+            m = min(k - self.since_exchange, n_steps - done)
+            _lib.check(self.lib.swarm_run(self.h, int(m), int(step0 + done), self._stream()))
+            self.since_exchange += m
+            done += m
+
+    def stats(self):
+        return self.sw.stats()
+
+    # --------------------------------------------------------------- read-out
+    def owned_host(self):
+        """(gid, x_global, y, theta) of the owned particles, host arrays sorted by gid."""
+        s, n = self.local, self.n
+        own = s["owned"][:n].bool()
+        gid = s["gid"][:n][own].cpu().numpy()
+        xg = unfold_global(s["x"][:n][own].cpu().numpy(), s["image"][:n][own].cpu().numpy(), self.plan)
+        y, th = s["y"][:n][own].cpu().numpy(), s["theta"][:n][own].cpu().numpy()
+        o = np.argsort(gid, kind="stable")
+        return gid[o], xg[o], y[o], th[o]
+
+    def field_reward(self, src, box_length, decay=_lib.DECAY_LINEAR, c0=1.0, c1=-1.0, scale=1.0, clip=True, init_only=False):
+        """GradientSensing reward (tasks/searching/gradient_sensing.py:92-150) of the owned particles and
+        its global mean (trainers/trainer.py:92-95): returns (per-slot rewards, device tensor [sum, mean])."""
+        torch = self.torch
+        if self.n_aux < 2:
+            raise ValueError("the field history needs n_aux >= 2")
+        a = self._dd(self.local)
+        s3 = (C.c_double * 3)(*[float(v) for v in src])
+        b2 = (C.c_double * 2)(float(box_length[0]), float(box_length[1]))
+        _lib.check(self.lib.swarm_dd_obs_field(self.h, self.n, C.byref(a), self.plan["x_offset"], self.plan["box_x"], s3, b2,
+                                               int(decay), float(c0), float(c1), float(scale), int(bool(clip)),
+                                               int(bool(init_only)), self.out.data_ptr(), self._stream()))
+        red = self.sw.reduce_mean(self.out[: max(self.n, 1)])
+        tot = red[:1].clone()
+        self.transport.all_reduce_sum(tot)
+        return self.out[: self.n], torch.cat([tot, tot / float(self.n_global)])
+
+    def close(self):
+        self.sw.close()
