@@ -172,6 +172,11 @@ int swarm_reserve(swarm_t *s, int64_t n_max);
  * Reset to NULL (slot index) by swarm_bind_state. */
 int swarm_bind_ids(swarm_t *s, const int64_t *gid_dev);
 
+/* Device-resident particle count (int32, device): the kernels of swarm_run then advance
+ * min(*n_dev, n) particles, n being the bound passed to swarm_bind_state.  Persistent kernels only.
+ * Reset to NULL by swarm_bind_state. */
+int swarm_bind_count(swarm_t *s, const int32_t *n_dev);
+
 /* ---- domain decomposition (no reference counterpart, ESPResSo runs single-rank) ---
  * Slab decomposition along x of a 2-D periodic swarm.  Local frame of a rank: owned slab
  * [halo, halo + slab_w), kept region [0, slab_w + 2 halo); the local swarm_t is created with
@@ -198,19 +203,22 @@ typedef struct {
 int64_t swarm_dd_buffer_doubles(const swarm_dd_geom_t *g);
 /* owned particles within `halo` of a slab face (or beyond it: migrants) -> send buffers, x already in
  * the receiver's frame */
-int swarm_dd_pack(swarm_t *s, const swarm_dd_geom_t *g, int64_t n, const swarm_dd_arrays_t *loc, double *send_left_dev,
-                  double *send_right_dev, void *stream);
+int swarm_dd_pack(swarm_t *s, const swarm_dd_geom_t *g, int64_t n, const int32_t *n_dev, const swarm_dd_arrays_t *loc,
+                  double *send_left_dev, double *send_right_dev, void *stream);
 /* new local set = old owned + both received buffers, restricted to the kept region; owned recomputed.
  * counts8_dev: [0] new n, [1] owned, [2] error bits (1 buffer overflow, 2 a particle outran the halo,
- * 4 local capacity exceeded). */
-int swarm_dd_merge(swarm_t *s, const swarm_dd_geom_t *g, int64_t n_old, const swarm_dd_arrays_t *old_loc,
+ * 4 local capacity exceeded), [3] the same bits, sticky across calls (never reset by the library).
+ * Every `n` of the dd calls is an upper bound when the matching *_dev count pointer is non-NULL: the live
+ * count is then read on the device (counts8_dev[0] of the previous merge), so a rank can queue
+ * exchange after exchange without a host synchronisation. */
+int swarm_dd_merge(swarm_t *s, const swarm_dd_geom_t *g, int64_t n_old, const int32_t *n_old_dev, const swarm_dd_arrays_t *old_loc,
                    const double *recv_left_dev, const double *recv_right_dev, int64_t cap_new,
                    const swarm_dd_arrays_t *new_loc, int32_t *counts8_dev, void *stream);
 
 /* swarm_obs_field for the owned particles of a sub-domain, on global unfolded coordinates
  * x_global = x_local + x_offset + image * box_x; history (p_prev) in aux channels 0, 1; out_dev[n],
  * 0 for ghosts.  init_only = 1 just seeds the history. */
-int swarm_dd_obs_field(swarm_t *s, int64_t n, const swarm_dd_arrays_t *loc, double x_offset, double box_x,
+int swarm_dd_obs_field(swarm_t *s, int64_t n, const int32_t *n_dev, const swarm_dd_arrays_t *loc, double x_offset, double box_x,
                        const double src[3], const double box_length[2], int32_t decay, double c0, double c1,
                        double scale, int32_t clip_nonneg, int32_t init_only, double *out_dev, void *stream);
 

@@ -90,11 +90,12 @@ SYMBOLS = {
     "swarm_bind_actions": (C.c_int, [_V, C.POINTER(ActionsDev)]),
     "swarm_reserve": (C.c_int, [_V, C.c_int64]),
     "swarm_bind_ids": (C.c_int, [_V, _V]),
+    "swarm_bind_count": (C.c_int, [_V, _V]),
     "swarm_dd_buffer_doubles": (C.c_int64, [C.POINTER(DDGeom)]),
-    "swarm_dd_pack": (C.c_int, [_V, C.POINTER(DDGeom), C.c_int64, C.POINTER(DDArrays), _V, _V, _V]),
-    "swarm_dd_merge": (C.c_int, [_V, C.POINTER(DDGeom), C.c_int64, C.POINTER(DDArrays), _V, _V, C.c_int64,
+    "swarm_dd_pack": (C.c_int, [_V, C.POINTER(DDGeom), C.c_int64, _V, C.POINTER(DDArrays), _V, _V, _V]),
+    "swarm_dd_merge": (C.c_int, [_V, C.POINTER(DDGeom), C.c_int64, _V, C.POINTER(DDArrays), _V, _V, C.c_int64,
                                  C.POINTER(DDArrays), _V, _V]),
-    "swarm_dd_obs_field": (C.c_int, [_V, C.c_int64, C.POINTER(DDArrays), C.c_double, C.c_double, _DP, _DP, C.c_int32,
+    "swarm_dd_obs_field": (C.c_int, [_V, C.c_int64, _V, C.POINTER(DDArrays), C.c_double, C.c_double, _DP, _DP, C.c_int32,
                                      C.c_double, C.c_double, C.c_double, C.c_int32, C.c_int32, _V, _V]),
     "swarm_apply_new_direction": (C.c_int, [_V, _V]),
     "swarm_relax": (C.c_int, [_V, C.c_int64, C.c_double, C.c_double, _V]),

@@ -64,7 +64,7 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_resident(const __grid_c
   const int ptid = (int)threadIdx.x - 32;  // warp 0 is the barrier warp
   const int ppc = R.particles_per_cta;     // particles are spread evenly over the CTAs (one CTA per SM)
   const long long i = (long long)blockIdx.x * ppc + ptid;
-  const bool act = ptid >= 0 && ptid < ppc && i < A.n;
+  const bool act = ptid >= 0 && ptid < ppc && i < sw_live_n(A);
   const bool leader = act && i == 0;
   double xi = 0.0, yi = 0.0, th = 0.0, xr = 0.0, yr = 0.0, fsw = 0.0, Tz = 0.0, fxe = 0.0, fye = 0.0;
   int sp = 0, ti = 0;
@@ -240,6 +240,150 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_resident(const __grid_c
       }
       A.vx[i] = vx_l + sv * gv[0]; A.vy[i] = vy_l + sv * gv[1]; A.vz[i] = 0.0;
       A.wx[i] = 0.0; A.wy[i] = 0.0; A.wz[i] = w + sw * gw[0];
+    }
+  }
+  if (leader) {
+    ctl->steps_done = s;
+    if (s < R.n_steps) ctl->halted = 1;
+    ctl->rebuild_flag[0] = 0; ctl->rebuild_flag[1] = 0; ctl->rebuild_flag[2] = 0;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// k_bd2d_stream -- the 2-D Brownian chunk for swarms too large for one particle per thread (the
+// 1M-particle slabs of the domain-decomposed swarm, BASELINE config 5).  Same loop as k_persist (one
+// grid barrier per step, in-kernel Verlet rebuild), but a lean step: per-species constants hoisted to
+// shared memory once per launch, the resident kernel's arithmetic (3-normal Philox draw, reciprocal
+// multiplies), neighbour positions fetched four at a time so their L2 round trips overlap, and a
+// register budget that keeps 3 CTAs (24 warps) per SM.
+// ---------------------------------------------------------------------------------------------
+struct Bd2dSpecies { double gt1, gt2, gr0, r_gt1, r_gt2, r_gr0, sg_par, sg_per, sg_rot, sv, sw; };
+
+template <bool NOISE>
+__device__ __forceinline__ bool bd2d_step_stream(const DevParams &P, const DevArrays &A, const Bd2dSpecies *S, int cur, u64 step,
+                                                 bool last, long long i, double lim2) {
+  const int nxt = cur ^ 1;
+  const int sp = A.species[i];
+  const int ti = P.sp_type[sp];
+  const Bd2dSpecies c = S[sp];
+  const double xi = ldcg(&A.x[cur][i]), yi = ldcg(&A.y[cur][i]);
+  const double th = A.theta[i];
+  const int cnt = A.nbr_cnt[i];
+  double Fx = 0.0, Fy = 0.0;
+  for (int k0 = 0; k0 < cnt; k0 += 4) {
+    int en[4];
+    double xj[4], yj[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      en[u] = (k0 + u < cnt) ? A.nbr[(long long)(k0 + u) * A.n_pad + i] : (int)i;
+      const int j = en[u] & SW_IDX_MASK;
+      xj[u] = ldcg(&A.x[cur][j]); yj[u] = ldcg(&A.y[cur][j]);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (k0 + u < cnt) bd2d_pair(P, xi, yi, ti, en[u] >> SW_TYPE_SHIFT, xj[u], yj[u], Fx, Fy);
+  }
+  double ex, ey;
+  sincos(th, &ey, &ex);
+  const Bd2dSelf sf = bd2d_self_forces(P, ti, xi, yi, ex, ey, A.f_swim[i]);
+  Fx += sf.wx; Fy += sf.wy;
+  Fx += sf.sx; Fy += sf.sy;
+  if (A.fex) { Fx += A.fex[i]; Fy += A.fey[i]; }
+  double g0 = 0.0, g1 = 0.0, g3 = 0.0;
+  const u64 pid = sw_pid(A, i);
+  if (NOISE) swm_gaussians_xyt(P.seed, pid, step, g0, g1, g3);
+  const double dt = P.dt;
+  double xn, yn, vx, vy;
+  if (c.gt1 == c.gt2) {
+    vx = swm_div_r(Fx, c.gt2, c.r_gt2); vy = swm_div_r(Fy, c.gt2, c.r_gt2);
+    xn = xi + vx * dt; yn = yi + vy * dt;
+    if (NOISE) { xn += c.sg_par * g0; yn += c.sg_par * g1; }
+  } else {
+    const double fpar = Fx * ex + Fy * ey, fper = -Fx * ey + Fy * ex;
+    const double vpar = swm_div_r(fpar, c.gt2, c.r_gt2), vper = swm_div_r(fper, c.gt1, c.r_gt1);
+    vx = vpar * ex - vper * ey; vy = vpar * ey + vper * ex;
+    xn = xi + vx * dt; yn = yi + vy * dt;
+    if (NOISE) {
+      const double spar = c.sg_par * g0, sper = c.sg_per * g1;
+      xn += spar * ex - sper * ey; yn += spar * ey + sper * ex;
+    }
+  }
+  const double w = swm_div_r(A.tqz[i], c.gr0, c.r_gr0);
+  double thn = th + w * dt;
+  if (NOISE) thn += c.sg_rot * g3;
+  A.theta[i] = thn;
+  A.x[nxt][i] = xn; A.y[nxt][i] = yn;
+  if (last) {
+    double gv[4] = {0, 0, 0, 0}, gw[4] = {0, 0, 0, 0};
+    if (NOISE) {
+      swm_gaussians(P.seed, pid, step, 2, gv);
+      swm_gaussians(P.seed, pid, step, 3, gw);
+    }
+    A.vx[i] = vx + c.sv * gv[0]; A.vy[i] = vy + c.sv * gv[1]; A.vz[i] = 0.0;
+    A.wx[i] = 0.0; A.wy[i] = 0.0; A.wz[i] = w + c.sw * gw[0];
+  }
+  const double ddx = xn - A.xr[i], ddy = yn - A.yr[i];
+  return (ddx * ddx + ddy * ddy) > lim2;
+}
+
+#define SW_STREAM_THREADS 256
+template <bool NOISE>
+__global__ void __launch_bounds__(SW_STREAM_THREADS, 3) k_bd2d_stream(const __grid_constant__ DevParams P, DevArrays A, RunArgs R) {
+  Ctl *ctl = A.ctl;
+  if (ldcg(&ctl->halted)) return;
+  __shared__ Bd2dSpecies S[SW_S];
+  if (threadIdx.x < P.n_species) {
+    const int sp = threadIdx.x;
+    Bd2dSpecies c;
+    c.gt1 = P.sp_gt[sp][1]; c.gt2 = P.sp_gt[sp][2]; c.gr0 = P.sp_gr[sp][0];
+    c.r_gt1 = swm_rcp(c.gt1); c.r_gt2 = swm_rcp(c.gt2); c.r_gr0 = swm_rcp(c.gr0);
+    c.sg_par = NOISE ? sqrt(2.0 * P.kT * P.dt / c.gt2) : 0.0;
+    c.sg_per = NOISE ? sqrt(2.0 * P.kT * P.dt / c.gt1) : 0.0;
+    c.sg_rot = NOISE ? sqrt(2.0 * P.kT * P.dt / c.gr0) : 0.0;
+    c.sv = NOISE ? sqrt(P.kT / P.sp_mass[sp]) : 0.0;
+    c.sw = NOISE ? sqrt(P.kT / P.sp_rin[sp][0]) : 0.0;
+    S[sp] = c;
+  }
+  __syncthreads();
+  unsigned int epoch = 0;
+  const long long lo = (long long)blockIdx.x * blockDim.x, hi = sw_live_n(A);
+  const long long gstride = (long long)gridDim.x * blockDim.x;
+  const bool leader = (blockIdx.x == 0 && threadIdx.x == 0);
+  const double lim2 = (0.5 * P.skin) * (0.5 * P.skin);
+
+  bool need = true;
+  if (!R.force_rebuild) {
+    bool moved = false;
+    for (long long i = lo + threadIdx.x; i < hi; i += gstride) moved |= moved_since_build<2>(P, A, 0, i);
+    if (moved) ctl->rebuild_flag[0] = 1;
+    grid_barrier(&ctl->barrier, epoch);
+    need = ldcg(&ctl->rebuild_flag[0]) != 0;
+  }
+  long long s = 0;
+  for (; s < R.n_steps; ++s) {
+    const int cur = (int)(s & 1);
+    if (s > 0) need = ldcg(&ctl->rebuild_flag[s % 3]) != 0;
+    if (need) {
+      for (long long i = lo + threadIdx.x; i < hi; i += gstride) phase_clear<2>(P, A, cur, i);
+      grid_barrier(&ctl->barrier, epoch);
+      for (long long i = lo + threadIdx.x; i < hi; i += gstride) phase_insert(A, i);
+      grid_barrier(&ctl->barrier, epoch);
+      for (long long i = lo + threadIdx.x; i < hi; i += gstride) phase_search<2>(P, A, cur, i);
+      if (leader) ctl->rebuilds += 1;
+      grid_barrier(&ctl->barrier, epoch);
+      if (ldcg(&ctl->overflow)) break;
+    }
+    const bool last = (s == R.n_steps - 1);
+    bool moved = false;
+    for (long long i = lo + threadIdx.x; i < hi; i += gstride)
+      moved |= bd2d_step_stream<NOISE>(P, A, S, cur, R.step0 + (u64)s, last, i, lim2);
+    if (moved) ctl->rebuild_flag[(s + 1) % 3] = 1;
+    if (leader) ctl->rebuild_flag[(s + 2) % 3] = 0;
+    grid_barrier(&ctl->barrier, epoch);
+  }
+  if (s & 1) {
+    for (long long i = lo + threadIdx.x; i < hi; i += gstride) {
+      A.x[0][i] = ldcg(&A.x[1][i]); A.y[0][i] = ldcg(&A.y[1][i]);
     }
   }
   if (leader) {

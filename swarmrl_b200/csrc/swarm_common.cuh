@@ -60,6 +60,7 @@ struct DevArrays {
   double *vx, *vy, *vz, *wx, *wy, *wz;
   double *f_swim, *tqx, *tqy, *tqz, *fex, *fey, *fez;
   const int *species;
+  const int *n_dev;           // live particle count on the device (<= n), or NULL; see swarm_bind_count
   const long long *gid;       // Philox id of every slot (domain decomposition); NULL => the slot index
   double *xr, *yr, *zr;        // positions at the last Verlet rebuild
   int *head, *next, *cellof;   // linked cells
@@ -67,6 +68,13 @@ struct DevArrays {
   int cap;
   Ctl *ctl;
 };
+
+// live particle count: the device-resident one when bound (domain decomposition re-partitions without a host sync)
+__device__ __forceinline__ long long sw_live_n(const DevArrays &A) {
+  if (!A.n_dev) return A.n;
+  const long long m = (long long)__ldg(A.n_dev);
+  return m < A.n ? m : A.n;
+}
 
 // Philox key id of slot i: the global particle id when the slots hold a sub-domain of a larger swarm
 __device__ __forceinline__ u64 sw_pid(const DevArrays &A, long long i) { return A.gid ? (u64)A.gid[i] : (u64)i; }

@@ -34,15 +34,31 @@ static DdArrays dd_arrays(const swarm_dd_arrays_t *a) {
   return d;
 }
 
-// warp-aggregated append: returns the slot of this lane (or -1 when !want)
-__device__ __forceinline__ long long dd_append(unsigned long long *counter, bool want) {
+// live count: device-resident when given (no host sync between exchanges), bounded by the host's n
+__device__ __forceinline__ long long dd_live(long long n, const int *n_dev) {
+  if (!n_dev) return n;
+  const long long m = (long long)__ldg(n_dev);   // L1-cached: a .cg load from a million threads hammers one L2 sector
+  return m < n ? m : n;
+}
+
+// CTA-aggregated append: one atomicAdd per CTA (same-address atomics serialise in L2 at ~2.5 ns each, so
+// one per warp made the 1M-particle merge atomic-bound).  Every thread of the CTA must call it; `slot`
+// selects one of two independent appends per kernel.  Returns this thread's slot, or -1 when !want.
+#define DD_THREADS 512
+__device__ __forceinline__ long long dd_append(unsigned long long *counter, bool want, int slot) {
+  __shared__ unsigned int wcnt[2][DD_THREADS / 32];
+  __shared__ unsigned long long base[2];
   const unsigned m = __ballot_sync(0xFFFFFFFFu, want);
-  if (!m) return -1;
-  const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
-  unsigned long long base = 0;
-  if (lane == leader) base = atomicAdd(counter, (unsigned long long)__popc(m));
-  base = __shfl_sync(0xFFFFFFFFu, base, leader);
-  return want ? (long long)(base + __popc(m & ((1u << lane) - 1u))) : -1;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) wcnt[slot][warp] = __popc(m);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned int tot = 0;
+    for (int w = 0; w < DD_THREADS / 32; ++w) { const unsigned int c = wcnt[slot][w]; wcnt[slot][w] = tot; tot += c; }
+    base[slot] = tot ? atomicAdd(counter, (unsigned long long)tot) : 0ULL;
+  }
+  __syncthreads();
+  return want ? (long long)(base[slot] + wcnt[slot][warp] + __popc(m & ((1u << lane) - 1u))) : -1;
 }
 
 __device__ __forceinline__ void dd_store(double *buf, long long cap, int n_aux, long long j, const DdArrays &L, long long i,
@@ -56,25 +72,28 @@ __device__ __forceinline__ void dd_store(double *buf, long long cap, int n_aux, 
   r[5 * cap + j] = (double)L.gid[i];
   r[6 * cap + j] = (double)L.species[i];
   r[7 * cap + j] = (double)image_new;
-  for (int c = 0; c < n_aux; ++c) r[(DD_FIXED + c) * cap + j] = L.aux[c][i];
+#pragma unroll
+  for (int c = 0; c < SWARM_DD_MAX_AUX; ++c)
+    if (c < n_aux) r[(DD_FIXED + c) * cap + j] = L.aux[c][i];
 }
 
-__global__ void k_dd_pack(swarm_dd_geom_t G, long long n, DdArrays L, double *send_left, double *send_right) {
+__global__ void k_dd_pack(swarm_dd_geom_t G, long long n, const int *n_dev, DdArrays L, double *send_left, double *send_right) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  const bool act = i < n && L.owned[i] != 0;
+  const bool act = i < dd_live(n, n_dev) && L.owned[i] != 0;
   const double x = act ? L.x[i] : 0.0;
   const bool to_l = act && x < 2.0 * G.halo;   // within H of the left face, or already beyond it
   const bool to_r = act && x >= G.slab_w;      // within H of the right face (H + W - H), or beyond
-  long long j = dd_append((unsigned long long *)send_left, to_l);
+  long long j = dd_append((unsigned long long *)send_left, to_l, 0);
   if (to_l && j < G.cap) dd_store(send_left, G.cap, G.n_aux, j, L, i, x + G.slab_w, L.image[i] + G.image_shift_left);
-  j = dd_append((unsigned long long *)send_right, to_r);
+  j = dd_append((unsigned long long *)send_right, to_r, 1);
   if (to_r && j < G.cap) dd_store(send_right, G.cap, G.n_aux, j, L, i, x - G.slab_w, L.image[i] + G.image_shift_right);
 }
 
 // t < n_old: old local slot t (kept when owned); then the records of recv_left, then of recv_right
-__global__ void k_dd_merge(swarm_dd_geom_t G, long long n_old, DdArrays O, const double *recv_left, const double *recv_right,
+__global__ void k_dd_merge(swarm_dd_geom_t G, long long n_bound, const int *n_dev, DdArrays O, const double *recv_left, const double *recv_right,
                            long long cap_new, DdArrays N, int *counts) {
   const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long n_old = dd_live(n_bound, n_dev);
   const unsigned long long cl = *(const unsigned long long *)recv_left, cr = *(const unsigned long long *)recv_right;
   if (t == 0 && (cl > (unsigned long long)G.cap || cr > (unsigned long long)G.cap)) atomicOr(&counts[2], 1);
   const long long nl = cl > (unsigned long long)G.cap ? G.cap : (long long)cl;
@@ -93,28 +112,35 @@ __global__ void k_dd_merge(swarm_dd_geom_t G, long long n_old, DdArrays O, const
   }
   const bool keep = cand && x >= 0.0 && x < G.slab_w + 2.0 * G.halo;
   if (cand && !keep && !rec) atomicOr(&counts[2], 2);  // an owned particle outran the halo: k or H too small
-  const long long o = dd_append((unsigned long long *)(counts + 4), keep);
+  const long long o = dd_append((unsigned long long *)(counts + 4), keep, 0);
+  const bool fits = keep && o < cap_new;
+  const int own = (fits && x >= G.halo && x < G.halo + G.slab_w) ? 1 : 0;
+  const int own_cta = __syncthreads_count(own);
+  if (threadIdx.x == 0 && own_cta) atomicAdd(&counts[1], own_cta);
   if (!keep) return;
-  if (o >= cap_new) { atomicOr(&counts[2], 4); return; }
-  const int own = (x >= G.halo && x < G.halo + G.slab_w) ? 1 : 0;
-  if (own) atomicAdd(&counts[1], 1);
+  if (!fits) { atomicOr(&counts[2], 4); return; }
   N.x[o] = x;
   N.owned[o] = own;
   if (!rec) {
     N.y[o] = O.y[t]; N.theta[o] = O.theta[t]; N.f_swim[o] = O.f_swim[t]; N.tqz[o] = O.tqz[t];
     N.gid[o] = O.gid[t]; N.species[o] = O.species[t]; N.image[o] = O.image[t];
-    for (int c = 0; c < G.n_aux; ++c) N.aux[c][o] = O.aux[c][t];
+#pragma unroll
+    for (int c = 0; c < SWARM_DD_MAX_AUX; ++c)
+      if (c < G.n_aux) N.aux[c][o] = O.aux[c][t];
   } else {
     const long long cap = G.cap;
     N.y[o] = rec[1 * cap + j]; N.theta[o] = rec[2 * cap + j]; N.f_swim[o] = rec[3 * cap + j]; N.tqz[o] = rec[4 * cap + j];
     N.gid[o] = (long long)rec[5 * cap + j]; N.species[o] = (int)rec[6 * cap + j]; N.image[o] = (int)rec[7 * cap + j];
-    for (int c = 0; c < G.n_aux; ++c) N.aux[c][o] = rec[(DD_FIXED + c) * cap + j];
+#pragma unroll
+    for (int c = 0; c < SWARM_DD_MAX_AUX; ++c)
+      if (c < G.n_aux) N.aux[c][o] = rec[(DD_FIXED + c) * cap + j];
   }
 }
 
 __global__ void k_dd_finish(int *counts) {
   const unsigned long long n = *(unsigned long long *)(counts + 4);
   counts[0] = (int)n;
+  counts[3] |= counts[2];   // sticky error bits: survive the next merge's reset of counts[2]
 }
 
 static int dd_check(const swarm_dd_geom_t *g) {
@@ -130,8 +156,8 @@ extern "C" int64_t swarm_dd_buffer_doubles(const swarm_dd_geom_t *g) {
   return 1 + (int64_t)(DD_FIXED + g->n_aux) * g->cap;
 }
 
-extern "C" int swarm_dd_pack(swarm_t *s, const swarm_dd_geom_t *g, int64_t n, const swarm_dd_arrays_t *loc, double *send_left_dev,
-                             double *send_right_dev, void *stream) {
+extern "C" int swarm_dd_pack(swarm_t *s, const swarm_dd_geom_t *g, int64_t n, const int32_t *n_dev, const swarm_dd_arrays_t *loc,
+                             double *send_left_dev, double *send_right_dev, void *stream) {
   if (!s || !loc || !send_left_dev || !send_right_dev || n < 0) { sw_set_error("bad arguments"); return SWARM_ERR_INVALID; }
   int rc = dd_check(g);
   if (rc) return rc;
@@ -140,14 +166,14 @@ extern "C" int swarm_dd_pack(swarm_t *s, const swarm_dd_geom_t *g, int64_t n, co
   SW_CUDA(cudaMemsetAsync(send_left_dev, 0, 8, st));
   SW_CUDA(cudaMemsetAsync(send_right_dev, 0, 8, st));
   if (n > 0) {
-    k_dd_pack<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(*g, n, dd_arrays(loc), send_left_dev, send_right_dev);
+    k_dd_pack<<<(unsigned)((n + DD_THREADS - 1) / DD_THREADS), DD_THREADS, 0, st>>>(*g, n, (const int *)n_dev, dd_arrays(loc), send_left_dev, send_right_dev);
     s->launches += 1;
   }
   SW_CUDA(cudaGetLastError());
   return SWARM_OK;
 }
 
-extern "C" int swarm_dd_merge(swarm_t *s, const swarm_dd_geom_t *g, int64_t n_old, const swarm_dd_arrays_t *old_loc,
+extern "C" int swarm_dd_merge(swarm_t *s, const swarm_dd_geom_t *g, int64_t n_old, const int32_t *n_old_dev, const swarm_dd_arrays_t *old_loc,
                               const double *recv_left_dev, const double *recv_right_dev, int64_t cap_new,
                               const swarm_dd_arrays_t *new_loc, int32_t *counts8_dev, void *stream) {
   if (!s || !old_loc || !new_loc || !recv_left_dev || !recv_right_dev || !counts8_dev || n_old < 0 || cap_new < 1) {
@@ -157,9 +183,11 @@ extern "C" int swarm_dd_merge(swarm_t *s, const swarm_dd_geom_t *g, int64_t n_ol
   if (rc) return rc;
   SW_CUDA(cudaSetDevice(s->cfg.device));
   cudaStream_t st = (cudaStream_t)stream;
-  SW_CUDA(cudaMemsetAsync(counts8_dev, 0, 8 * sizeof(int), st));
+  // counts[3] (sticky error bits) survives; everything else restarts
+  SW_CUDA(cudaMemsetAsync(counts8_dev, 0, 3 * sizeof(int), st));
+  SW_CUDA(cudaMemsetAsync(counts8_dev + 4, 0, 4 * sizeof(int), st));
   const long long total = n_old + 2LL * g->cap;
-  k_dd_merge<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(*g, n_old, dd_arrays(old_loc), recv_left_dev, recv_right_dev, cap_new,
+  k_dd_merge<<<(unsigned)((total + DD_THREADS - 1) / DD_THREADS), DD_THREADS, 0, st>>>(*g, n_old, (const int *)n_old_dev, dd_arrays(old_loc), recv_left_dev, recv_right_dev, cap_new,
                                                              dd_arrays(new_loc), counts8_dev);
   k_dd_finish<<<1, 1, 0, st>>>(counts8_dev);
   s->launches += 2;
@@ -179,11 +207,11 @@ __device__ __forceinline__ double dd_decay(int kind, double c0, double c1, doubl
   }
 }
 
-__global__ void k_dd_obs_field(long long n, DdArrays L, double x_off, double box_x, double s0, double s1, double s2, double b0,
+__global__ void k_dd_obs_field(long long n, const int *n_dev, DdArrays L, double x_off, double box_x, double s0, double s1, double s2, double b0,
                                double b1, int decay, double c0, double c1, double scale, int clip, int init_only, double *out) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  if (!L.owned[i]) { out[i] = 0.0; return; }
+  if (i >= dd_live(n, n_dev) || !L.owned[i]) { out[i] = 0.0; return; }
   const double xg = L.x[i] + x_off + (double)L.image[i] * box_x;
   const double p0 = xg / b0, p1 = L.y[i] / b1;
   const double h0 = L.aux[0][i], h1 = L.aux[1][i];
@@ -196,7 +224,7 @@ __global__ void k_dd_obs_field(long long n, DdArrays L, double x_off, double box
   out[i] = v;
 }
 
-extern "C" int swarm_dd_obs_field(swarm_t *s, int64_t n, const swarm_dd_arrays_t *loc, double x_offset, double box_x,
+extern "C" int swarm_dd_obs_field(swarm_t *s, int64_t n, const int32_t *n_dev, const swarm_dd_arrays_t *loc, double x_offset, double box_x,
                                   const double src[3], const double box_length[2], int32_t decay, double c0, double c1,
                                   double scale, int32_t clip_nonneg, int32_t init_only, double *out_dev, void *stream) {
   if (!s || !loc || !src || !box_length || !out_dev || n < 0 || !loc->aux[0] || !loc->aux[1]) {
@@ -205,7 +233,7 @@ extern "C" int swarm_dd_obs_field(swarm_t *s, int64_t n, const swarm_dd_arrays_t
   if (decay < SWARM_DECAY_NONE || decay > SWARM_DECAY_INVERSE) { sw_set_error("unknown decay kind"); return SWARM_ERR_INVALID; }
   SW_CUDA(cudaSetDevice(s->cfg.device));
   if (n == 0) return SWARM_OK;
-  k_dd_obs_field<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(n, dd_arrays(loc), x_offset, box_x, src[0], src[1],
+  k_dd_obs_field<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(n, (const int *)n_dev, dd_arrays(loc), x_offset, box_x, src[0], src[1],
                                                                                src[2], box_length[0], box_length[1], decay, c0, c1,
                                                                                scale, clip_nonneg, init_only, out_dev);
   s->launches += 1;

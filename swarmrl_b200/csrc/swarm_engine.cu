@@ -398,7 +398,7 @@ __global__ void __launch_bounds__(SW_THREADS) k_persist(const __grid_constant__ 
   if (ldcg(&ctl->halted)) return;
   unsigned int epoch = 0;
   // grid-stride ownership: thread t owns particles t, t + T, t + 2T, ... (balanced to one particle)
-  const long long lo = (long long)blockIdx.x * blockDim.x, hi = A.n;
+  const long long lo = (long long)blockIdx.x * blockDim.x, hi = sw_live_n(A);
   const long long gstride = (long long)gridDim.x * blockDim.x;
   const bool leader = (blockIdx.x == 0 && threadIdx.x == 0);
 
@@ -828,6 +828,7 @@ extern "C" int swarm_bind_state(swarm_t *s, int64_t n, const swarm_state_dev_t *
   A.vx = st->vx; A.vy = st->vy; A.vz = st->vz; A.wx = st->wx; A.wy = st->wy; A.wz = st->wz;
   A.species = st->species;
   A.gid = nullptr;
+  A.n_dev = nullptr;
   s->P.env_size = (int)(n / s->P.n_envs);
   if (s->P.env_size < 1) s->P.env_size = 1;
   if (!reuse) {
@@ -878,6 +879,15 @@ extern "C" int swarm_reserve(swarm_t *s, int64_t n_max) {
   if (!s || n_max < 0) { sw_set_error("bad arguments"); return SWARM_ERR_INVALID; }
   if (n_max >= (1LL << SW_TYPE_SHIFT)) { sw_set_error("n_max must be < 2^28 particles per handle"); return SWARM_ERR_INVALID; }
   s->n_reserved = n_max;
+  return SWARM_OK;
+}
+
+extern "C" int swarm_bind_count(swarm_t *s, const int32_t *n_dev) {
+  if (!s) return SWARM_ERR_INVALID;
+  if (!s->state_bound) { sw_set_error("bind the state first"); return SWARM_ERR_STATE; }
+  if (n_dev && !s->persistent) { sw_set_error("a device-resident count needs the persistent kernels"); return SWARM_ERR_STATE; }
+  s->A.n_dev = (const int *)n_dev;
+  s->list_valid = false;
   return SWARM_OK;
 }
 
@@ -991,6 +1001,29 @@ static int sw_launch_resident(swarm *s, const RunArgs &R, cudaStream_t st, bool 
   return SWARM_OK;
 }
 
+// large 2-D swarms: lean grid-stride chunk kernel, every CTA co-resident (3 per SM)
+template <bool NOISE>
+static int sw_launch_stream(swarm *s, const RunArgs &R, cudaStream_t st) {
+  auto kern = k_bd2d_stream<NOISE>;
+  int bpsm = 0;
+  SW_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bpsm, kern, SW_STREAM_THREADS, 0));
+  if (bpsm < 1) { sw_set_error("stream kernel does not fit on an SM"); return SWARM_ERR_CUDA; }
+  s->coop_blocks_per_sm = bpsm;
+  long long want = (s->A.n + SW_STREAM_THREADS - 1) / SW_STREAM_THREADS;
+  long long maxb = (long long)s->num_sms * bpsm;
+  int grid = (int)(want >= maxb ? maxb : (want > 0 ? want : 1));
+  const char *env = getenv("SWARM_B200_GRID");
+  if (env) { int g = atoi(env); if (g >= 1 && g <= maxb) grid = g; }
+  SW_CUDA(cudaMemsetAsync(&s->A.ctl->barrier, 0, sizeof(unsigned int), st));
+  DevParams P = s->P;
+  DevArrays A = s->A;
+  RunArgs Rr = R;
+  void *args[] = {(void *)&P, (void *)&A, (void *)&Rr};
+  SW_CUDA(cudaLaunchCooperativeKernel((void *)kern, dim3(grid), dim3(SW_STREAM_THREADS), args, 0, st));
+  s->launches += 1;
+  return SWARM_OK;
+}
+
 template <int DIM, bool NOISE>
 static int sw_launch_np(swarm *s, const RunArgs &R, cudaStream_t st) {
   const int T = SW_THREADS, B = sw_blocks(s->A.n > 0 ? s->A.n : 1, T);
@@ -1037,6 +1070,8 @@ static int sw_run_common(swarm *s, RunArgs R, cudaStream_t st) {
       if (rc) return rc;
     }
     if (done_resident) {
+    } else if (s->persistent && s->P.n_dims == 2 && R.mode == MODE_BD && !getenv("SWARM_B200_NO_STREAM")) {
+      rc = noise ? sw_launch_stream<true>(s, Rc, st) : sw_launch_stream<false>(s, Rc, st);
     } else if (s->persistent) {
       if (s->P.n_dims == 2) rc = noise ? sw_launch_persist<2, true>(s, Rc, st) : sw_launch_persist<2, false>(s, Rc, st);
       else rc = noise ? sw_launch_persist<3, true>(s, Rc, st) : sw_launch_persist<3, false>(s, Rc, st);

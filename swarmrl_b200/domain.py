@@ -175,8 +175,10 @@ class DomainSwarm:
                                 self.plan["image_shift_left"], self.plan["image_shift_right"])
         nd = int(self.lib.swarm_dd_buffer_doubles(C.byref(self.geom)))
         self.bufs = {k: torch.zeros(nd, **f64) for k in ("send_l", "send_r", "recv_l", "recv_r")}
-        self.counts = torch.zeros(8, dtype=torch.int32, device=self.dev)
-        self.counts_host = torch.zeros(8, dtype=torch.int32).pin_memory()
+        # per half: [0] live particle count, [1] owned, [2] error bits of the last merge, [3] sticky error bits.
+        # The count stays on the device: kernels read it there, so exchanges queue without a host sync.
+        self.counts = [torch.zeros(8, dtype=torch.int32, device=self.dev) for _ in range(2)]
+        self.counts_host = torch.zeros((2, 8), dtype=torch.int32).pin_memory()
         self.out = torch.zeros(self.cap, **f64)
         _lib.check(self.lib.swarm_reserve(self.h, self.cap))
 
@@ -195,12 +197,13 @@ class DomainSwarm:
         st.vx, st.vy, st.vz = (self.vel[a].data_ptr() for a in range(3))
         st.wx, st.wy, st.wz = (self.omega[a].data_ptr() for a in range(3))
         st.species = s["species"].data_ptr()
-        _lib.check(self.lib.swarm_bind_state(self.h, self.n, C.byref(st)))
+        _lib.check(self.lib.swarm_bind_state(self.h, self.cap, C.byref(st)))   # cap = upper bound; live count below
         act = _lib.ActionsDev()
         act.f_swim, act.tqx, act.tqy, act.tqz = s["f_swim"].data_ptr(), self.zeros.data_ptr(), self.zeros.data_ptr(), s["tqz"].data_ptr()
         _lib.check(self.lib.swarm_bind_actions(self.h, C.byref(act)))
         _lib.check(self.lib.swarm_bind_ids(self.h, s["gid"].data_ptr()))
-        self.sw.n = self.n
+        _lib.check(self.lib.swarm_bind_count(self.h, self.counts[self.cur].data_ptr()))
+        self.sw.n = self.cap
 
     @property
     def local(self):
@@ -231,44 +234,52 @@ class DomainSwarm:
         s["owned"][:n] = up(owned, np.int32)
         self.n_global = n_glob
         self.cur, self.n, self.n_owned = 0, n, int(owned.sum())
+        self.counts[0][:2] = torch.tensor([self.n, self.n_owned], dtype=torch.int32, device=self.dev)
         self.since_exchange = 0
         self._bind()
 
     def set_actions_global(self, f_swim_dev, tqz_dev):
         """manage_forces (espresso.py:1227-1235) from device arrays indexed by global id; ghosts included,
         because they are integrated redundantly."""
-        s, n = self.local, self.n
-        g = s["gid"][:n]
-        s["f_swim"][:n] = f_swim_dev[g]
-        s["tqz"][:n] = tqz_dev[g]
+        s = self.local   # whole capacity: slots past the live count hold stale but valid ids and are never read
+        torch = self.torch
+        torch.index_select(f_swim_dev, 0, s["gid"], out=s["f_swim"])
+        torch.index_select(tqz_dev, 0, s["gid"], out=s["tqz"])
 
     def _stream(self):
         return self.sw._stream()
 
     # --------------------------------------------------------------- exchange
     def exchange(self):
-        """halo refresh + migration; one device->host read of 8 ints."""
+        """halo refresh + migration, enqueued only: the new particle count stays on the device (see `sync`)."""
         b, g = self.bufs, self.geom
         old, new = self.sets[self.cur], self.sets[self.cur ^ 1]
+        c_old, c_new = self.counts[self.cur], self.counts[self.cur ^ 1]
         a_old, a_new = self._dd(old), self._dd(new)
-        _lib.check(self.lib.swarm_dd_pack(self.h, C.byref(g), self.n, C.byref(a_old), b["send_l"].data_ptr(),
-                                          b["send_r"].data_ptr(), self._stream()))
+        _lib.check(self.lib.swarm_dd_pack(self.h, C.byref(g), self.cap, c_old.data_ptr(), C.byref(a_old),
+                                          b["send_l"].data_ptr(), b["send_r"].data_ptr(), self._stream()))
         self.transport.exchange(b["send_l"], b["send_r"], b["recv_l"], b["recv_r"])
-        _lib.check(self.lib.swarm_dd_merge(self.h, C.byref(g), self.n, C.byref(a_old), b["recv_l"].data_ptr(),
-                                           b["recv_r"].data_ptr(), self.cap, C.byref(a_new), self.counts.data_ptr(),
-                                           self._stream()))
-        self.counts_host.copy_(self.counts, non_blocking=True)
+        _lib.check(self.lib.swarm_dd_merge(self.h, C.byref(g), self.cap, c_old.data_ptr(), C.byref(a_old),
+                                           b["recv_l"].data_ptr(), b["recv_r"].data_ptr(), self.cap, C.byref(a_new),
+                                           c_new.data_ptr(), self._stream()))
+        self.cur ^= 1
+        self.since_exchange = 0
+        self.exchanges += 1
+        self._bind()
+
+    def sync(self):
+        """Wait for the queued work, refresh `n` / `n_owned`, and raise if any exchange since the last call
+        overflowed a buffer or lost a particle (the device keeps sticky error bits)."""
+        for h in range(2):
+            self.counts_host[h].copy_(self.counts[h], non_blocking=True)
         self.torch.cuda.current_stream(self.dev).synchronize()
-        n_new, n_owned, err = (int(v) for v in self.counts_host[:3])
+        err = int(self.counts_host[0, 3]) | int(self.counts_host[1, 3])
         if err:
             why = [m for bit, m in ((1, "exchange buffer overflow"), (2, "an owned particle outran the halo"),
                                     (4, "local capacity exceeded")) if err & bit]
             raise OverflowError("domain exchange failed: " + ", ".join(why))
-        self.cur ^= 1
-        self.n, self.n_owned = n_new, n_owned
-        self.since_exchange = 0
-        self.exchanges += 1
-        self._bind()
+        self.n, self.n_owned = int(self.counts_host[self.cur, 0]), int(self.counts_host[self.cur, 1])
+        return self.n
 
     # ------------------------------------------------------------ integration
     def run(self, n_steps, step0):
@@ -283,12 +294,13 @@ class DomainSwarm:
             done += m
 
     def stats(self):
+        self.sync()
         return self.sw.stats()
 
     # --------------------------------------------------------------- read-out
     def owned_host(self):
         """(gid, x_global, y, theta) of the owned particles, host arrays sorted by gid."""
-        s, n = self.local, self.n
+        s, n = self.local, self.sync()
         own = s["owned"][:n].bool()
         gid = s["gid"][:n][own].cpu().numpy()
         xg = unfold_global(s["x"][:n][own].cpu().numpy(), s["image"][:n][own].cpu().numpy(), self.plan)
@@ -305,13 +317,13 @@ class DomainSwarm:
         a = self._dd(self.local)
         s3 = (C.c_double * 3)(*[float(v) for v in src])
         b2 = (C.c_double * 2)(float(box_length[0]), float(box_length[1]))
-        _lib.check(self.lib.swarm_dd_obs_field(self.h, self.n, C.byref(a), self.plan["x_offset"], self.plan["box_x"], s3, b2,
+        _lib.check(self.lib.swarm_dd_obs_field(self.h, self.cap, self.counts[self.cur].data_ptr(), C.byref(a), self.plan["x_offset"], self.plan["box_x"], s3, b2,
                                                int(decay), float(c0), float(c1), float(scale), int(bool(clip)),
                                                int(bool(init_only)), self.out.data_ptr(), self._stream()))
-        red = self.sw.reduce_mean(self.out[: max(self.n, 1)])
+        red = self.sw.reduce_mean(self.out)      # slots past the live count were written as 0
         tot = red[:1].clone()
         self.transport.all_reduce_sum(tot)
-        return self.out[: self.n], torch.cat([tot, tot / float(self.n_global)])
+        return self.out, torch.cat([tot, tot / float(self.n_global)])
 
     def close(self):
         self.sw.close()
