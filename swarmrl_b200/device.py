@@ -167,6 +167,12 @@ class DeviceSwarm:
         act.has_nd = self.has_new_dir.data_ptr()
         _lib.check(self.lib.swarm_bind_actions(self.h, C.byref(act)))
 
+    def bind_ids(self, gid):
+        """Philox ids of the bound slots (int64 device tensor): the global agent index when this handle holds
+        a shard of a larger ensemble / swarm, so results do not depend on the sharding."""
+        self._gid = gid.contiguous()
+        _lib.check(self.lib.swarm_bind_ids(self.h, self._gid.data_ptr()))
+
     # ------------------------------------------------------------ integration
     def run(self, n_steps, step0):
         """integrator.run(n_steps) -- enqueue only (espresso.py:1304-1306)."""

@@ -268,3 +268,35 @@ def test_batched_environments_are_independent():
         o.f_swim[:] = f[sl]
         o.bd_steps(0, 400, mode=0)
         assert rel_err(p[sl], o.pos) < 1e-9, e
+
+
+def test_ensemble_shards_reproduce_the_whole_ensemble_with_noise():
+    """Ensemble sharding: two handles holding E/2 environments each, their Philox ids bound
+    to the GLOBAL agent index (swarm_bind_ids), give bit-for-bit the trajectories of one handle holding all
+    E environments -- noise on, so a single mis-keyed random number would show."""
+    import torch
+
+    from swarmrl_b200.device import DeviceSwarm
+
+    E, m, L = 8, 32, 60.0
+    rng = np.random.default_rng(23)
+    sp, wca = species_for([1.0]), wca_for([1.0])
+    pos = np.concatenate([jittered_lattice(m, L, 2, rng) for _ in range(E)])
+    th = rng.uniform(0, 2 * np.pi, E * m)
+    f = rng.uniform(0, 20.0, E * m) * sp[0]["gamma_t"][0]
+
+    def run(lo, hi):
+        sl = slice(lo * m, hi * m)
+        d = DeviceSwarm(2, (L,) * 3, True, 1e-3, KT_300, 42, sp, wca, n_envs=hi - lo, skin=1.0)
+        d.set_state(pos[sl], np.zeros((hi - lo) * m, dtype=np.int32), theta=th[sl])
+        d.bind_ids(torch.arange(lo * m, hi * m, dtype=torch.int64, device=d.dev))
+        d.set_actions_host(f[sl], np.zeros(((hi - lo) * m, 3)))
+        d.run_checked(300, 0)
+        p, v, e = d.particle_data_host()
+        return p, v, e
+
+    whole = run(0, E)
+    for lo, hi in ((0, E // 2), (E // 2, E)):
+        part = run(lo, hi)
+        for a, b in zip(part, whole):
+            assert np.array_equal(a, b[lo * m:hi * m])
