@@ -259,16 +259,35 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_resident(const __grid_c
 // ---------------------------------------------------------------------------------------------
 struct Bd2dSpecies { double gt1, gt2, gr0, r_gt1, r_gt2, r_gr0, sg_par, sg_per, sg_rot, sv, sw; };
 
+__device__ __forceinline__ void sw_prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
 template <bool NOISE>
 __device__ __forceinline__ bool bd2d_step_stream(const DevParams &P, const DevArrays &A, const Bd2dSpecies *S, int cur, u64 step,
-                                                 bool last, long long i, double lim2) {
+                                                 bool last, long long i, long long i_next, double lim2) {
   const int nxt = cur ^ 1;
+  // every per-particle input is requested up front: without __restrict__ the compiler keeps each load
+  // behind the stores of the previous particle and next to its first use, which serialised four DRAM
+  // round trips per particle (ncu: 44 % long-scoreboard stalls)
   const int sp = A.species[i];
-  const int ti = P.sp_type[sp];
-  const Bd2dSpecies c = S[sp];
+  const int cnt = A.nbr_cnt[i];
   const double xi = ldcg(&A.x[cur][i]), yi = ldcg(&A.y[cur][i]);
   const double th = A.theta[i];
-  const int cnt = A.nbr_cnt[i];
+  const double fsw = A.f_swim[i], tqz = A.tqz[i];
+  const double xr = A.xr[i], yr = A.yr[i];
+  const u64 pid = sw_pid(A, i);
+  double fxe = 0.0, fye = 0.0;
+  if (A.fex) { fxe = A.fex[i]; fye = A.fey[i]; }
+  if (i_next >= 0) {
+    // pull the next particle of this thread towards L2 while this one computes
+    sw_prefetch_l2(&A.x[cur][i_next]); sw_prefetch_l2(&A.y[cur][i_next]); sw_prefetch_l2(&A.theta[i_next]);
+    sw_prefetch_l2(&A.f_swim[i_next]); sw_prefetch_l2(&A.tqz[i_next]); sw_prefetch_l2(&A.xr[i_next]); sw_prefetch_l2(&A.yr[i_next]);
+    sw_prefetch_l2(&A.nbr_cnt[i_next]); sw_prefetch_l2(&A.species[i_next]);
+    if (A.gid) sw_prefetch_l2(&A.gid[i_next]);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) sw_prefetch_l2(&A.nbr[(long long)u * A.n_pad + i_next]);
+  }
+  const int ti = P.sp_type[sp];
+  const Bd2dSpecies c = S[sp];
   double Fx = 0.0, Fy = 0.0;
   for (int k0 = 0; k0 < cnt; k0 += 4) {
     int en[4];
@@ -285,12 +304,11 @@ __device__ __forceinline__ bool bd2d_step_stream(const DevParams &P, const DevAr
   }
   double ex, ey;
   sincos(th, &ey, &ex);
-  const Bd2dSelf sf = bd2d_self_forces(P, ti, xi, yi, ex, ey, A.f_swim[i]);
+  const Bd2dSelf sf = bd2d_self_forces(P, ti, xi, yi, ex, ey, fsw);
   Fx += sf.wx; Fy += sf.wy;
   Fx += sf.sx; Fy += sf.sy;
-  if (A.fex) { Fx += A.fex[i]; Fy += A.fey[i]; }
+  if (A.fex) { Fx += fxe; Fy += fye; }
   double g0 = 0.0, g1 = 0.0, g3 = 0.0;
-  const u64 pid = sw_pid(A, i);
   if (NOISE) swm_gaussians_xyt(P.seed, pid, step, g0, g1, g3);
   const double dt = P.dt;
   double xn, yn, vx, vy;
@@ -308,7 +326,7 @@ __device__ __forceinline__ bool bd2d_step_stream(const DevParams &P, const DevAr
       xn += spar * ex - sper * ey; yn += spar * ey + sper * ex;
     }
   }
-  const double w = swm_div_r(A.tqz[i], c.gr0, c.r_gr0);
+  const double w = swm_div_r(tqz, c.gr0, c.r_gr0);
   double thn = th + w * dt;
   if (NOISE) thn += c.sg_rot * g3;
   A.theta[i] = thn;
@@ -322,7 +340,7 @@ __device__ __forceinline__ bool bd2d_step_stream(const DevParams &P, const DevAr
     A.vx[i] = vx + c.sv * gv[0]; A.vy[i] = vy + c.sv * gv[1]; A.vz[i] = 0.0;
     A.wx[i] = 0.0; A.wy[i] = 0.0; A.wz[i] = w + c.sw * gw[0];
   }
-  const double ddx = xn - A.xr[i], ddy = yn - A.yr[i];
+  const double ddx = xn - xr, ddy = yn - yr;
   return (ddx * ddx + ddy * ddy) > lim2;
 }
 
@@ -376,7 +394,7 @@ __global__ void __launch_bounds__(SW_STREAM_THREADS, 3) k_bd2d_stream(const __gr
     const bool last = (s == R.n_steps - 1);
     bool moved = false;
     for (long long i = lo + threadIdx.x; i < hi; i += gstride)
-      moved |= bd2d_step_stream<NOISE>(P, A, S, cur, R.step0 + (u64)s, last, i, lim2);
+      moved |= bd2d_step_stream<NOISE>(P, A, S, cur, R.step0 + (u64)s, last, i, (i + gstride < hi) ? i + gstride : -1, lim2);
     if (moved) ctl->rebuild_flag[(s + 1) % 3] = 1;
     if (leader) ctl->rebuild_flag[(s + 2) % 3] = 0;
     grid_barrier(&ctl->barrier, epoch);
