@@ -244,6 +244,17 @@ int swarm_obs_vision(swarm_t *s, const int32_t *row_of_dev, int64_t rows, double
                      int32_t n_cones, const double *radii_dev, const int32_t *type_col_dev, int32_t n_type_col,
                      int32_t n_cols, const double *dirs_dev, double *out_dev, void *stream);
 
+/* ParticleSensing.compute_observable (observables/particle_sensing.py:95-178) and SpeciesSearch.__call__
+ * (tasks/searching/species_search.py:97-184): field of the n_sensed particles listed (ascending) in
+ * sensed_idx_dev at every particle with row_of >= 0, with the reference's nonzero(size=n_sensed-1) rule
+ * (zero distances skipped, at most n_sensed-1 terms, padding re-reads sensed[0]).
+ *   out[row] = scale * clip(field - hist[row]); hist[row] <- field.
+ * clip_mode 0 none (observable), 1 keep >= 0 (task), -1 keep <= 0 (task, avoid=True).  init_only = 1 only
+ * seeds hist (the classes' initialize()).  out_dev / field_dev may be NULL. */
+int swarm_obs_pair_field(swarm_t *s, const int32_t *row_of_dev, const int32_t *sensed_idx_dev, int64_t n_sensed,
+                         const double box_length[3], int32_t decay, double c0, double c1, double scale, int32_t clip_mode,
+                         int32_t init_only, double *hist_rows_dev, double *out_dev, double *field_dev, void *stream);
+
 /* PositionObservable (observables/position.py:32-60): out[row] = pos / box_length, [rows][3] */
 int swarm_obs_position(swarm_t *s, const int32_t *row_of_dev, const double box_length[3], double *out_dev, void *stream);
 

@@ -19,6 +19,11 @@ Each fixture stores the inputs and the reference's outputs:
                           (gradient_sensing.py:61-150), incl. test_gradient_sensing.py:70-113
   position_director.npz   PositionObservable / Director (position.py:32-60, director.py:30-58)
   force_fn_routing.npz    ForceFunction.calc_action per-type routing (force_fn.py:52-86)
+  pair_field.npz          ParticleSensing.compute_observable (particle_sensing.py:95-178) and
+                          SpeciesSearch.__call__ (species_search.py:97-184) over call sequences:
+                          observer among the sensed set, observer of another type (the
+                          nonzero(size=n-1) quirk drops the LAST sensed particle), coincident
+                          particles (padding re-reads sensed[0]), avoid=True
 """
 from __future__ import annotations
 
@@ -192,6 +197,55 @@ def force_fn_routing():
     assert list(forces) == [0.0, 0.0, 1.0, 200.0, 0.0, 2.0, 201.0]
 
 
+def pair_fields():
+    PS = ref_shim.ref("observables.particle_sensing").ParticleSensing
+    SS = ref_shim.ref("tasks.searching.species_search").SpeciesSearch
+    Colloid = ref_shim.ref("components.colloid").Colloid
+    rng = np.random.default_rng(31)
+    n, steps = 40, 3
+    box = np.array([1000.0, 1000.0, 1000.0])
+    types = rng.integers(0, 2, n)
+    traj = np.zeros((steps + 1, n, 3))
+    traj[0, :, :2] = rng.uniform(100, 900, (n, 2))
+    for s in range(steps):
+        traj[s + 1] = traj[s]
+        traj[s + 1, :, :2] += rng.normal(0, 40, (n, 2))
+    # coincident particles: two type-0 particles share a position in the last frame
+    zero = np.nonzero(types == 0)[0]
+    traj[steps, zero[3]] = traj[steps, zero[1]]
+    dirs = np.tile([1.0, 0, 0], (n, 1))
+
+    def decay_exp(d):          # kind 2: c0 exp(-c1 d), c0 = 1, c1 = 4
+        return np.exp(-4.0 * d)
+
+    def decay_inv(d):          # kind 3: c0 / (d + c1), c0 = 0.01, c1 = 0.05
+        return 0.01 / (d + 0.05)
+
+    out = dict(traj=traj, types=types, box=box)
+    cases = [("ps_same", PS, dict(decay_fn=decay_exp, box_length=box, sensing_type=0, scale_factor=100, particle_type=0)),
+             ("ps_other", PS, dict(decay_fn=decay_inv, box_length=box, sensing_type=1, scale_factor=100, particle_type=0)),
+             ("ss_same", SS, dict(decay_fn=decay_exp, box_length=box, sensing_type=1, avoid=False, scale_factor=100, particle_type=1)),
+             ("ss_avoid", SS, dict(decay_fn=decay_inv, box_length=box, sensing_type=0, avoid=True, scale_factor=10, particle_type=1))]
+    for name, cls, kw in cases:
+        ob = cls(**kw)
+        ob.initialize(_colloids(Colloid, traj[0], dirs, types))
+        vals = []
+        for s in range(1, steps + 1):
+            cols = _colloids(Colloid, traj[s], dirs, types)
+            r = ob.compute_observable(cols) if cls is PS else ob(cols)
+            vals.append(np.asarray(r, dtype=float).reshape(-1))
+        out[name] = np.array(vals)
+    np.savez_compressed(OUT / "pair_field.npz", **out)
+
+    # the reference's own unit case (CI/unit_tests/tasks/test_species_search.py:46-128): history values
+    ss = SS(decay_fn=lambda x: 1 - x, box_length=np.array([1.0, 1.0, 1.0]), sensing_type=1, avoid=False, scale_factor=1,
+            particle_type=0)
+    p = np.array([[0.0, 0, 0], [1.0, 1, 0], [0.0, 1, 0], [1.0, 0, 0]])
+    ss.initialize(_colloids(Colloid, p, np.tile([1.0, 0, 0], (4, 1)), [0, 1, 1, 1]))
+    hist = np.array([ss.historical_field[str(i)] for i in [0]])
+    np.savez_compressed(OUT / "species_search_unit.npz", pos=p, types=np.array([0, 1, 1, 1]), hist=hist)
+
+
 if __name__ == "__main__":
     OUT.mkdir(parents=True, exist_ok=True)
     vision_cones()
@@ -199,4 +253,5 @@ if __name__ == "__main__":
     field_sequences()
     position_director()
     force_fn_routing()
+    pair_fields()
     print("golden fixtures written to", OUT)

@@ -273,6 +273,39 @@ class OracleSwarm:
         return out
 
 
+def decay_eval(kind, c0, c1, d):
+    """swarm_decay_t: 1 linear c0 + c1 d, 2 exponential c0 exp(-c1 d), 3 inverse c0 / (d + c1)."""
+    d = np.asarray(d, dtype=np.float64)
+    return {1: lambda: c0 + c1 * d, 2: lambda: c0 * np.exp(-c1 * d), 3: lambda: c0 / (d + c1)}[int(kind)]()
+
+
+def pair_field(pos, ptype, particle_type, sensing_type, box_length, kind, c0, c1):
+    """Field value of every particle of `particle_type` (index order) summed over the particles of
+    `sensing_type`: ParticleSensing.compute_single_observable (/root/reference/swarmrl/observables/
+    particle_sensing.py:95-131) == SpeciesSearch.compute_single_particle_task (tasks/searching/
+    species_search.py:97-133):
+        d = |(x_j - x_i) / box_length|;  idx = nonzero(d, size=M-1)  (first M-1 non-zero entries in
+        index order, PADDED WITH INDEX 0 when fewer exist);  field = sum decay(d[idx]).
+    So an observer outside the sensed set silently loses the LAST sensed particle, and coincident
+    particles make sensed[0] count again."""
+    pos = np.asarray(pos, dtype=np.float64).reshape(-1, 3)
+    ptype = np.asarray(ptype)
+    box = np.asarray(box_length, dtype=np.float64)
+    sensed = pos[ptype == sensing_type]
+    M = len(sensed)
+    out = []
+    for i in np.nonzero(ptype == particle_type)[0]:
+        d = np.sqrt((((sensed - pos[i]) / box) ** 2).sum(axis=1))
+        nz = np.nonzero(d)[0][: max(M - 1, 0)]
+        idx = np.zeros(max(M - 1, 0), dtype=np.int64)
+        idx[: len(nz)] = nz
+        total = 0.0
+        for v in decay_eval(kind, c0, c1, d[idx]) if M > 1 else []:   # ascending-index summation, as the kernel
+            total += float(v)
+        out.append(total)
+    return np.array(out)
+
+
 def set_skin(skin):
     """Verlet skin of mode 2 (cell_system.skin, espresso.py:269)."""
     lib().orc_set_skin(float(skin))

@@ -71,6 +71,8 @@ def _make_jax():
             for i in range(n):
                 call = [a if ax is None else np.take(a, i, axis=ax) for a, ax in zip(args, axes)]
                 res.append(fn(*call))
+            if res and isinstance(res[0], tuple):   # tuple-valued functions map to a tuple of stacked arrays, as in JAX
+                return tuple(np.stack([r[k] for r in res], axis=out_axes) for k in range(len(res[0])))
             return np.stack(res, axis=out_axes)
 
         return mapped

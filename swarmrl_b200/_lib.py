@@ -111,6 +111,8 @@ SYMBOLS = {
     "swarm_gaussians": (C.c_int, [_V, C.c_int64, C.c_uint64, C.c_uint64, _V, _V]),
     "swarm_obs_field": (C.c_int, [_V, _V, _DP, _DP, _V, C.c_int32, C.c_double, C.c_double, C.c_double, C.c_int32, _V, _V, _V, _V]),
     "swarm_obs_vision": (C.c_int, [_V, _V, C.c_int64, C.c_double, C.c_double, C.c_int32, _V, _V, C.c_int32, C.c_int32, _V, _V, _V]),
+    "swarm_obs_pair_field": (C.c_int, [_V, _V, _V, C.c_int64, _DP, C.c_int32, C.c_double, C.c_double, C.c_double, C.c_int32,
+                                       C.c_int32, _V, _V, _V, _V]),
     "swarm_obs_position": (C.c_int, [_V, _V, _DP, _V, _V]),
     "swarm_reduce_mean": (C.c_int, [_V, _V, C.c_int64, _V, _V]),
     "swarm_set_actions_host": (C.c_int, [_V, _V, _V, _V]),

@@ -321,6 +321,61 @@ __global__ void k_obs_position(long long n, const double *x, const double *y, co
   out[3LL * row] = x[i] / b0; out[3LL * row + 1] = y[i] / b1; out[3LL * row + 2] = z[i] / b2;
 }
 
+// ---- pairwise field: ParticleSensing / SpeciesSearch ------------------------------------------------
+// field_i = sum of decay(|(x_j - x_i) / box|) over the first M-1 sensed particles at NON-ZERO distance, in
+// ascending index, padded with sensed[0] when fewer exist -- the reference's nonzero(size=M-1)
+// (observables/particle_sensing.py:124-131, tasks/searching/species_search.py:126-133).  All pairs, no
+// cut-off (the decay function has none): sensed positions are staged through shared memory tile by tile,
+// one thread per particle, fixed summation order.
+#define PF_TILE 256
+__global__ void __launch_bounds__(PF_TILE) k_pair_field(long long n, const double *x, const double *y, const double *z,
+                                                        const int *row_of, const int *sensed, long long M, double ib0, double ib1,
+                                                        double ib2, int decay, double c0, double c1, double scale, int clip_mode,
+                                                        int init_only, double *hist, double *out, double *field) {
+  __shared__ double sx[PF_TILE], sy[PF_TILE], sz[PF_TILE];
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int row = (i < n) ? (row_of ? row_of[i] : (int)i) : -1;
+  const bool act = row >= 0;
+  double xi = 0.0, yi = 0.0, zi = 0.0;
+  if (act) { xi = x[i]; yi = y[i]; zi = z[i]; }
+  double total = 0.0, pend = 0.0, v0 = 0.0;
+  long long nnz = 0;
+  bool have = false;
+  for (long long t0 = 0; t0 < M; t0 += PF_TILE) {
+    const long long j = t0 + threadIdx.x;
+    __syncthreads();
+    if (j < M) { const int p = sensed[j]; sx[threadIdx.x] = x[p]; sy[threadIdx.x] = y[p]; sz[threadIdx.x] = z[p]; }
+    __syncthreads();
+    if (!act) continue;
+    const int m = (int)((M - t0 < PF_TILE) ? (M - t0) : PF_TILE);
+    for (int k = 0; k < m; ++k) {
+      const double dx = (sx[k] - xi) * ib0, dy = (sy[k] - yi) * ib1, dz = (sz[k] - zi) * ib2;
+      const double d = sqrt(dx * dx + dy * dy + dz * dz);
+      if (t0 == 0 && k == 0) v0 = decay_eval(decay, c0, c1, d);
+      if (d != 0.0) {
+        if (have) total += pend;
+        pend = decay_eval(decay, c0, c1, d);
+        have = true;
+        ++nnz;
+      }
+    }
+  }
+  if (!act) return;
+  if (M <= 1) total = 0.0;
+  else {
+    if (have && nnz <= M - 1) total += pend;          // nnz == M: the last sensed particle is dropped
+    for (long long q = nnz; q < M - 1; ++q) total += v0;  // padding re-reads sensed[0]
+  }
+  const double h = hist[row];
+  hist[row] = total;
+  if (field) field[row] = total;
+  if (init_only || !out) return;
+  double v = total - h;
+  if (clip_mode > 0 && !(v > 0.0)) v = 0.0;
+  if (clip_mode < 0 && !(v < 0.0)) v = 0.0;
+  out[row] = scale * v;
+}
+
 // ---- deterministic two-stage sum -------------------------------------------------------------
 #define RED_BLOCKS 296
 __global__ void k_reduce_partial(long long n, const double *in, double *partial) {
@@ -363,6 +418,25 @@ extern "C" int swarm_obs_field(swarm_t *s, const int32_t *row_of, const double s
   k_obs_field<<<sw_blocks(A.n, 256), 256, 0, (cudaStream_t)stream>>>(A.n, A.x[0], A.y[0], A.z[0], row_of, src[0], src[1], src[2],
                                                                      box_length[0], box_length[1], box_length[2], hist, decay,
                                                                      c0, c1, scale, clip, out, d_now, d_prev);
+  s->launches += 1;
+  SW_CUDA(cudaGetLastError());
+  return SWARM_OK;
+}
+
+extern "C" int swarm_obs_pair_field(swarm_t *s, const int32_t *row_of, const int32_t *sensed_idx, int64_t n_sensed,
+                                    const double box_length[3], int32_t decay, double c0, double c1, double scale,
+                                    int32_t clip_mode, int32_t init_only, double *hist_rows, double *out, double *field,
+                                    void *stream) {
+  if (!s || !s->state_bound || !box_length || !hist_rows || n_sensed < 0 || (n_sensed > 0 && !sensed_idx)) {
+    sw_set_error("bad arguments"); return SWARM_ERR_INVALID;
+  }
+  if (decay < SWARM_DECAY_LINEAR || decay > SWARM_DECAY_INVERSE) { sw_set_error("unknown decay kind"); return SWARM_ERR_INVALID; }
+  SW_CUDA(cudaSetDevice(s->cfg.device));
+  const DevArrays &A = s->A;
+  if (A.n == 0) return SWARM_OK;
+  k_pair_field<<<sw_blocks(A.n, PF_TILE), PF_TILE, 0, (cudaStream_t)stream>>>(
+      A.n, A.x[0], A.y[0], A.z[0], row_of, sensed_idx, n_sensed, 1.0 / box_length[0], 1.0 / box_length[1], 1.0 / box_length[2],
+      decay, c0, c1, scale, clip_mode, init_only, hist_rows, out, field);
   s->launches += 1;
   SW_CUDA(cudaGetLastError());
   return SWARM_OK;

@@ -312,6 +312,22 @@ class DeviceSwarm:
             dirs.data_ptr() if dirs is not None else None, out.data_ptr(), self._stream()))
         return out[:n_rows]
 
+    def sensed_index(self, sensing_type):
+        """int32 device tensor of the particles of `sensing_type`, ascending (the reference's `test_points`)."""
+        sel = np.nonzero(self.ptype_host == int(sensing_type))[0].astype(np.int32)
+        return self.torch.from_numpy(sel).to(self.dev), len(sel)
+
+    def obs_pair_field(self, row_of, n_rows, sensed, n_sensed, box_length, hist_rows, decay, c0, c1, scale=1.0, clip_mode=0,
+                       init_only=False):
+        """ParticleSensing / SpeciesSearch field (swarm_obs_pair_field); hist_rows (n_rows,) is updated in place."""
+        out = self.torch.zeros(max(n_rows, 1), dtype=self.torch.float64, device=self.dev)
+        b3 = (C.c_double * 3)(*[float(v) for v in box_length])
+        _lib.check(self.lib.swarm_obs_pair_field(
+            self.h, row_of.data_ptr(), sensed.data_ptr() if n_sensed else None, int(n_sensed), b3, int(decay), float(c0),
+            float(c1), float(scale), int(clip_mode), int(bool(init_only)), hist_rows.data_ptr(), out.data_ptr(), None,
+            self._stream()))
+        return out[:n_rows]
+
     def obs_position(self, row_of, n_rows, box_length):
         torch = self.torch
         out = torch.zeros((max(n_rows, 1), 3), dtype=torch.float64, device=self.dev)

@@ -240,3 +240,89 @@ class SubdividedVisionCones(Observable):
     def compute_observable(self, colloids):
         out = self.compute_observable_device(colloids).cpu().numpy()
         return [out[i] for i in range(out.shape[0])]
+
+
+class _PairField:
+    """Shared body of ParticleSensing (observable) and SpeciesSearch (task): a field summed over all
+    particles of `sensing_type`, history per observer (the reference's dict keyed by str(id))."""
+
+    def _pf_init(self, decay_fn, box_length, sensing_type, scale_factor):
+        self.decay_fn = decay_fn
+        self.box_length = np.asarray(box_length, dtype=float)
+        self.sensing_type = sensing_type
+        self.scale_factor = scale_factor
+        self._hist = None
+
+    @property
+    def historical_field(self):
+        if self._hist is None:
+            return {}
+        return {str(i): float(v) for i, v in zip(self._hist_ids, self._hist.cpu().numpy())}
+
+    def _pf_call(self, colloids, clip_mode, init_only):
+        swarm, ids = resolve_swarm(colloids)
+        spec = _decay_spec(self.decay_fn)
+        if spec is None:
+            raise NotImplementedError(
+                "the all-pairs field is summed in-kernel: pass one of swarmrl_b200.decay.{Linear, Exponential, Inverse} "
+                "as decay_fn (an arbitrary Python callable would need the n x m distance matrix on the host)")
+        row_of, rows = swarm.row_map(self.particle_type)
+        sensed, m = swarm.sensed_index(self.sensing_type)
+        if self._hist is None or init_only:
+            self._hist = swarm.torch.zeros(max(rows, 1), dtype=swarm.torch.float64, device=swarm.dev)
+            sel = np.nonzero(swarm.ptype_host == int(self.particle_type))[0]
+            self._hist_ids = [int(ids[i]) for i in sel] if ids is not None else [int(i) for i in sel]
+        return swarm.obs_pair_field(row_of, rows, sensed, m, self.box_length, self._hist, spec[0], spec[1], spec[2],
+                                    scale=self.scale_factor, clip_mode=clip_mode, init_only=init_only)
+
+
+class ParticleSensing(_PairField, Observable):
+    """/root/reference/swarmrl/observables/particle_sensing.py:18-178."""
+
+    def __init__(self, decay_fn: callable, box_length: np.ndarray, sensing_type: int = 0, scale_factor: int = 100,
+                 particle_type: int = 0):
+        Observable.__init__(self, particle_type=particle_type)
+        self._pf_init(decay_fn, box_length, sensing_type, scale_factor)
+
+    def initialize(self, colloids):
+        self._pf_call(colloids, 0, True)
+
+    def compute_observable_device(self, colloids):
+        if self._hist is None:
+            raise ValueError(f"{type(self).__name__} requires initialization. Please set the "
+                             "initialize attribute of the gym to true and try again.")
+        return self._pf_call(colloids, 0, False).reshape(-1, 1)
+
+    def compute_observable(self, colloids):
+        return self.compute_observable_device(colloids).cpu().numpy()
+
+
+class MultiSensing(Observable):
+    """/root/reference/swarmrl/observables/multi_sensing.py:18-88: the observables' outputs side by side,
+    one row per colloid of the (common) particle type."""
+
+    def __init__(self, observables):
+        super().__init__(particle_type=observables[0].particle_type if observables else 0)
+        self.observables = observables
+
+    def initialize(self, colloids):
+        for item in self.observables:
+            item.initialize(colloids)
+
+    def compute_observable_device(self, colloids):
+        """(n_colloids, sum of feature sizes) device tensor: what a device policy consumes."""
+        import torch
+
+        outs = [item.compute_observable_device(colloids) for item in self.observables]
+        return torch.cat([o.reshape(o.shape[0], -1) for o in outs], dim=1)
+
+    def compute_observable(self, colloids):
+        """Object array (n_colloids, n_observables) of the per-observable arrays, as the reference returns
+        (multi_sensing.py:75-88)."""
+        per_obs = [np.asarray(item.compute_observable(colloids)) for item in self.observables]
+        n = len(per_obs[0])
+        out = np.empty((n, len(per_obs)), dtype=object)
+        for k, item in enumerate(per_obs):
+            for j in range(n):
+                out[j, k] = item[j]
+        return out

@@ -3,12 +3,14 @@ Task rewards evaluated on the device.
 
   Task              /root/reference/swarmrl/tasks/task.py:15-118
   GradientSensing   /root/reference/swarmrl/tasks/searching/gradient_sensing.py:21-150
+  SpeciesSearch     /root/reference/swarmrl/tasks/searching/species_search.py:17-184
+  MultiTasking      /root/reference/swarmrl/tasks/multi_tasking.py:15-62
 """
 from __future__ import annotations
 
 import numpy as np
 
-from .observables import _FieldHistory, _apply_decay, _decay_spec, resolve_swarm
+from .observables import _FieldHistory, _PairField, _apply_decay, _decay_spec, resolve_swarm
 
 
 class Task:
@@ -79,6 +81,51 @@ class GradientSensing(Task):
         _, dn, dp = swarm.obs_field(row_of, rows, self.source, self.box_length, self._history.hist)
         delta = _apply_decay(self.decay_fn, dn) - _apply_decay(self.decay_fn, dp)
         return (self.reward_scale_factor * delta).clamp_min(0.0)
+
+    def __call__(self, colloids):
+        return self.call_device(colloids).cpu().numpy()
+
+
+class SpeciesSearch(_PairField, Task):
+    """reward_i = scale * clip(field_i - field_i_prev) with the field summed over `sensing_type`;
+    avoid=True keeps the negative part (species_search.py:178-184)."""
+
+    def __init__(self, decay_fn: callable, box_length: np.ndarray, sensing_type: int = 0, avoid: bool = False,
+                 scale_factor: int = 100, particle_type: int = 0):
+        Task.__init__(self, particle_type=particle_type)
+        self._pf_init(decay_fn, box_length, sensing_type, scale_factor)
+        self.avoid = avoid
+
+    def initialize(self, colloids):
+        self._pf_call(colloids, 0, True)
+
+    def call_device(self, colloids):
+        if self._hist is None:
+            raise ValueError(f"{type(self).__name__} requires initialization. Please set the "
+                             "initialize attribute of the gym to true and try again.")
+        return self._pf_call(colloids, -1 if self.avoid else 1, False)
+
+    def __call__(self, colloids):
+        return self.call_device(colloids).cpu().numpy()
+
+
+class MultiTasking(Task):
+    """Sum of several tasks' rewards (multi_tasking.py:43-62)."""
+
+    def __init__(self, particle_type: int = 0, tasks=None):
+        super().__init__(particle_type)
+        self.tasks = tasks or []
+
+    def initialize(self, colloids):
+        for item in self.tasks:
+            item.initialize(colloids)
+
+    def call_device(self, colloids):
+        rewards = [item.call_device(colloids) for item in self.tasks]
+        out = rewards[0].clone()
+        for r in rewards[1:]:
+            out += r
+        return out
 
     def __call__(self, colloids):
         return self.call_device(colloids).cpu().numpy()

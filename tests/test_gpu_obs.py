@@ -170,3 +170,81 @@ def test_position_observable_and_mean_reduction():
     # deterministic: identical bits run to run
     v = torch.from_numpy(rng.normal(size=50000)).to(d.dev)
     assert np.array_equal(d.reduce_mean(v).cpu().numpy(), d.reduce_mean(v).cpu().numpy())
+
+
+PAIR_CASES = {  # name: (particle_type, sensing_type, decay, scale, clip_mode)
+    "ps_same": (0, 0, ("Exponential", 1.0, 4.0), 100.0, 0),
+    "ps_other": (0, 1, ("Inverse", 0.01, 0.05), 100.0, 0),
+    "ss_same": (1, 1, ("Exponential", 1.0, 4.0), 100.0, 1),
+    "ss_avoid": (1, 0, ("Inverse", 0.01, 0.05), 10.0, -1),
+}
+
+
+class _C:
+    def __init__(self, pos, i, t):
+        self.pos, self.director, self.id, self.type, self.velocity = pos, np.array([1.0, 0, 0]), i, int(t), np.zeros(3)
+
+
+@pytest.mark.parametrize("name", sorted(PAIR_CASES))
+def test_pair_field_golden_through_the_host_classes(golden, name):
+    """ParticleSensing / SpeciesSearch (same constructor arguments as the reference) on lists of colloids,
+    replaying the sequences the reference produced -- k_pair_field underneath."""
+    from swarmrl_b200 import decay
+    from swarmrl_b200.observables import ParticleSensing
+    from swarmrl_b200.tasks import SpeciesSearch
+
+    g = golden("pair_field.npz")
+    pt, st, (dk, c0, c1), scale, clip = PAIR_CASES[name]
+    fn = getattr(decay, dk)(c0, c1)
+    traj, types, box = g["traj"], g["types"], g["box"]
+    cols = lambda s: [_C(traj[s, i], i, types[i]) for i in range(len(types))]
+    if clip == 0:
+        ob = ParticleSensing(decay_fn=fn, box_length=box, sensing_type=st, scale_factor=scale, particle_type=pt)
+        call = lambda c: ob.compute_observable(c).reshape(-1)
+    else:
+        ob = SpeciesSearch(decay_fn=fn, box_length=box, sensing_type=st, avoid=clip < 0, scale_factor=scale, particle_type=pt)
+        call = ob
+    with pytest.raises(ValueError):
+        call(cols(1))                      # not initialised: the reference raises ValueError
+    ob.initialize(cols(0))
+    for s in range(1, traj.shape[0]):
+        assert np.allclose(call(cols(s)), g[name][s - 1], rtol=1e-9, atol=1e-10), s
+    assert len(ob.historical_field) == int(np.sum(types == pt))
+
+
+def test_pair_field_matches_oracle_at_scale_and_multi_classes():
+    """6000 particles, three types: all-pairs kernel vs the oracle; MultiSensing / MultiTasking on top."""
+    import torch
+
+    from oracle.oracle import pair_field
+    from swarmrl_b200 import decay
+    from swarmrl_b200.device_view import SwarmDeviceView
+    from swarmrl_b200.observables import MultiSensing, ParticleSensing
+    from swarmrl_b200.tasks import MultiTasking, SpeciesSearch
+
+    rng = np.random.default_rng(8)
+    n, L = 6000, 500.0
+    pos = np.zeros((n, 3)); pos[:, :2] = rng.uniform(0, L, (n, 2))
+    pos[17] = pos[4000]                                  # a coincident pair
+    types = rng.integers(0, 3, n)
+    d = _golden_swarm(pos, types)
+    box = np.array([L, L, L])
+    view = SwarmDeviceView(type("E", (), {"_backend": d, "_types": types})())   # an engine-shaped holder
+    ps = [ParticleSensing(decay.Exponential(1.0, 6.0), box, sensing_type=t, scale_factor=1.0, particle_type=0) for t in (0, 1)]
+    ms = MultiSensing(ps)
+    mt = MultiTasking(0, [SpeciesSearch(decay.Inverse(0.02, 0.1), box, sensing_type=2, scale_factor=3.0, particle_type=0),
+                          SpeciesSearch(decay.Linear(1.0, -1.0), box, sensing_type=1, avoid=True, scale_factor=2.0, particle_type=0)])
+    ms.initialize(view); mt.initialize(view)
+    f0 = [pair_field(pos, types, 0, t, box, 2, 1.0, 6.0) for t in (0, 1)]
+    g0 = [pair_field(pos, types, 0, 2, box, 3, 0.02, 0.1), pair_field(pos, types, 0, 1, box, 1, 1.0, -1.0)]
+    pos2 = pos.copy(); pos2[:, :2] += rng.normal(0, 5.0, (n, 2))
+    d.pos[:, :n] = torch.from_numpy(np.ascontiguousarray(pos2.T)).to(d.dev)
+    obs = ms.compute_observable_device(view).cpu().numpy()
+    rew = mt.call_device(view).cpu().numpy()
+    f1 = [pair_field(pos2, types, 0, t, box, 2, 1.0, 6.0) for t in (0, 1)]
+    g1 = [pair_field(pos2, types, 0, 2, box, 3, 0.02, 0.1), pair_field(pos2, types, 0, 1, box, 1, 1.0, -1.0)]
+    assert obs.shape == (int(np.sum(types == 0)), 2)
+    for k in range(2):
+        assert np.allclose(obs[:, k], f1[k] - f0[k], rtol=1e-9, atol=1e-9)
+    want = 3.0 * np.clip(g1[0] - g0[0], 0, None) + 2.0 * np.clip(g1[1] - g0[1], None, 0)
+    assert np.allclose(rew, want, rtol=1e-9, atol=1e-9)
