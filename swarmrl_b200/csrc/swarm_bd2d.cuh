@@ -369,35 +369,46 @@ __global__ void __launch_bounds__(SW_STREAM_THREADS, 3) k_bd2d_stream(const __gr
   const bool leader = (blockIdx.x == 0 && threadIdx.x == 0);
   const double lim2 = (0.5 * P.skin) * (0.5 * P.skin);
 
+  // grid barrier = the resident kernel's: one acq_rel atomic per CTA on a 64-bit word whose high half counts
+  // the CTAs that saw a particle beyond skin/2 (so the rebuild decision rides on the barrier), a separate
+  // release word to poll, no fence.sc and no per-step flag traffic.
+  __shared__ int s_need;
+  unsigned int movers_seen = 0;
+  auto step_barrier = [&](bool moved) -> bool {
+    const int any = __syncthreads_or(moved);
+    if (threadIdx.x == 0) {
+      grid_arrive64(&ctl->bar64, epoch, any != 0);
+      const unsigned int mv = (unsigned int)(grid_poll64(&ctl->bar64, epoch) >> 32);
+      s_need = (mv != movers_seen);
+      movers_seen = mv;
+    }
+    __syncthreads();
+    return s_need != 0;
+  };
   bool need = true;
   if (!R.force_rebuild) {
     bool moved = false;
     for (long long i = lo + threadIdx.x; i < hi; i += gstride) moved |= moved_since_build<2>(P, A, 0, i);
-    if (moved) ctl->rebuild_flag[0] = 1;
-    grid_barrier(&ctl->barrier, epoch);
-    need = ldcg(&ctl->rebuild_flag[0]) != 0;
+    need = step_barrier(moved);
   }
   long long s = 0;
   for (; s < R.n_steps; ++s) {
     const int cur = (int)(s & 1);
-    if (s > 0) need = ldcg(&ctl->rebuild_flag[s % 3]) != 0;
     if (need) {
       for (long long i = lo + threadIdx.x; i < hi; i += gstride) phase_clear<2>(P, A, cur, i);
-      grid_barrier(&ctl->barrier, epoch);
+      grid_barrier64(&ctl->bar64, epoch);
       for (long long i = lo + threadIdx.x; i < hi; i += gstride) phase_insert(A, i);
-      grid_barrier(&ctl->barrier, epoch);
+      grid_barrier64(&ctl->bar64, epoch);
       for (long long i = lo + threadIdx.x; i < hi; i += gstride) phase_search<2>(P, A, cur, i);
       if (leader) ctl->rebuilds += 1;
-      grid_barrier(&ctl->barrier, epoch);
+      grid_barrier64(&ctl->bar64, epoch);
       if (ldcg(&ctl->overflow)) break;
     }
     const bool last = (s == R.n_steps - 1);
     bool moved = false;
     for (long long i = lo + threadIdx.x; i < hi; i += gstride)
       moved |= bd2d_step_stream<NOISE>(P, A, S, cur, R.step0 + (u64)s, last, i, (i + gstride < hi) ? i + gstride : -1, lim2);
-    if (moved) ctl->rebuild_flag[(s + 1) % 3] = 1;
-    if (leader) ctl->rebuild_flag[(s + 2) % 3] = 0;
-    grid_barrier(&ctl->barrier, epoch);
+    need = step_barrier(moved);
   }
   if (s & 1) {
     for (long long i = lo + threadIdx.x; i < hi; i += gstride) {

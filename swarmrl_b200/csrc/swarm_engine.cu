@@ -1014,7 +1014,7 @@ static int sw_launch_stream(swarm *s, const RunArgs &R, cudaStream_t st) {
   int grid = (int)(want >= maxb ? maxb : (want > 0 ? want : 1));
   const char *env = getenv("SWARM_B200_GRID");
   if (env) { int g = atoi(env); if (g >= 1 && g <= maxb) grid = g; }
-  SW_CUDA(cudaMemsetAsync(&s->A.ctl->barrier, 0, sizeof(unsigned int), st));
+  SW_CUDA(cudaMemsetAsync(&s->A.ctl->bar64, 0, sizeof(unsigned long long) * 32, st));
   DevParams P = s->P;
   DevArrays A = s->A;
   RunArgs Rr = R;

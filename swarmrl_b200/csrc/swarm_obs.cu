@@ -14,6 +14,7 @@
 //   one thread per observer walks the 3^d neighbouring cells, each row of which is ONE contiguous
 //   range of the packed arrays.
 #include <math.h>
+#include <stdlib.h>
 
 #include "swarm_common.cuh"
 
@@ -281,6 +282,86 @@ __global__ void __launch_bounds__(128) k_vis_cones(long long n, const int *items
   for (int a = 0; a < nacc; ++a) o[a] = acc[a];
 }
 
+// One WARP per cell-ordered slot: the ~30 candidates of an observer (3 x 3 cells of edge `range`) are
+// spread over the lanes, so the acos / divisions of one observer run 32-wide instead of in one thread's
+// serial loop (the thread-per-observer kernel above was latency-bound: 128 us for 100k observers).  Each
+// lane keeps private cone sums in shared memory (conflict-free [acc][thread] layout), combined at the end
+// by a fixed shuffle tree: deterministic, though no longer in ascending particle order.
+#define VISW_THREADS 128
+#define VISW_MAX_ACC 32
+template <int GS>
+__global__ void __launch_bounds__(VISW_THREADS) k_vis_cones_warp(long long n, const int *items, const int *row_of, const VisGrid *G,
+                                                                  const int *start, const double *sx, const double *sy,
+                                                                  const double *sz, const double *sr, const int *scol, int n_dims,
+                                                                  const double *theta, const double *q0, const double *q1,
+                                                                  const double *q2, const double *q3, const double *dirs,
+                                                                  double range, double half_angle, int n_cones, int n_cols,
+                                                                  double *out) {
+  extern __shared__ double sacc[];   // [nacc][VISW_THREADS]
+  const int lane = threadIdx.x & (GS - 1);   // GS lanes share one observer
+  long long k = ((long long)blockIdx.x * blockDim.x + threadIdx.x) / GS;
+  const bool in_range = k < n;
+  if (!in_range) k = n - 1;          // no early exit: every lane takes part in the shuffles below
+  const int i = items[k];
+  const int row = in_range ? row_of[i] : -1;
+  const int nacc = n_cones * n_cols;
+  for (int a = 0; a < nacc; ++a) sacc[a * VISW_THREADS + threadIdx.x] = 0.0;
+  const double xi = sx[k], yi = sy[k], zi = sz[k];
+  double ex, ey, ez;
+  if (dirs) { ex = dirs[i]; ey = dirs[n + i]; ez = dirs[2 * n + i]; }
+  else if (n_dims == 2) { sincos(theta[i], &ey, &ex); ez = 0.0; }
+  else {
+    double a = q0[i], b = q1[i], c = q2[i], d = q3[i];
+    ex = 2 * (b * d + a * c); ey = 2 * (c * d - a * b); ez = a * a - b * b - c * c + d * d;
+  }
+  {
+    double en = sqrt(ex * ex + ey * ey + ez * ez);
+    ex /= en; ey /= en; ez /= en;
+  }
+  const double cone_w = half_angle * 2.0 / (double)n_cones;
+  const int cx = vis_coord(xi, G->lo[0], G->inv_cs, G->nc[0]);
+  const int cy = vis_coord(yi, G->lo[1], G->inv_cs, G->nc[1]);
+  const int cz = vis_coord(zi, G->lo[2], G->inv_cs, G->nc[2]);
+  const int x0 = max(cx - 1, 0), x1 = min(cx + 1, G->nc[0] - 1);
+  for (int zz = max(cz - 1, 0); zz <= min(cz + 1, G->nc[2] - 1); ++zz)
+    for (int yy = max(cy - 1, 0); yy <= min(cy + 1, G->nc[1] - 1); ++yy) {
+      const long long rowbase = ((long long)zz * G->nc[1] + yy) * G->nc[0];
+      const int b = start[rowbase + x0], e = (row >= 0) ? start[rowbase + x1 + 1] : b;
+      for (int m = b + lane; m < e; m += GS) {
+        const int col = __ldg(&scol[m]);
+        if (col < 0) continue;
+        double dx = __ldg(&sx[m]) - xi, dy = __ldg(&sy[m]) - yi, dz = __ldg(&sz[m]) - zi;
+        double d = sqrt(dx * dx + dy * dy + dz * dz);
+        if (!(d < range) || d == 0.0) continue;
+        double w = 2.0 * __ldg(&sr[m]) / d;
+        if (w > 1.0) w = 1.0;
+        double s0 = dx / d, s1 = dy / d, s2 = dz / d;
+        double sn = sqrt(s0 * s0 + s1 * s1 + s2 * s2);
+        s0 /= sn; s1 /= sn; s2 /= sn;
+        double c = s0 * ex + s1 * ey + s2 * ez;
+        c = fmin(1.0, fmax(-1.0, c));
+        double ang = acos(c);
+        double od = s0 * (-ey) + s1 * ex + s2 * ez;
+        if (!(od >= 0.0)) ang = -ang;
+        // the rims are evaluated exactly as in the serial kernel; only the candidate cone is guessed
+        int kc = (int)floor((ang + half_angle) / cone_w);
+        for (int t = kc - 1; t <= kc + 1; ++t) {
+          if (t < 0 || t >= n_cones) continue;
+          double lo = -half_angle + (double)t * half_angle * 2.0 / (double)n_cones;
+          double hi = -half_angle + (double)(t + 1) * half_angle * 2.0 / (double)n_cones;
+          if (lo < ang && hi > ang) sacc[(t * n_cols + col) * VISW_THREADS + threadIdx.x] += w;
+        }
+      }
+    }
+  __syncwarp();
+  for (int a = 0; a < nacc; ++a) {
+    double v = sacc[a * VISW_THREADS + threadIdx.x];
+#pragma unroll
+    for (int off = GS / 2; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+    if (lane == 0 && row >= 0) out[(long long)row * nacc + a] = v;
+  }
+}
+
 // ---- concentration field / gradient sensing ---------------------------------------------------
 __device__ __forceinline__ double decay_eval(int kind, double c0, double c1, double d) {
   switch (kind) {
@@ -518,8 +599,24 @@ extern "C" int swarm_obs_vision(swarm_t *s, const int32_t *row_of, int64_t rows,
   k_vis_fill<<<B, T, 0, st>>>(n, cellid, fill, items);
   k_vis_sortcell<<<sw_blocks(ncell_max, T), T, 0, st>>>(G, start, items);
   k_vis_pack<<<B, T, 0, st>>>(n, items, A.x[0], A.y[0], A.z[0], radii, A.species, s->P, type_col, n_type_col, sx, sy, sz, sr, scol);
-  k_vis_cones<<<sw_blocks(n, 128), 128, 0, st>>>(n, items, row_of, G, start, sx, sy, sz, sr, scol, s->P.n_dims, A.theta, A.q0,
-                                                 A.q1, A.q2, A.q3, dirs, vision_range, half_angle, n_cones, n_cols, out);
+  if (n_cones * n_cols <= VISW_MAX_ACC && !getenv("SWARM_B200_VIS_SERIAL")) {
+    const size_t smem = sizeof(double) * (size_t)(n_cones * n_cols) * VISW_THREADS;
+    const char *eg = getenv("SWARM_B200_VIS_GROUP");
+    const int gs = eg ? atoi(eg) : 4;   // measured at C4 (tools/bench_vision.py): 4 lanes per observer is the fastest
+#define VISW_LAUNCH(GS_)                                                                                                         \
+  k_vis_cones_warp<GS_><<<sw_blocks(n * GS_, VISW_THREADS), VISW_THREADS, smem, st>>>(                                           \
+      n, items, row_of, G, start, sx, sy, sz, sr, scol, s->P.n_dims, A.theta, A.q0, A.q1, A.q2, A.q3, dirs, vision_range,        \
+      half_angle, n_cones, n_cols, out)
+    if (gs == 32) VISW_LAUNCH(32);
+    else if (gs == 16) VISW_LAUNCH(16);
+    else if (gs == 8) VISW_LAUNCH(8);
+    else if (gs == 2) VISW_LAUNCH(2);
+    else VISW_LAUNCH(4);
+#undef VISW_LAUNCH
+  } else {
+    k_vis_cones<<<sw_blocks(n, 128), 128, 0, st>>>(n, items, row_of, G, start, sx, sy, sz, sr, scol, s->P.n_dims, A.theta, A.q0,
+                                                   A.q1, A.q2, A.q3, dirs, vision_range, half_angle, n_cones, n_cols, out);
+  }
   s->launches += 11;
   SW_CUDA(cudaGetLastError());
   return SWARM_OK;

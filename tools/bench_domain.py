@@ -31,6 +31,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=2)
     ap.add_argument("--exchange-every", dest="k", type=int, default=10, help="steps between halo exchanges")
     ap.add_argument("--skin", type=float, default=1.0)
+    ap.add_argument("--margin", type=float, default=0.25, help="halo = k * r_cut * (1 + margin)")
     ap.add_argument("--kT", type=float, default=300.0 / 293.0)
     args = ap.parse_args()
 
@@ -65,7 +66,7 @@ def main():
     pos += rng.uniform(-0.25 * (a - 2.0), 0.25 * (a - 2.0), (n, 2))
     theta = rng.uniform(0, 2 * np.pi, n)
 
-    d = DomainSwarm((L, L), 1e-3, args.kT, 42, species, wca, exchange_every=args.k, skin=args.skin, world=world, rank=rank,
+    d = DomainSwarm((L, L), 1e-3, args.kT, 42, species, wca, exchange_every=args.k, margin=args.margin, skin=args.skin, world=world, rank=rank,
                     device=local)
     d.scatter(pos, theta)
     del pos
