@@ -219,7 +219,7 @@ class DomainSwarm:
         p = self.plan
         frac = (p["slab_w"] + 2.0 * p["halo"]) / p["box_x"]
         cap = capacity or int(max(len(idx), frac * n_glob) * self.capacity_factor) + 1024
-        bcap = buffer_capacity or int(max(1.0, 2.0 * p["halo"] / p["box_x"] * n_glob) * 2.0) + 1024
+        bcap = buffer_capacity or int(max(1.0, p["halo"] / p["box_x"] * n_glob) * 1.5) + 1024   # 1.5 x the mean face population
         self._alloc(cap, bcap)
         n = len(idx)
         s = self.sets[0]
