@@ -390,6 +390,11 @@ def run_ours(args):
     if n_gpus == 1 and not args.no_cpu:
         cb = cpu_slice_rate(sample_steps=args.cpu_steps, observers=2000)
         line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        # the reference's CI runs ESPResSo single-threaded (OMP_NUM_THREADS=1, .github/workflows/espresso.yml:41)
+        cb1 = cpu_slice_rate(sample_steps=max(4, args.cpu_steps // 10), observers=250, threads=1)
+        line["cpu_baseline"]["single_thread_value"] = cb1["value"]
+        from oracle import oracle as _orc
+        _orc.set_num_threads(cb["cores"])
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
