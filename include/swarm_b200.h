@@ -262,6 +262,28 @@ int swarm_obs_position(swarm_t *s, const int32_t *row_of_dev, const double box_l
  * Deterministic two-stage reduction. */
 int swarm_reduce_mean(swarm_t *s, const double *in_dev, int64_t n, double *out2_dev, void *stream);
 
+/* ---- fused policy forward ----------------------------------------------------
+ * ActorCriticAgent.calc_action (agents/actor_critic.py:159-184) -> FlaxModel.compute_action
+ * (networks/flax_network.py:153-195) -> GumbelDistribution (sampling_strategies/gumbel_distribution.py:
+ * 19-42) -> manage_forces' writes (engine/espresso.py:1227-1235), for the network of the reference's
+ * tests (test_rl_trainers.py:17-26): Dense(hidden)+ReLU, actor Dense(n_actions), critic Dense(1).
+ * Parameters are fp32 device arrays laid out like flax Dense kernels, [in][out] row-major. */
+typedef struct {
+  int32_t obs_dim, hidden, n_actions;
+  const float *w1, *b1;   /* [obs_dim][hidden], [hidden] */
+  const float *wa, *ba;   /* [hidden][n_actions], [n_actions] */
+  const float *wv, *bv;   /* [hidden], [1] */
+} swarm_policy_t;
+
+/* obs_dev [rows][obs_dim] fp64 (what the observable kernels write); row_of as elsewhere (NULL: every
+ * particle).  sample = 1: Gumbel-max with Philox uniforms keyed (particle id, seed; call); 0: greedy.
+ * Outputs per row (each may be NULL): idx, log(softmax + 1e-8)[idx], value, logits [rows][n_actions].
+ * act_force_dev [n_actions] / act_torque_dev [n_actions][3]: when given, the chosen action is written
+ * into the bound f_swim / torque arrays of every selected particle (no host round trip). */
+int swarm_policy_forward(swarm_t *s, const swarm_policy_t *net, const double *obs_dev, const int32_t *row_of_dev, uint64_t call,
+                         int32_t sample, const double *act_force_dev, const double *act_torque_dev, int32_t *idx_out_dev,
+                         float *logp_out_dev, float *value_out_dev, float *logits_out_dev, void *stream);
+
 /* ---- host-buffer entry points (what a cgo/ctypes binding of the reference would call) --- */
 /* manage_forces: write f_swim and ext torque of every particle (espresso.py:1227-1235) */
 int swarm_set_actions_host(swarm_t *s, const double *f_swim_host, const double *torque3n_host, void *stream);

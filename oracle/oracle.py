@@ -306,6 +306,39 @@ def pair_field(pos, ptype, particle_type, sensing_type, box_length, kind, c0, c1
     return np.array(out)
 
 
+def policy_forward(obs, params, seed=0, ids=None, call=0, sample=False):
+    """fp32 restatement of the reference's action path for the network of its tests
+    (CI/espresso_tests/integration_tests/test_rl_trainers.py:17-26):
+        h = relu(obs @ w1 + b1); logits = h @ wa + ba; value = h @ wv + bv      (flax Dense: x @ kernel + bias)
+        log_prob = log(softmax(logits) + 1e-8)[idx]                             (networks/flax_network.py:180-192)
+        idx = argmax(logits - log(-log(u)))                                     (sampling_strategies/gumbel_distribution.py:37-40)
+    u comes from the engine's documented Philox layout -- counter (call, 4 + 16 * (a // 4), 0, 0), key (id, seed),
+    u = ((r >> 11) + 0.5) / 2^53 for action a = word a % 4 -- not from JAX's threefry (unavailable offline)."""
+    f = np.float32
+    x = np.asarray(obs, dtype=np.float64).astype(f)
+    w1, b1, wa, ba, wv, bv = (np.asarray(params[k], dtype=f) for k in ("w1", "b1", "wa", "ba", "wv", "bv"))
+    h = np.maximum(x @ w1 + b1, f(0))
+    logits = (h @ wa + ba).astype(f)
+    value = (h @ wv.reshape(-1, 1) + bv.reshape(1, 1)).reshape(-1).astype(f)
+    n, A = logits.shape
+    if sample:
+        ids = np.arange(n) if ids is None else np.asarray(ids)
+        pert = np.empty_like(logits)
+        for r in range(n):
+            for a0 in range(0, A, 4):
+                w = philox4x64((call, 4 + 16 * (a0 // 4), 0, 0), (int(ids[r]), int(seed)))
+                for u in range(min(4, A - a0)):
+                    uu = (float(int(w[u]) >> 11) + 0.5) / 9007199254740992.0
+                    pert[r, a0 + u] = logits[r, a0 + u] - f(np.log(-np.log(uu)))
+        idx = np.argmax(pert, axis=1)
+    else:
+        idx = np.argmax(logits, axis=1)
+    e = np.exp(logits - logits.max(axis=1, keepdims=True))
+    sm = e / e.sum(axis=1, keepdims=True)
+    logp = np.log(sm + f(1e-8))[np.arange(n), idx]
+    return idx.astype(np.int32), logp.astype(f), value, logits
+
+
 def set_skin(skin):
     """Verlet skin of mode 2 (cell_system.skin, espresso.py:269)."""
     lib().orc_set_skin(float(skin))

@@ -8,7 +8,7 @@ the C-ABI of libswarm_b200.so (include/swarm_b200.h).  There is no CPU fallback:
 """
 from . import _lib, units  # noqa: F401
 from .agents import (ActorCriticAgent, Agent, ClassicalAgent, ConstForce, ConstForceAndTorque,  # noqa: F401
-                     ConstTorque, CounterPolicy, DeviceAgent, ToConstDirection, TrajectoryInformation)
+                     ConstTorque, CounterPolicy, DeviceAgent, FusedActorCritic, ToConstDirection, TrajectoryInformation)
 from .components import Action, Colloid  # noqa: F401
 from .engine import Engine, EspressoMD, MDParams, SwarmEngine  # noqa: F401
 from .force_functions import ForceFunction  # noqa: F401

@@ -75,6 +75,10 @@ class DDArrays(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in "x y theta f_swim tqz gid species image owned".split()] + [("aux", C.c_void_p * DD_MAX_AUX)]
 
 
+class Policy(C.Structure):
+    _fields_ = [("obs_dim", C.c_int32), ("hidden", C.c_int32), ("n_actions", C.c_int32)] + [(n, C.c_void_p) for n in "w1 b1 wa ba wv bv".split()]
+
+
 # every symbol include/swarm_b200.h declares: (name, restype, argtypes)
 _V = C.c_void_p
 SYMBOLS = {
@@ -115,6 +119,7 @@ SYMBOLS = {
                                        C.c_int32, _V, _V, _V, _V]),
     "swarm_obs_position": (C.c_int, [_V, _V, _DP, _V, _V]),
     "swarm_reduce_mean": (C.c_int, [_V, _V, C.c_int64, _V, _V]),
+    "swarm_policy_forward": (C.c_int, [_V, C.POINTER(Policy), _V, _V, C.c_uint64, C.c_int32, _V, _V, _V, _V, _V, _V, _V]),
     "swarm_set_actions_host": (C.c_int, [_V, _V, _V, _V]),
     "swarm_get_particle_data_host": (C.c_int, [_V, _V, _V, _V, _V]),
 }

@@ -226,6 +226,16 @@ class DeviceAgent(Agent):
         f_tab, t_tab = self._tables(swarm)
         obs = self.observable.compute_observable_device(view)
         self.last_observable = obs
+        if hasattr(self.policy, "act"):
+            # fused path (FusedActorCritic): network, sampling and the action write in one kernel
+            row_of, rows = swarm.row_map(self.particle_type)
+            idx, logp = self.policy.act(swarm, obs.reshape(rows, -1), row_of, rows, f_tab, t_tab.reshape(-1))
+            if self.train and self.keep_trajectory:
+                self.trajectory.features.append(obs)
+                self.trajectory.actions.append(idx)
+                self.trajectory.log_probs.append(logp)
+                self.trajectory.killed = self.task.kill_switch
+            return
         out = self.policy(obs)
         idx, logp = out if isinstance(out, tuple) else (out, None)
         if self._all:
@@ -284,3 +294,44 @@ class CounterPolicy:
         x = x ^ (x >> 15)
         self.call += 1
         return x % self.k
+
+
+class FusedActorCritic:
+    """Device policy for `DeviceAgent`: the network of the reference's tests (Dense(H)+ReLU trunk, actor and critic
+    heads; test_rl_trainers.py:17-26) evaluated, sampled (Gumbel-max) and -- when the agent's action table is handed
+    over -- written into the engine's action arrays by ONE kernel (swarm_policy_forward), so a slice needs no host
+    round trip.  `params` mirrors a flax parameter tree: {"Dense_0": {"kernel", "bias"}, "Dense_1": critic,
+    "Dense_2": actor} (creation order of the reference's module) or the flat keys w1, b1, wa, ba, wv, bv."""
+
+    def __init__(self, params, swarm=None, sample=True):
+        self.host = self._flatten(params)
+        self.sample = sample
+        self.call = 0
+        self._dev = None
+        self.last_value = None
+        if swarm is not None:
+            self._upload(swarm)
+
+    @staticmethod
+    def _flatten(p):
+        if "w1" in p:
+            src = p
+        else:
+            src = {"w1": p["Dense_0"]["kernel"], "b1": p["Dense_0"]["bias"], "wv": p["Dense_1"]["kernel"], "bv": p["Dense_1"]["bias"],
+                   "wa": p["Dense_2"]["kernel"], "ba": p["Dense_2"]["bias"]}
+        out = {k: np.ascontiguousarray(np.asarray(v, dtype=np.float32)) for k, v in src.items()}
+        out["wv"] = out["wv"].reshape(-1)
+        out["bv"] = out["bv"].reshape(1)
+        return out
+
+    def _upload(self, swarm):
+        self._dev = {k: swarm.torch.from_numpy(v).to(swarm.dev) for k, v in self.host.items()}
+        self._swarm = swarm
+
+    def act(self, swarm, obs, row_of, n_rows, act_force=None, act_torque=None):
+        if self._dev is None or self._swarm is not swarm:
+            self._upload(swarm)
+        idx, logp, val = swarm.policy_forward(self._dev, obs, row_of, n_rows, self.call, self.sample, act_force, act_torque)
+        self.call += 1
+        self.last_value = val
+        return idx, logp

@@ -15,7 +15,7 @@ import sys
 PKG = pathlib.Path(__file__).resolve().parent
 CSRC = PKG / "csrc"
 LIB = PKG / "libswarm_b200.so"
-SOURCES = ["swarm_engine.cu", "swarm_obs.cu", "swarm_dd.cu"]
+SOURCES = ["swarm_engine.cu", "swarm_obs.cu", "swarm_dd.cu", "swarm_policy.cu"]
 HEADERS = [CSRC / "swarm_common.cuh", CSRC / "swarm_math.cuh", CSRC / "swarm_bd2d.cuh", PKG.parent / "include" / "swarm_b200.h"]
 
 NVCC_FLAGS = [

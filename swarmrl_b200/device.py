@@ -328,6 +328,27 @@ class DeviceSwarm:
             self._stream()))
         return out[:n_rows]
 
+    def policy_forward(self, net, obs, row_of, n_rows, call, sample=True, act_force=None, act_torque=None, want_logits=False):
+        """swarm_policy_forward: `net` is a dict of fp32 device tensors w1 [D,H], b1 [H], wa [H,A], ba [A], wv [H], bv [1].
+        Returns (idx int32, log_prob fp32, value fp32[, logits]) device tensors of n_rows; when the action tables are
+        given the chosen action is also written into f_swim / torque."""
+        torch = self.torch
+        D, H = net["w1"].shape
+        A = net["wa"].shape[1]
+        p = _lib.Policy(int(D), int(H), int(A), *[net[k].data_ptr() for k in ("w1", "b1", "wa", "ba", "wv", "bv")])
+        m = max(n_rows, 1)
+        idx = torch.zeros(m, dtype=torch.int32, device=self.dev)
+        logp = torch.zeros(m, dtype=torch.float32, device=self.dev)
+        val = torch.zeros(m, dtype=torch.float32, device=self.dev)
+        lg = torch.zeros((m, A), dtype=torch.float32, device=self.dev) if want_logits else None
+        obs = obs.contiguous()
+        _lib.check(self.lib.swarm_policy_forward(
+            self.h, C.byref(p), obs.data_ptr(), row_of.data_ptr() if row_of is not None else None, int(call), int(bool(sample)),
+            act_force.data_ptr() if act_force is not None else None, act_torque.data_ptr() if act_torque is not None else None,
+            idx.data_ptr(), logp.data_ptr(), val.data_ptr(), lg.data_ptr() if lg is not None else None, self._stream()))
+        out = (idx[:n_rows], logp[:n_rows], val[:n_rows])
+        return out + (lg[:n_rows],) if want_logits else out
+
     def obs_position(self, row_of, n_rows, box_length):
         torch = self.torch
         out = torch.zeros((max(n_rows, 1), 3), dtype=torch.float64, device=self.dev)

@@ -210,3 +210,23 @@ def test_add_colloids_rng_draw_order(tmp_path):
         d = e.get_particle_data()
         assert np.allclose(d["Unwrapped_Positions"][i], [500 + r * np.cos(th), 500 + r * np.sin(th), 0])
         assert np.allclose(d["Directors"][i], [np.cos(ph), np.sin(ph), 0], atol=1e-15)
+
+
+def test_oracle_policy_forward_definitions():
+    """The oracle's restatement of the reference's action path (flax_network.py:180-192, gumbel_distribution.py:37-40):
+    greedy = argmax(logits), log_prob = log(softmax + 1e-8)[idx], value = critic head; sampling reproducible per call."""
+    from oracle.oracle import policy_forward
+
+    rng = np.random.default_rng(2)
+    P = dict(w1=rng.normal(size=(3, 16)), b1=rng.normal(size=16), wa=rng.normal(size=(16, 4)), ba=rng.normal(size=4),
+             wv=rng.normal(size=16), bv=rng.normal(size=1))
+    obs = rng.normal(size=(50, 3))
+    idx, logp, val, lg = policy_forward(obs, P)
+    h = np.maximum(obs @ P["w1"] + P["b1"], 0)
+    assert np.allclose(lg, h @ P["wa"] + P["ba"], atol=1e-4) and np.allclose(val, h @ P["wv"] + P["bv"], atol=1e-4)
+    assert np.array_equal(idx, np.argmax(lg, axis=1))
+    sm = np.exp(lg - lg.max(1, keepdims=True)); sm /= sm.sum(1, keepdims=True)
+    assert np.allclose(logp, np.log(sm + 1e-8)[np.arange(50), idx], atol=1e-5)
+    a = policy_forward(obs, P, seed=1, call=7, sample=True)[0]
+    assert np.array_equal(a, policy_forward(obs, P, seed=1, call=7, sample=True)[0])
+    assert (a != policy_forward(obs, P, seed=1, call=8, sample=True)[0]).any()
