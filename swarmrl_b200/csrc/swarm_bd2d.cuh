@@ -421,3 +421,110 @@ __global__ void __launch_bounds__(SW_STREAM_THREADS, 3) k_bd2d_stream(const __gr
     ctl->rebuild_flag[0] = 0; ctl->rebuild_flag[1] = 0; ctl->rebuild_flag[2] = 0;
   }
 }
+
+// ---------------------------------------------------------------------------------------------
+// k_bd2d_env -- batched independent environments (BASELINE config 3): ONE WARP PER ENVIRONMENT, one agent per
+// lane (env_size <= 32).  Environments never interact, so nothing here is grid-wide: no cell list, no Verlet
+// list, no barrier of any kind.  An agent's state stays in registers for the whole chunk of steps and its
+// neighbours' positions arrive by warp shuffle -- all pairs of the environment, visited in ascending agent
+// index, which is exactly the order of the (ascending) Verlet list the other kernels and the oracle sum in;
+// pairs beyond the cut-off add nothing, so the result equals the list kernels' up to FMA contraction (1e-13).
+// ---------------------------------------------------------------------------------------------
+#define SW_ENV_THREADS 256
+// RunArgs.force_rebuild is meaningless for the list-free kernel: the launcher reuses it as "exact pairs only"
+__device__ __forceinline__ bool getenv_no_prefilter(const RunArgs &R) { return R.force_rebuild == 2; }
+template <bool NOISE>
+__global__ void __launch_bounds__(SW_ENV_THREADS) k_bd2d_env(const __grid_constant__ DevParams P, DevArrays A, RunArgs R) {
+  Ctl *ctl = A.ctl;
+  if (ldcg(&ctl->halted)) return;
+  const int lane = threadIdx.x & 31;
+  const long long env = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (env >= P.n_envs) return;   // whole warp
+  const int m = P.env_size;
+  const bool act = lane < m;
+  const long long i = env * m + (act ? lane : 0);
+  double xi = A.x[0][i], yi = A.y[0][i], th = A.theta[i];
+  const double fsw = A.f_swim[i], Tz = A.tqz[i];
+  double fxe = 0.0, fye = 0.0;
+  if (A.fex) { fxe = A.fex[i]; fye = A.fey[i]; }
+  const int sp = A.species[i], ti = P.sp_type[sp];
+  const u64 pid = sw_pid(A, i);
+  const double dt = P.dt, kT = P.kT;
+  const double gt1 = P.sp_gt[sp][1], gt2 = P.sp_gt[sp][2], gr0 = P.sp_gr[sp][0];
+  const bool iso = (gt1 == gt2);
+  const double r_gt1 = swm_rcp(gt1), r_gt2 = swm_rcp(gt2), r_gr0 = swm_rcp(gr0);
+  const double sg_par = NOISE ? sqrt(2.0 * kT * dt / gt2) : 0.0;
+  const double sg_per = NOISE ? sqrt(2.0 * kT * dt / gt1) : 0.0;
+  const double sg_rot = NOISE ? sqrt(2.0 * kT * dt / gr0) : 0.0;
+  const double w = swm_div_r(Tz, gr0, r_gr0);
+  double vx_l = 0.0, vy_l = 0.0;
+  const bool prefilter = P.periodic[0] && P.periodic[1] && !getenv_no_prefilter(R);
+  const float bxf = (float)P.box[0], byf = (float)P.box[1], ibxf = (float)P.inv_box[0], ibyf = (float)P.inv_box[1];
+  const float pr = (float)(P.max_cut + 1e-4 * (1.0 + fmax(P.box[0], P.box[1])));
+  const float pref2 = pr * pr;
+  for (long long s = 0; s < R.n_steps; ++s) {
+    double ex, ey, g0 = 0.0, g1 = 0.0, g3 = 0.0;
+    sincos(th, &ey, &ex);
+    const Bd2dSelf sf = bd2d_self_forces(P, ti, xi, yi, ex, ey, fsw);
+    if (NOISE) swm_gaussians_xyt(P.seed, pid, R.step0 + (u64)s, g0, g1, g3);
+    double Fx = 0.0, Fy = 0.0;
+    // fp32 pre-filter on wrapped coordinates: all 32 x 31 pairs are screened at full fp32 rate with one shuffle per
+    // coordinate, and the exact fp64 pair (two shuffles per coordinate, half-rate arithmetic) runs only for the
+    // partners j that some lane of the warp may actually touch (about one in ten at the densities of config 3).
+    // The screen radius exceeds the cut-off by far more than the fp32 rounding of a wrapped coordinate, so it can
+    // only admit extra pairs, never drop one.
+    float xf = 0.0f, yf = 0.0f;
+    if (prefilter) {
+      xf = (float)__dsub_rn(xi, __dmul_rn(P.box[0], rint(__dmul_rn(xi, P.inv_box[0]))));
+      yf = (float)__dsub_rn(yi, __dmul_rn(P.box[1], rint(__dmul_rn(yi, P.inv_box[1]))));
+    }
+    for (int j = 0; j < m; ++j) {
+      if (prefilter) {
+        float dxf = xf - __shfl_sync(0xffffffffu, xf, j), dyf = yf - __shfl_sync(0xffffffffu, yf, j);
+        dxf -= bxf * rintf(dxf * ibxf); dyf -= byf * rintf(dyf * ibyf);
+        const bool cand = act && j != lane && (dxf * dxf + dyf * dyf < pref2);
+        if (!__any_sync(0xffffffffu, cand)) continue;
+      }
+      const double xj = __shfl_sync(0xffffffffu, xi, j), yj = __shfl_sync(0xffffffffu, yi, j);
+      const int tj = __shfl_sync(0xffffffffu, ti, j);
+      if (j != lane) bd2d_pair(P, xi, yi, ti, tj, xj, yj, Fx, Fy);
+    }
+    Fx += sf.wx; Fy += sf.wy;
+    Fx += sf.sx; Fy += sf.sy;
+    if (A.fex) { Fx += fxe; Fy += fye; }
+    double xn, yn;
+    if (iso) {
+      vx_l = swm_div_r(Fx, gt2, r_gt2); vy_l = swm_div_r(Fy, gt2, r_gt2);
+      xn = xi + vx_l * dt; yn = yi + vy_l * dt;
+      if (NOISE) { xn += sg_par * g0; yn += sg_par * g1; }
+    } else {
+      double fpar = Fx * ex + Fy * ey, fper = -Fx * ey + Fy * ex;
+      double vpar = swm_div_r(fpar, gt2, r_gt2), vper = swm_div_r(fper, gt1, r_gt1);
+      vx_l = vpar * ex - vper * ey; vy_l = vpar * ey + vper * ex;
+      xn = xi + vx_l * dt; yn = yi + vy_l * dt;
+      if (NOISE) {
+        double spar = sg_par * g0, sper = sg_per * g1;
+        xn += spar * ex - sper * ey; yn += spar * ey + sper * ex;
+      }
+    }
+    double thn = th + w * dt;
+    if (NOISE) thn += sg_rot * g3;
+    xi = xn; yi = yn; th = thn;
+  }
+  if (act) {
+    A.x[0][i] = xi; A.y[0][i] = yi; A.theta[i] = th;
+    if (R.n_steps > 0) {
+      double gv[4] = {0, 0, 0, 0}, gw[4] = {0, 0, 0, 0};
+      double sv = 0.0, sw = 0.0;
+      if (NOISE) {
+        swm_gaussians(P.seed, pid, R.step0 + (u64)(R.n_steps - 1), 2, gv);
+        swm_gaussians(P.seed, pid, R.step0 + (u64)(R.n_steps - 1), 3, gw);
+        sv = sqrt(kT / P.sp_mass[sp]);
+        sw = sqrt(kT / P.sp_rin[sp][0]);
+      }
+      A.vx[i] = vx_l + sv * gv[0]; A.vy[i] = vy_l + sv * gv[1]; A.vz[i] = 0.0;
+      A.wx[i] = 0.0; A.wy[i] = 0.0; A.wz[i] = w + sw * gw[0];
+    }
+  }
+  if (env == 0 && lane == 0) ctl->steps_done = R.n_steps;
+}

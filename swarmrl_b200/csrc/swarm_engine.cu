@@ -1001,6 +1001,19 @@ static int sw_launch_resident(swarm *s, const RunArgs &R, cudaStream_t st, bool 
   return SWARM_OK;
 }
 
+// batched environments of <= 32 agents: one warp per environment, no lists, no barrier, plain launch
+template <bool NOISE>
+static int sw_launch_env(swarm *s, const RunArgs &R, cudaStream_t st) {
+  const long long warps_per_block = SW_ENV_THREADS / 32;
+  const long long blocks = (s->P.n_envs + warps_per_block - 1) / warps_per_block;
+  RunArgs Rr = R;
+  Rr.force_rebuild = getenv("SWARM_B200_ENV_EXACT_PAIRS") ? 2 : 0;   // 2 = skip the fp32 pre-filter (cross-check)
+  k_bd2d_env<NOISE><<<(unsigned)blocks, SW_ENV_THREADS, 0, st>>>(s->P, s->A, Rr);
+  s->launches += 1;
+  SW_CUDA(cudaGetLastError());
+  return SWARM_OK;
+}
+
 // large 2-D swarms: lean grid-stride chunk kernel, every CTA co-resident (3 per SM)
 template <bool NOISE>
 static int sw_launch_stream(swarm *s, const RunArgs &R, cudaStream_t st) {
@@ -1065,6 +1078,13 @@ static int sw_run_common(swarm *s, RunArgs R, cudaStream_t st) {
     // only the last sub-launch of a chunk materialises v / omega on its final step: handled by
     // Rc.n_steps bookkeeping -- earlier sub-launches also write them, harmlessly.
     bool done_resident = false;
+    if (s->persistent && s->P.n_dims == 2 && R.mode == MODE_BD && s->P.n_envs > 1 && s->P.env_size <= 32 && !s->A.n_dev &&
+        !getenv("SWARM_B200_NO_ENV_KERNEL")) {
+      rc = noise ? sw_launch_env<true>(s, Rc, st) : sw_launch_env<false>(s, Rc, st);
+      if (rc) return rc;
+      done += Rc.n_steps;
+      continue;
+    }
     if (s->persistent && s->P.n_dims == 2 && R.mode == MODE_BD && !getenv("SWARM_B200_NO_RESIDENT")) {
       rc = noise ? sw_launch_resident<true>(s, Rc, st, &done_resident) : sw_launch_resident<false>(s, Rc, st, &done_resident);
       if (rc) return rc;

@@ -300,3 +300,44 @@ def test_ensemble_shards_reproduce_the_whole_ensemble_with_noise():
         part = run(lo, hi)
         for a, b in zip(part, whole):
             assert np.array_equal(a, b[lo * m:hi * m])
+
+
+def test_warp_per_environment_kernel_equals_the_list_kernels(monkeypatch):
+    """k_bd2d_env (one warp per environment, all pairs by shuffle in ascending index, no lists) against the
+    Verlet-list kernels on the same batched ensemble: same trajectories to 1e-12 (FMA contraction differs between
+    the kernels), noise on, ragged environment size (29 < 32), two particle types; and the fp32 pre-filter of the
+    pair loop changes NOTHING (bitwise) against the exact all-pairs loop."""
+    import torch
+
+    from swarmrl_b200.device import DeviceSwarm
+
+    E, m, L = 64, 29, 60.0
+    rng = np.random.default_rng(5)
+    sp, wca = species_for([1.0, 1.5]), wca_for([1.0, 1.5])
+    pos = np.concatenate([jittered_lattice(m, L, 2, rng, jitter=0.15) for _ in range(E)])
+    th = rng.uniform(0, 2 * np.pi, E * m)
+    sidx = rng.integers(0, 2, E * m).astype(np.int32)
+    f = rng.uniform(0, 30.0, E * m) * sp[0]["gamma_t"][0]
+    tq = np.zeros((E * m, 3)); tq[:, 2] = rng.uniform(-1, 1, E * m) * sp[0]["gamma_r"][0]
+
+    def run(env_kernel, exact_pairs=False):
+        monkeypatch.delenv("SWARM_B200_ENV_EXACT_PAIRS", raising=False)
+        if exact_pairs:
+            monkeypatch.setenv("SWARM_B200_ENV_EXACT_PAIRS", "1")
+        if env_kernel:
+            monkeypatch.delenv("SWARM_B200_NO_ENV_KERNEL", raising=False)
+        else:
+            monkeypatch.setenv("SWARM_B200_NO_ENV_KERNEL", "1")
+        d = DeviceSwarm(2, (L,) * 3, True, 1e-3, KT_300, 7, sp, wca, n_envs=E, skin=1.0)
+        d.set_state(pos, sidx, theta=th)
+        d.set_actions_host(f, tq)
+        st0 = d.run_checked(150, 0)
+        st1 = d.run_checked(50, 150)
+        assert st1.steps_done == 50
+        return d.particle_data_host() + (int(st1.rebuilds),)
+
+    a, b, c = run(True), run(False), run(True, exact_pairs=True)
+    assert a[3] == 0 and b[3] > 0          # the environment kernel never builds a neighbour list
+    for u, v, w in zip(a[:3], b[:3], c[:3]):
+        assert rel_err(u, v) < 1e-12
+        assert np.array_equal(u, w)
