@@ -319,6 +319,13 @@ __global__ void __launch_bounds__(VISW_THREADS) k_vis_cones_warp(long long n, co
     ex /= en; ey /= en; ez /= en;
   }
   const double cone_w = half_angle * 2.0 / (double)n_cones;
+  // rims and their cosines, once per CTA (the rim expression is the serial kernel's, bit for bit)
+  __shared__ double rim[VIS_MAX_ACC + 1], crim[VIS_MAX_ACC + 1];
+  for (int t = threadIdx.x; t <= n_cones; t += blockDim.x) {
+    rim[t] = -half_angle + (double)t * half_angle * 2.0 / (double)n_cones;
+    crim[t] = cos(rim[t]);
+  }
+  __syncthreads();
   const int cx = vis_coord(xi, G->lo[0], G->inv_cs, G->nc[0]);
   const int cy = vis_coord(yi, G->lo[1], G->inv_cs, G->nc[1]);
   const int cz = vis_coord(zi, G->lo[2], G->inv_cs, G->nc[2]);
@@ -335,6 +342,29 @@ __global__ void __launch_bounds__(VISW_THREADS) k_vis_cones_warp(long long n, co
         if (!(d < range) || d == 0.0) continue;
         double w = 2.0 * __ldg(&sr[m]) / d;
         if (w > 1.0) w = 1.0;
+        {
+          // fast cone decision: compare cos(angle) with the cosines of the rims instead of taking acos and
+          // normalising the separation twice.  Whenever the cosine lies within 1e-9 of a rim's (or the side
+          // test within 1e-9 of zero) the exact sequence below decides, so the chosen cone is always the one the
+          // serial kernel / the oracle choose; everywhere else the margin exceeds the rounding by six decades.
+          const double inv_d = 1.0 / d;
+          const double cf = (dx * ex + dy * ey + dz * ez) * inv_d;
+          const double of = (dx * (-ey) + dy * ex + dz * ez) * inv_d;
+          bool near = fabs(of) < 1e-9;
+          int tf = -1;
+          for (int t = 0; t < n_cones; ++t) {
+            const double r0 = rim[t], r1 = rim[t + 1], c0 = crim[t], c1 = crim[t + 1];
+            near = near || fabs(cf - c0) < 1e-9 || fabs(cf - c1) < 1e-9;
+            bool in;
+            if (of >= 0.0) in = (r0 < 0.0 || cf < c0) && (r1 > 0.0 && cf > c1);      // r0 < acos(c) < r1
+            else in = (r0 < 0.0 && cf > c0) && (r1 > 0.0 || cf < c1);               // r0 < -acos(c) < r1
+            if (in) tf = t;
+          }
+          if (!near) {
+            if (tf >= 0) sacc[(tf * n_cols + col) * VISW_THREADS + threadIdx.x] += w;
+            continue;
+          }
+        }
         double s0 = dx / d, s1 = dy / d, s2 = dz / d;
         double sn = sqrt(s0 * s0 + s1 * s1 + s2 * s2);
         s0 /= sn; s1 /= sn; s2 /= sn;
