@@ -47,7 +47,7 @@ VISION = dict(range=10.0, half_angle=np.pi / 2, n_cones=5)
 BYTES_PER_AGENT_STEP = 68  # 2-D steady-state step, read 44 B + write 24 B
 # dram__bytes_read.sum + dram__bytes_write.sum of one k_bd2d_resident launch (100 steps), from the ncu --set full
 # capture profiles/r01_k_bd2d_resident.ncu-rep (10.70 MB + 0.12 MB): the state is register / L2 resident
-NCU_DRAM_BYTES_PER_LAUNCH = 10.82e6
+NCU_DRAM_BYTES_PER_LAUNCH = 10.89e6  # dram__bytes_read + write of one k_bd2d_resident launch, profiles/r01_ncu_k_bd2d_resident_summary.txt
 METRIC = "agent_steps_per_sec_100k_agents"
 UNIT = "agent-steps/s"
 
@@ -111,7 +111,34 @@ class ClockSampler(threading.Thread):
         except Exception:
             return None
 
+    def _run_nvml(self):
+        """NVML in-process: a sample every 2 ms, so even a 15 ms timed region is covered (nvidia-smi takes ~30 ms
+        per query).  Returns False when NVML is unusable and the nvidia-smi loop should run instead."""
+        try:
+            import pynvml as nv
+
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+        except Exception:
+            return False
+        bits = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40,
+                "hw_power_brake_slowdown": 0x80}
+        while not self._halt.is_set():
+            try:
+                self.samples.append(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
+                r = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(h))
+                for nme, b in bits.items():
+                    if r & b:
+                        self.reasons.add(nme)
+            except Exception:
+                pass
+            self._halt.wait(0.002)
+        return True
+
     def run(self):
+        if self._run_nvml():
+            return
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap", "hw_power_brake_slowdown"]
         q = "clocks.sm,clocks.max.sm," + ",".join("clocks_throttle_reasons." + n for n in names)
         while not self._halt.is_set():
@@ -145,8 +172,14 @@ def cpu_slice_rate(sample_steps=40, observers=2000, threads=None):
     from oracle import oracle
     from oracle.oracle import OracleSwarm
 
-    if threads:
-        oracle.set_num_threads(threads)
+    # all host threads unless told otherwise: torchrun exports OMP_NUM_THREADS=1 to its workers, which would
+    # silently turn the "all cores" baseline into a single-threaded one
+    if not threads:
+        try:
+            threads = len(os.sched_getaffinity(0))
+        except AttributeError:
+            threads = os.cpu_count() or 1
+    oracle.set_num_threads(threads)
     cores = oracle.num_threads()
     n = N_AGENTS
     pos, th = initial_state(n, BOX, SEED)
@@ -403,7 +436,7 @@ def run_ours(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--skin", type=float, default=2.0, help="Verlet skin (performance only; espresso.py:269 uses 0.4)")

@@ -506,11 +506,16 @@ __global__ void k_reduce_partial(long long n, const double *in, double *partial)
   }
 }
 __global__ void k_reduce_final(long long n, const double *partial, double *out2) {
-  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  // one warp, fixed order: lane l adds partial[l], partial[l + 32], ... then a fixed shuffle tree (deterministic;
+  // the former single-thread loop over 296 dependent DADDs took 10 us)
+  if (blockIdx.x != 0 || threadIdx.x >= 32) return;
   double t = 0.0;
-  for (int k = 0; k < RED_BLOCKS; ++k) t += partial[k];
-  out2[0] = t;
-  out2[1] = (n > 0) ? t / (double)n : 0.0;
+  for (int k = threadIdx.x; k < RED_BLOCKS; k += 32) t += partial[k];
+  for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+  if (threadIdx.x == 0) {
+    out2[0] = t;
+    out2[1] = (n > 0) ? t / (double)n : 0.0;
+  }
 }
 
 // ---------------------------------------------------------------------------------------------
