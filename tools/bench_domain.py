@@ -32,6 +32,7 @@ def main():
     ap.add_argument("--exchange-every", dest="k", type=int, default=10, help="steps between halo exchanges")
     ap.add_argument("--skin", type=float, default=1.0)
     ap.add_argument("--margin", type=float, default=0.25, help="halo = k * r_cut * (1 + margin)")
+    ap.add_argument("--capacity-factor", type=float, default=1.3, help="local array capacity / expected local particles")
     ap.add_argument("--kT", type=float, default=300.0 / 293.0)
     args = ap.parse_args()
 
@@ -67,7 +68,7 @@ def main():
     theta = rng.uniform(0, 2 * np.pi, n)
 
     d = DomainSwarm((L, L), 1e-3, args.kT, 42, species, wca, exchange_every=args.k, margin=args.margin, skin=args.skin, world=world, rank=rank,
-                    device=local)
+                    device=local, capacity_factor=args.capacity_factor)
     d.scatter(pos, theta)
     del pos
     f_glob = torch.from_numpy(rng.uniform(0.0, 10.0 * gt, n)).to(d.dev)
