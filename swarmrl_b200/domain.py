@@ -16,7 +16,6 @@ send/recv pairs over NVLink (torch.distributed) -> k_dd_merge -> re-bind.  No pe
 from __future__ import annotations
 
 import ctypes as C
-import math
 
 import numpy as np
 

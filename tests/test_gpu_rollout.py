@@ -85,3 +85,47 @@ def test_fused_policy_drives_a_rollout(tmp_path):
     # the last action written by the kernel is what the engine holds
     f = e._backend.f_swim[:10].cpu().numpy()
     assert np.array_equal(f != 0.0, acts[-1] == 0)
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_chemotaxis_reward_curve_device_engine_vs_oracle_engine(tmp_path, seed):
+    """north_star's third parity check (reward curves with noise ON): the same rollout driven once by the CUDA engine and
+    once by the CPU oracle behind the same SwarmEngine host code (tests/oracle_backend.py), same counter policy, same
+    thermostat seed.  Because both draw the same Philox noise the curves must agree far inside 2 sigma: to 1e-7."""
+    from oracle_backend import OracleBackend
+
+    class CpuEngine(sw.SwarmEngine):
+        backend_factory = staticmethod(lambda **kw: OracleBackend(**kw))
+
+    class ListPath(ObjectPathOnly):
+        """hands the agents plain lists of Colloid, as the reference does, so that observable and task kernels run on
+        a scratch copy whichever backend integrates (the oracle backend has no device arrays to view)"""
+
+        def calc_reward(self, colloids, external_reward=0.0):
+            return super().calc_reward(colloids.as_colloids() if hasattr(colloids, "as_colloids") else colloids, external_reward)
+
+    def rollout(cls, sub):
+        ureg = UnitRegistry()
+        dt = ureg.Quantity(0.1, "second")
+        md = sw.MDParams(ureg=ureg, fluid_dyn_viscosity=ureg.Quantity(8.9e-4, "pascal * second"),
+                         WCA_epsilon=ureg.Quantity(297.0, "kelvin") * ureg.boltzmann_constant,
+                         temperature=ureg.Quantity(300.0, "kelvin"), box_length=ureg.Quantity(3 * [1000.0], "micrometer"),
+                         time_step=dt, time_slice=dt * 10, write_interval=dt * 10)
+        e = cls(md_params=md, n_dims=2, seed=seed, out_folder=tmp_path / sub, write_chunk_size=100)
+        e.add_colloids(10, ureg.Quantity(2.14, "micrometer"), ureg.Quantity(np.array([500.0, 500.0, 0.0]), "micrometer"),
+                       ureg.Quantity(400.0, "micrometer"), type_colloid=0)
+        agent = _agent(sw.CounterPolicy(4, seed=7))
+        ff = ListPath({"0": agent})
+        agent.reset_agent(e.colloids.as_colloids())
+        for _ in range(3):                       # 3 episodes x 5 slices, as the reference's trainer test loops
+            e.integrate(5, ff)
+        e.finalize()
+        r = np.array([np.asarray(x.cpu() if hasattr(x, "cpu") else x) for x in agent.trajectory.rewards])
+        return r, e.get_particle_data()["Unwrapped_Positions"]
+
+    r_dev, p_dev = rollout(sw.SwarmEngine, "dev")
+    r_cpu, p_cpu = rollout(CpuEngine, "cpu")
+    assert r_dev.shape == r_cpu.shape == (15, 10)
+    assert np.allclose(p_dev, p_cpu, rtol=1e-9, atol=1e-9)
+    assert np.allclose(r_dev, r_cpu, rtol=1e-7, atol=1e-7)
+    assert r_dev.sum() > 0
