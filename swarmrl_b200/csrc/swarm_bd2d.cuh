@@ -369,8 +369,11 @@ __device__ __forceinline__ bool bd2d_step_stream(const DevParams &P, const DevAr
 }
 
 #define SW_STREAM_THREADS 256
+#ifndef SW_STREAM_MINB
+#define SW_STREAM_MINB 3
+#endif
 template <bool NOISE>
-__global__ void __launch_bounds__(SW_STREAM_THREADS, 3) k_bd2d_stream(const __grid_constant__ DevParams P, DevArrays A, RunArgs R) {
+__global__ void __launch_bounds__(SW_STREAM_THREADS, SW_STREAM_MINB) k_bd2d_stream(const __grid_constant__ DevParams P, DevArrays A, RunArgs R) {
   Ctl *ctl = A.ctl;
   if (ldcg(&ctl->halted)) return;
   __shared__ Bd2dSpecies S[SW_S];
