@@ -90,6 +90,7 @@ struct swarm {
   swarm_actions_dev_t act{};
   swarm_state_dev_t st{};
   bool list_valid = false;
+  bool cells_dirty = false;  // scratch reused for new particles: linked cells reset on the next launch's stream
   long long launches = 0;
   long long steps_requested = 0;
   int num_sms = 0;

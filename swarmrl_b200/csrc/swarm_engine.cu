@@ -848,10 +848,9 @@ extern "C" int swarm_bind_state(swarm_t *s, int64_t n, const swarm_state_dev_t *
     A.head = nullptr;
     s->ncell_alloc = 0;
   } else {
-    // same scratch, different particles: the linked cells of the previous occupants are stale
-    SW_CUDA(cudaMemsetAsync(A.next, 0xFF, sizeof(int) * (size_t)A.n_pad, 0));
-    SW_CUDA(cudaMemsetAsync(A.cellof, 0, sizeof(int) * (size_t)A.n_pad, 0));
-    if (A.head) SW_CUDA(cudaMemsetAsync(A.head, 0xFF, sizeof(int) * (size_t)s->ncell_alloc, 0));
+    // same scratch, different particles: the linked cells of the previous occupants are stale; they are reset
+    // by the next launch, on that launch's stream (sw_prepare), so the order holds on non-blocking streams too
+    s->cells_dirty = true;
   }
   // default actions: zeros
   A.f_swim = s->zeros; A.tqx = s->zeros; A.tqy = s->zeros; A.tqz = s->zeros;
@@ -916,7 +915,7 @@ extern "C" int swarm_set_max_neighbors(swarm_t *s, int32_t cap) {
   return SWARM_OK;
 }
 
-static int sw_prepare(swarm *s) {
+static int sw_prepare(swarm *s, cudaStream_t st) {
   if (!s->state_bound) { sw_set_error("no state bound"); return SWARM_ERR_STATE; }
   if (!s->species_set || !s->wca_set) { sw_set_error("species / WCA tables not set"); return SWARM_ERR_STATE; }
   SW_CUDA(cudaSetDevice(s->cfg.device));
@@ -936,9 +935,16 @@ static int sw_prepare(swarm *s) {
       s->A.head = h;
       s->ncell_alloc = ncell;
     }
-    SW_CUDA(cudaMemset(s->A.head, 0xFF, sizeof(int) * (size_t)s->ncell_alloc));
-    SW_CUDA(cudaMemset(s->A.cellof, 0, sizeof(int) * (size_t)s->A.n_pad));
+    SW_CUDA(cudaMemsetAsync(s->A.head, 0xFF, sizeof(int) * (size_t)s->ncell_alloc, st));
+    SW_CUDA(cudaMemsetAsync(s->A.cellof, 0, sizeof(int) * (size_t)s->A.n_pad, st));
     s->list_valid = false;
+  } else if (s->cells_dirty) {
+    SW_CUDA(cudaMemsetAsync(s->A.head, 0xFF, sizeof(int) * (size_t)s->ncell_alloc, st));
+    SW_CUDA(cudaMemsetAsync(s->A.cellof, 0, sizeof(int) * (size_t)s->A.n_pad, st));
+  }
+  if (s->cells_dirty) {
+    SW_CUDA(cudaMemsetAsync(s->A.next, 0xFF, sizeof(int) * (size_t)s->A.n_pad, st));
+    s->cells_dirty = false;
   }
   return SWARM_OK;
 }
@@ -1057,7 +1063,7 @@ static int sw_launch_np(swarm *s, const RunArgs &R, cudaStream_t st) {
 }
 
 static int sw_run_common(swarm *s, RunArgs R, cudaStream_t st) {
-  int rc = sw_prepare(s);
+  int rc = sw_prepare(s, st);
   if (rc) return rc;
   if (R.n_steps < 0) { sw_set_error("n_steps must be >= 0"); return SWARM_ERR_INVALID; }
   s->steps_requested = R.n_steps;
@@ -1175,7 +1181,7 @@ extern "C" int swarm_directors(swarm_t *s, double *ex, double *ey, double *ez, v
 
 // rebuild the Verlet list at the current positions (0-step run with a forced rebuild)
 static int sw_force_rebuild(swarm *s, cudaStream_t st) {
-  int rc = sw_prepare(s);
+  int rc = sw_prepare(s, st);
   if (rc) return rc;
   if (s->A.n == 0) return SWARM_OK;
   const int T = SW_THREADS, B = sw_blocks(s->A.n, T);
