@@ -119,6 +119,15 @@ int swarm_set_walls(swarm_t *s, int32_t enabled, const double *sigma, const doub
 /* thermostat.set_brownian(kT, seed) (espresso.py:1180-1186) -- may be changed between runs */
 int swarm_set_thermostat(swarm_t *s, double kT, uint64_t seed);
 
+/* MDParams.thermostat_type (espresso.py:62, 1173-1201): "brownian" = thermostat.set_brownian +
+ * integrator.set_brownian_dynamics (the default, :1179-1186); "langevin" = thermostat.set_langevin +
+ * integrator.set_vv (:1187-1201, without a lattice-Boltzmann fluid).  Under LANGEVIN swarm_run advances
+ * velocity Verlet steps: v and omega of the bound state are INPUTS as well as outputs, every species
+ * needs mass > 0 and rinertia > 0 (espresso.py:391-400; isotropic rinertia in 3-D), every run starts
+ * with a force recalculation at the current (x, v) as ESPResSo does after particle properties change. */
+typedef enum { SWARM_INTEGRATOR_BROWNIAN = 0, SWARM_INTEGRATOR_LANGEVIN = 1 } swarm_integrator_t;
+int swarm_set_integrator(swarm_t *s, int32_t kind);
+
 /* Bind caller-owned device arrays (no copy).  n must be a multiple of n_envs. */
 int swarm_bind_state(swarm_t *s, int64_t n, const swarm_state_dev_t *st);
 int swarm_bind_actions(swarm_t *s, const swarm_actions_dev_t *act);

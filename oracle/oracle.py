@@ -78,6 +78,7 @@ def lib():
         L.orc_gaussians.argtypes = [C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, _DP]
         L.orc_forces.argtypes = [C.POINTER(Params), C.POINTER(State), C.c_int, C.c_int, _DP, _DP, _DP]
         L.orc_bd_steps.argtypes = [C.POINTER(Params), C.POINTER(State), C.c_uint64, C.c_int64, C.c_int]
+        L.orc_lv_steps.argtypes = [C.POINTER(Params), C.POINTER(State), C.c_uint64, C.c_int64, C.c_int]
         L.orc_sd_steps.argtypes = [C.POINTER(Params), C.POINTER(State), C.c_int64, C.c_double, C.c_double, C.c_int]
         L.orc_pairs_within.argtypes = [C.POINTER(Params), C.POINTER(State), C.c_double, _IP, C.c_int64]
         L.orc_pairs_within.restype = C.c_int64
@@ -224,6 +225,10 @@ class OracleSwarm:
 
     def bd_steps(self, step0, nsteps, mode=0):
         lib().orc_bd_steps(C.byref(self.params), C.byref(self.state), int(step0), int(nsteps), mode)
+
+    def lv_steps(self, step0, nsteps, mode=0):
+        """Langevin thermostat + velocity Verlet (espresso.py:1187-1201); v and omega are state here."""
+        lib().orc_lv_steps(C.byref(self.params), C.byref(self.state), int(step0), int(nsteps), mode)
 
     def sd_steps(self, nsteps, gamma=0.1, max_disp=0.1, mode=0):
         lib().orc_sd_steps(C.byref(self.params), C.byref(self.state), int(nsteps), gamma, max_disp, mode)

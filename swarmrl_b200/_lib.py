@@ -20,6 +20,7 @@ MAX_TYPES = 8
 
 OK, ERR_INVALID, ERR_STATE, ERR_CUDA, ERR_OVERFLOW, ERR_NOMEM = 0, -1, -2, -3, -4, -5
 DECAY_NONE, DECAY_LINEAR, DECAY_EXP, DECAY_INVERSE = 0, 1, 2, 3
+INTEGRATOR_BROWNIAN, INTEGRATOR_LANGEVIN = 0, 1
 FLAG_NO_PERSISTENT = 1
 
 _DP = C.POINTER(C.c_double)
@@ -90,6 +91,7 @@ SYMBOLS = {
     "swarm_set_wca": (C.c_int, [_V, C.c_int32, _DP, _DP, _DP]),
     "swarm_set_walls": (C.c_int, [_V, C.c_int32, _DP, _DP, _DP]),
     "swarm_set_thermostat": (C.c_int, [_V, C.c_double, C.c_uint64]),
+    "swarm_set_integrator": (C.c_int, [_V, C.c_int32]),
     "swarm_bind_state": (C.c_int, [_V, C.c_int64, C.POINTER(StateDev)]),
     "swarm_bind_actions": (C.c_int, [_V, C.POINTER(ActionsDev)]),
     "swarm_reserve": (C.c_int, [_V, C.c_int64]),

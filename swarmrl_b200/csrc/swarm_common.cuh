@@ -90,6 +90,10 @@ struct swarm {
   swarm_actions_dev_t act{};
   swarm_state_dev_t st{};
   bool list_valid = false;
+  int integrator = 0;        // swarm_integrator_t
+  int last_mode = 0;         // mode of the last run (steps_done bookkeeping)
+  bool lv_resume = false;    // next Langevin run continues an interrupted chunk
+  bool lv_was_resume = false;
   bool cells_dirty = false;  // scratch reused for new particles: linked cells reset on the next launch's stream
   long long launches = 0;
   long long steps_requested = 0;

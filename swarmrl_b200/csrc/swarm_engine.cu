@@ -30,7 +30,7 @@
 #define SW_TYPE_SHIFT 28
 #define SW_THREADS 256
 
-enum { MODE_BD = 0, MODE_SD = 1 };
+enum { MODE_BD = 0, MODE_SD = 1, MODE_LV = 2 };
 
 struct RunArgs {
   long long n_steps;
@@ -39,6 +39,9 @@ struct RunArgs {
   int force_rebuild;
   double sd_gamma, sd_maxd;
   int particles_per_cta;  // resident kernel only
+  // MODE_LV (velocity Verlet): iteration 0 of the launch is the force recalculation at the start of a chunk
+  // (no closing half kick); the last iteration only closes the final step (no drift)
+  int lv_first, lv_close;
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -242,6 +245,43 @@ __device__ __forceinline__ bool phase_step(const DevParams &P, const DevArrays &
       yn = yi + clampd(R.sd_gamma * F[1], -R.sd_maxd, R.sd_maxd);
       double l = fabs(R.sd_gamma * Tz);
       if (l > 0.0) A.theta[i] = th + (Tz > 0 ? 1.0 : -1.0) * clampd(l, -R.sd_maxd, R.sd_maxd);
+    } else if (R.mode == MODE_LV) {
+      // Langevin thermostat + velocity Verlet (oracle: orc_lv_steps): this force evaluation closes the previous
+      // step (second half kick) and opens the next one (first half kick + drift)
+      const double gt1 = P.sp_gt[sp][1], gt2 = P.sp_gt[sp][2], gr0 = P.sp_gr[sp][0];
+      const double m = P.sp_mass[sp], hk = 0.5 * dt;
+      double u[4] = {0.0, 0.0, 0.0, 0.0};
+      if (NOISE) swm_uniforms(P.seed, pid, step, 4, u);
+      double vx = A.vx[i], vy = A.vy[i], w = A.wz[i];
+      double fx = F[0], fy = F[1];
+      if (gt1 == gt2) {
+        fx -= gt2 * vx; fy -= gt2 * vy;
+        if (NOISE) {
+          double pref = sqrt(24.0 * kT * gt2 / dt);
+          fx += pref * u[0]; fy += pref * u[1];
+        }
+      } else {
+        double vpar = vx * e[0] + vy * e[1], vper = -vx * e[1] + vy * e[0];
+        double fpar = -(gt2 * vpar), fper = -(gt1 * vper);
+        if (NOISE) {
+          fpar += sqrt(24.0 * kT * gt2 / dt) * u[0];
+          fper += sqrt(24.0 * kT * gt1 / dt) * u[1];
+        }
+        fx += fpar * e[0] - fper * e[1]; fy += fpar * e[1] + fper * e[0];
+      }
+      double tq = Tz - gr0 * w;
+      if (NOISE) tq += sqrt(24.0 * kT * gr0 / dt) * u[3];
+      const double ax = fx / m, ay = fy / m, al = tq / P.sp_rin[sp][0];
+      const bool first = R.lv_first && step == R.step0, close = R.lv_close && last;
+      if (!first) { vx += hk * ax; vy += hk * ay; w += hk * al; }
+      xn = xi; yn = yi;
+      if (!close) {
+        vx += hk * ax; vy += hk * ay; w += hk * al;
+        xn = xi + dt * vx; yn = yi + dt * vy;
+        A.theta[i] = th + dt * w;
+      }
+      A.vx[i] = vx; A.vy[i] = vy; A.vz[i] = 0.0;
+      A.wx[i] = 0.0; A.wy[i] = 0.0; A.wz[i] = w;
     } else {
       const double gt1 = P.sp_gt[sp][1], gt2 = P.sp_gt[sp][2], gr0 = P.sp_gr[sp][0];
       double g[4] = {0.0, 0.0, 0.0, 0.0};
@@ -300,6 +340,63 @@ __device__ __forceinline__ bool phase_step(const DevParams &P, const DevArrays &
         sw_quat_rotate_body(q, ax, clampd(l, -R.sd_maxd, R.sd_maxd));
         A.q0[i] = q[0]; A.q1[i] = q[1]; A.q2[i] = q[2]; A.q3[i] = q[3];
       }
+    } else if (R.mode == MODE_LV) {
+      const double *gt = P.sp_gt[sp], *gr = P.sp_gr[sp];
+      const double m = P.sp_mass[sp], hk = 0.5 * dt;
+      double u[4] = {0.0, 0.0, 0.0, 0.0}, ur[4] = {0.0, 0.0, 0.0, 0.0};
+      if (NOISE) { swm_uniforms(P.seed, pid, step, 4, u); swm_uniforms(P.seed, pid, step, 5, ur); }
+      double v[3] = {A.vx[i], A.vy[i], A.vz[i]};
+      const double wl[3] = {A.wx[i], A.wy[i], A.wz[i]};
+      if (gt[0] == gt[1] && gt[1] == gt[2]) {
+        const double pref = NOISE ? sqrt(24.0 * kT * gt[0] / dt) : 0.0;
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+          F[a] -= gt[0] * v[a];
+          if (NOISE) F[a] += pref * u[a];
+        }
+      } else {
+        double fb[3];
+#pragma unroll
+        for (int b = 0; b < 3; ++b) {
+          double vb = Rm[0][b] * v[0] + Rm[1][b] * v[1] + Rm[2][b] * v[2];
+          fb[b] = -(gt[b] * vb);
+          if (NOISE) fb[b] += sqrt(24.0 * kT * gt[b] / dt) * u[b];
+        }
+#pragma unroll
+        for (int a = 0; a < 3; ++a) F[a] += Rm[a][0] * fb[0] + Rm[a][1] * fb[1] + Rm[a][2] * fb[2];
+      }
+      double wb[3], alb[3];
+#pragma unroll
+      for (int b = 0; b < 3; ++b) {
+        wb[b] = Rm[0][b] * wl[0] + Rm[1][b] * wl[1] + Rm[2][b] * wl[2];
+        double tb = Rm[0][b] * T[0] + Rm[1][b] * T[1] + Rm[2][b] * T[2];
+        tb -= gr[b] * wb[b];
+        if (NOISE) tb += sqrt(24.0 * kT * gr[b] / dt) * ur[b];
+        alb[b] = tb / P.sp_rin[sp][b];
+      }
+      const bool first = R.lv_first && step == R.step0, close = R.lv_close && last;
+      if (!first) {
+#pragma unroll
+        for (int a = 0; a < 3; ++a) { v[a] += hk * (F[a] / m); wb[a] += hk * alb[a]; }
+      }
+      xn = xi; yn = yi; zn = zi;
+      if (!close) {
+#pragma unroll
+        for (int a = 0; a < 3; ++a) { v[a] += hk * (F[a] / m); wb[a] += hk * alb[a]; }
+        xn = xi + dt * v[0]; yn = yi + dt * v[1]; zn = zi + dt * v[2];
+        double dphi[3] = {wb[0] * dt, wb[1] * dt, wb[2] * dt};
+        double mg = sqrt(dphi[0] * dphi[0] + dphi[1] * dphi[1] + dphi[2] * dphi[2]);
+        if (mg > 0.0) {
+          double ax[3] = {dphi[0] / mg, dphi[1] / mg, dphi[2] / mg};
+          sw_quat_rotate_body(q, ax, mg);
+          sw_quat_to_mat(q, Rm);
+        }
+        A.q0[i] = q[0]; A.q1[i] = q[1]; A.q2[i] = q[2]; A.q3[i] = q[3];
+      }
+      A.vx[i] = v[0]; A.vy[i] = v[1]; A.vz[i] = v[2];
+      A.wx[i] = Rm[0][0] * wb[0] + Rm[0][1] * wb[1] + Rm[0][2] * wb[2];
+      A.wy[i] = Rm[1][0] * wb[0] + Rm[1][1] * wb[1] + Rm[1][2] * wb[2];
+      A.wz[i] = Rm[2][0] * wb[0] + Rm[2][1] * wb[1] + Rm[2][2] * wb[2];
     } else {
       const double *gt = P.sp_gt[sp], *gr = P.sp_gr[sp];
       double g[4] = {0.0, 0.0, 0.0, 0.0};
@@ -1067,12 +1164,19 @@ static int sw_run_common(swarm *s, RunArgs R, cudaStream_t st) {
   if (rc) return rc;
   if (R.n_steps < 0) { sw_set_error("n_steps must be >= 0"); return SWARM_ERR_INVALID; }
   s->steps_requested = R.n_steps;
+  s->last_mode = R.mode;
+  s->lv_was_resume = (R.mode == MODE_LV) && s->lv_resume;
   R.force_rebuild = s->list_valid ? 0 : 1;
   if (R.n_steps == 0 || s->A.n == 0) {
     SW_CUDA(cudaMemsetAsync(&s->A.ctl->steps_done, 0, sizeof(long long), st));
     return SWARM_OK;
   }
-  const bool noise = (R.mode == MODE_BD) && (s->P.kT > 0.0);
+  const bool noise = (R.mode == MODE_BD || R.mode == MODE_LV) && (s->P.kT > 0.0);
+  // velocity Verlet: n steps are n + 1 force evaluations (see RunArgs); the kernels count evaluations
+  const bool lv = (R.mode == MODE_LV);
+  if (lv) R.n_steps += 1;
+  const bool lv_resume = lv && s->lv_resume;
+  s->lv_resume = false;
   // bound the length of one cooperative launch (32-bit barrier counter, watchdog friendliness)
   const long long max_chunk = s->persistent ? 8192 : 1024;
   long long done = 0;
@@ -1081,6 +1185,8 @@ static int sw_run_common(swarm *s, RunArgs R, cudaStream_t st) {
     Rc.n_steps = (R.n_steps - done < max_chunk) ? R.n_steps - done : max_chunk;
     Rc.step0 = R.step0 + (u64)done;
     if (done > 0) Rc.force_rebuild = 0;
+    Rc.lv_first = (lv && done == 0 && !lv_resume) ? 1 : 0;
+    Rc.lv_close = (lv && done + Rc.n_steps == R.n_steps) ? 1 : 0;
     // only the last sub-launch of a chunk materialises v / omega on its final step: handled by
     // Rc.n_steps bookkeeping -- earlier sub-launches also write them, harmlessly.
     bool done_resident = false;
@@ -1115,8 +1221,31 @@ static int sw_run_common(swarm *s, RunArgs R, cudaStream_t st) {
 extern "C" int swarm_run(swarm_t *s, int64_t n_steps, uint64_t step0, void *stream) {
   if (!s) return SWARM_ERR_INVALID;
   RunArgs R{};
-  R.n_steps = n_steps; R.step0 = step0; R.mode = MODE_BD;
+  R.n_steps = n_steps; R.step0 = step0; R.mode = (s->integrator == SWARM_INTEGRATOR_LANGEVIN) ? MODE_LV : MODE_BD;
   return sw_run_common(s, R, (cudaStream_t)stream);
+}
+
+extern "C" int swarm_set_integrator(swarm_t *s, int32_t kind) {
+  if (!s) return SWARM_ERR_INVALID;
+  if (kind != SWARM_INTEGRATOR_BROWNIAN && kind != SWARM_INTEGRATOR_LANGEVIN) {
+    sw_set_error("integrator must be SWARM_INTEGRATOR_BROWNIAN or SWARM_INTEGRATOR_LANGEVIN");
+    return SWARM_ERR_INVALID;
+  }
+  if (kind == SWARM_INTEGRATOR_LANGEVIN) {
+    if (!s->species_set) { sw_set_error("set the species table before selecting the Langevin integrator"); return SWARM_ERR_STATE; }
+    for (int k = 0; k < s->P.n_species; ++k) {
+      const double *ri = s->P.sp_rin[k];
+      bool ok = s->P.sp_mass[k] > 0.0 && ri[0] > 0.0;
+      if (s->P.n_dims == 3) ok = ok && ri[0] == ri[1] && ri[1] == ri[2];
+      if (!ok) {
+        sw_set_error("Langevin integrator: every species needs a positive mass and rotational inertia (isotropic in 3-D)");
+        return SWARM_ERR_INVALID;
+      }
+    }
+  }
+  s->integrator = kind;
+  s->lv_resume = false;
+  return SWARM_OK;
 }
 
 extern "C" int swarm_relax(swarm_t *s, int64_t n_iter, double gamma, double max_disp, void *stream) {
@@ -1134,6 +1263,12 @@ extern "C" int swarm_sync_stats(swarm_t *s, void *stream, swarm_stats_t *out) {
   SW_CUDA(cudaStreamSynchronize(st));
   out->steps_done = s->ctl_host->steps_done;
   out->steps_requested = s->steps_requested;
+  if (s->last_mode == MODE_LV) {
+    // the kernels counted force evaluations; an interrupted chunk (Verlet overflow) stopped between the half kicks
+    // of a step, and the resumed run closes that step instead of starting with a recalculation
+    if (s->ctl_host->overflow && (out->steps_done > 0 || s->lv_was_resume)) s->lv_resume = true;
+    if (out->steps_done > out->steps_requested) out->steps_done = out->steps_requested;
+  }
   out->rebuilds = s->ctl_host->rebuilds;
   out->launches = s->launches;
   out->overflow = s->ctl_host->overflow;

@@ -130,6 +130,14 @@ __device__ __forceinline__ void swm_gaussians_xyt(u64 seed, u64 id, u64 step, do
   g0 = m0 * c0; g1 = m0 * s0; g3 = m1 * s1;
 }
 
+// four uniforms in (-1/2, 1/2): the Langevin thermostat's noise (oracle: orc_uniforms)
+__device__ __forceinline__ void swm_uniforms(u64 seed, u64 id, u64 step, u64 stream, double u[4]) {
+  u64 r[4];
+  swm_philox4x64_10(step, stream, 0ULL, 0ULL, id, seed, r);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) u[k] = swm_u01(r[k]) - 0.5;
+}
+
 // all four normals with the fast kernels (parity hook / 3-D)
 __device__ __forceinline__ void swm_gaussians(u64 seed, u64 id, u64 step, u64 stream, double g[4]) {
   u64 r[4];

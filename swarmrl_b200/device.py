@@ -117,6 +117,14 @@ class DeviceSwarm:
         _lib.check(self.lib.swarm_set_thermostat(self.h, float(kT), int(seed)))
         self.kT, self.seed = float(kT), int(seed)
 
+    def set_integrator(self, thermostat_type):
+        """MDParams.thermostat_type: "brownian" (default) or "langevin" (velocity Verlet; v, omega are state)."""
+        kinds = {"brownian": _lib.INTEGRATOR_BROWNIAN, "langevin": _lib.INTEGRATOR_LANGEVIN}
+        if thermostat_type not in kinds:
+            raise ValueError(f"integrator_type must be one of {list(kinds)}")
+        _lib.check(self.lib.swarm_set_integrator(self.h, kinds[thermostat_type]))
+        self.thermostat_type = thermostat_type
+
     # ------------------------------------------------------------------- state
     def _stream(self):
         return C.c_void_p(self.torch.cuda.current_stream(self.dev).cuda_stream)

@@ -11,8 +11,11 @@ The control flow of `integrate` follows espresso.py:1251-1308 statement by state
 the per-chunk `calc_reward`, the kill-switch ordering and the snapshot-before-chunk rule); the
 physics that the reference delegates to ESPResSo runs in libswarm_b200.so.
 
+`thermostat_type="langevin"` selects the Langevin thermostat with velocity Verlet (espresso.py:1187-1201,
+without a fluid); mass and rinertia are then mandatory as in the reference (:391-400).
+
 Out of scope: rods / virtual sites, Gay-Berne, lattice Boltzmann, flow and
-potential fields, user-defined walls, the Langevin (velocity-Verlet) integrator.
+potential fields, user-defined walls.
 """
 from __future__ import annotations
 
@@ -307,8 +310,11 @@ class SwarmEngine(Engine):
         self._check_already_initialised()
         if aspect_ratio != 1.0:
             raise NotImplementedError("Gay-Berne (aspect_ratio != 1) is outside the B200 hot path")
-        if self.params.thermostat_type != "brownian":
-            raise NotImplementedError("only thermostat_type='brownian' is implemented on the B200 path")
+        if self.params.thermostat_type == "langevin":  # espresso.py:391-400
+            if mass is None:
+                raise ValueError("If you use the Langevin thermostat, you must set a particle mass")
+            if rinertia is None:
+                raise ValueError("If you use the Langevin thermostat, you must set a particle rotational inertia")
         if radius_colloid is None:
             radius_colloid = self.ureg.Quantity(1, "micrometer")
         if init_position is None:
@@ -475,9 +481,11 @@ class SwarmEngine(Engine):
         self._backend.set_ext_force_host(F)
 
     def _remove_overlap(self):
-        """espresso.py:1161-1186: 1000 steepest-descent iterations, time restored, BD thermostat on."""
+        """espresso.py:1161-1201: 1000 steepest-descent iterations, time restored, then the thermostat and the
+        integrator of `thermostat_type` (Brownian dynamics, or Langevin + velocity Verlet without a fluid)."""
         self._backend.relax_checked(1000, 0.1, 0.1)
         self._backend.set_thermostat(self._kT, int(self.seed))
+        self._backend.set_integrator(self.params.thermostat_type)
         self._state_version += 1
 
     # -------------------------------------------------------------- trajectory

@@ -17,6 +17,7 @@ class OracleBackend:
         self.n = 0
         self.kT, self.seed = kT, seed
         self.runs = []
+        self.thermostat_type = "brownian"
 
     def set_state(self, pos, species, theta=None, quat=None):
         self._o.set_state(pos, species, theta=theta, quat=quat)
@@ -28,12 +29,20 @@ class OracleBackend:
     def set_thermostat(self, kT, seed):
         self._o.params.kT, self._o.params.seed = float(kT), int(seed)
 
+    def set_integrator(self, thermostat_type):
+        if thermostat_type not in ("brownian", "langevin"):
+            raise ValueError("integrator_type must be one of ['brownian', 'langevin']")
+        self.thermostat_type = thermostat_type
+
     def relax_checked(self, n_iter=1000, gamma=0.1, max_disp=0.1):
         self._o.sd_steps(n_iter, gamma, max_disp, mode=0)
 
     def run_checked(self, n_steps, step0, grow=True):
         self.runs.append((int(n_steps), int(step0)))
-        self._o.bd_steps(step0, n_steps, mode=0)
+        if self.thermostat_type == "langevin":
+            self._o.lv_steps(step0, n_steps, mode=0)
+        else:
+            self._o.bd_steps(step0, n_steps, mode=0)
 
     def particle_data_host(self):
         return self._o.pos.copy(), self._o.velocities.copy(), self._o.directors.copy()

@@ -230,3 +230,41 @@ def test_oracle_policy_forward_definitions():
     a = policy_forward(obs, P, seed=1, call=7, sample=True)[0]
     assert np.array_equal(a, policy_forward(obs, P, seed=1, call=7, sample=True)[0])
     assert (a != policy_forward(obs, P, seed=1, call=8, sample=True)[0]).any()
+
+
+def test_langevin_thermostat_setup_and_terminal_velocity(tmp_path):
+    """thermostat_type="langevin" (espresso.py:1187-1201 without a fluid): mass and rinertia are mandatory
+    (:391-400); v is integrated state and relaxes to f e / gamma_t with time constant m / gamma_t."""
+    ureg = UnitRegistry()
+    time_step = ureg.Quantity(0.001, "second")
+    kw = dict(ureg=ureg, fluid_dyn_viscosity=ureg.Quantity(8.9e-4, "pascal * second"),
+              WCA_epsilon=ureg.Quantity(293, "kelvin") * ureg.boltzmann_constant,
+              temperature=ureg.Quantity(0, "kelvin"), box_length=ureg.Quantity(3 * [1000], "micrometer"),
+              time_step=time_step, time_slice=time_step * 100, write_interval=time_step * 100)
+    with pytest.raises(ValueError):
+        bad = CpuEngine(md_params=sw.MDParams(thermostat_type="nose-hoover", **kw), n_dims=2, out_folder=tmp_path)
+        bad.add_colloids(1, ureg.Quantity(1, "micrometer"), ureg.Quantity(np.array([500, 500, 0]), "micrometer"),
+                         ureg.Quantity(100, "micrometer"))
+        bad.integrate(1, sw.ForceFunction({"0": sw.ConstForce(1.0)}))
+    e = CpuEngine(md_params=sw.MDParams(thermostat_type="langevin", **kw), n_dims=2, seed=3, out_folder=tmp_path)
+    place = (ureg.Quantity(1, "micrometer"), ureg.Quantity(np.array([500, 500, 0]), "micrometer"),
+             ureg.Quantity(100, "micrometer"))
+    with pytest.raises(ValueError, match="particle mass"):
+        e.add_colloids(1, *place)
+    gt, _ = e_gamma = sw.engine._calc_friction_coefficients(
+        float(kw["fluid_dyn_viscosity"].m_as("sim_dyn_viscosity")), 1.0)
+    mass = ureg.Quantity(gt * 0.001 / 0.02, "sim_mass")  # m / gamma = 50 time steps
+    with pytest.raises(ValueError, match="rotational inertia"):
+        e.add_colloids(1, *place, mass=mass)
+    rin = ureg.Quantity(e_gamma[1] * 0.001 / 0.02, "sim_rinertia")
+    e.add_colloids(4, *place, mass=mass, rinertia=rin)
+    f = 2.0 * gt
+    ff = sw.ForceFunction({"0": sw.ConstForce(f)})
+    e.integrate(1, ff)  # 100 steps = 2 relaxation times
+    d = e.get_particle_data()
+    speed = np.sum(d["Velocities"] * d["Directors"], axis=1)
+    assert np.all(np.abs(speed / 2.0 - (1 - np.exp(-2.0))) < 2e-2)
+    e.integrate(20, ff)
+    d = e.get_particle_data()
+    assert np.allclose(d["Velocities"], 2.0 * d["Directors"], rtol=1e-9, atol=1e-12)
+    assert e._backend.thermostat_type == "langevin"

@@ -167,3 +167,88 @@ def test_verlet_and_cell_trajectories_equal_brute_force_bitwise():
     assert 1 < oracle.last_verlet_builds() < 300
     for r in res[1:]:
         assert all(np.array_equal(a, b) for a, b in zip(res[0], r))
+
+
+# ---- Langevin thermostat + velocity Verlet (espresso.py:1187-1201): parity-unpinned, pinned analytically ----
+def _langevin_species(radius=1.0, a=0.02, dt=1e-3):
+    """Stokes friction; mass / inertia chosen so that gamma dt / m = a (the reference demands explicit values,
+    espresso.py:391-400: water-density colloids relax in 2.5e-7 s, far below any usable time step)."""
+    gt, gr = stokes(radius)
+    return [dict(type=0, gamma_t=(gt,) * 3, gamma_r=(gr,) * 3, mass=gt * dt / a, rinertia=(gr * dt / a,) * 3)]
+
+
+@pytest.mark.parametrize("n_dims", [2, 3])
+def test_langevin_terminal_velocity_and_relaxation_time(n_dims):
+    """kT = 0: v(t) = (f/gamma)(1 - exp(-gamma t / m)) e, omega(t) likewise with tau/gamma_r and I/gamma_r."""
+    dt, a = 1e-3, 0.01
+    sp = _langevin_species(a=a, dt=dt)
+    zero = dict(sigma=np.zeros((1, 1)), eps=np.zeros((1, 1)), cut=np.zeros((1, 1)))
+    o = OracleSwarm(n_dims, (1e3,) * 3, True, dt, 0.0, 7, sp, zero)
+    o.set_state(np.array([[500.0, 500.0, 0.0 if n_dims == 2 else 500.0]]), np.zeros(1, dtype=np.int32),
+                theta=np.array([0.3]), quat=np.array([[1.0, 0, 0, 0]]))
+    gt, gr = stokes(1.0)
+    o.f_swim[:] = 2.0 * gt
+    o.lv_steps(0, 100)  # t = m / gamma
+    e = o.directors[0]
+    assert abs(np.dot(o.velocities[0], e) / 2.0 - (1 - np.exp(-1.0))) < 5e-3
+    o.lv_steps(100, 3000)  # 31 relaxation times
+    assert np.allclose(o.velocities[0], 2.0 * e, rtol=1e-9, atol=1e-12)
+    # rotation about lab z: in 2-D this is the only rotational degree of freedom; in 3-D the director is body z
+    o.f_swim[:] = 0.0
+    o.torque[2][:] = 0.5 * gr
+    o.lv_steps(3100, 100)
+    assert abs(o.omegas[0, 2] / 0.5 - (1 - np.exp(-1.0))) < 5e-3
+    o.lv_steps(3200, 3000)
+    assert abs(o.omegas[0, 2] - 0.5) < 1e-9
+    if n_dims == 2:
+        assert np.all(o.pos[:, 2] == 0.0) and np.all(o.omegas[:, :2] == 0.0)
+
+
+@pytest.mark.parametrize("n_dims", [2, 3])
+def test_langevin_equipartition_and_diffusion(n_dims):
+    """<v^2> = d kT/m, <omega^2> = d_r kT/I, MSD = 2 d (kT/gamma)(t - m/gamma) for t >> m/gamma."""
+    n, steps, dt, a = 4000, 1500, 1e-3, 0.04
+    sp = _langevin_species(a=a, dt=dt)
+    zero = dict(sigma=np.zeros((1, 1)), eps=np.zeros((1, 1)), cut=np.zeros((1, 1)))
+    o = OracleSwarm(n_dims, (1e4,) * 3, True, dt, KT_300, 11, sp, zero)
+    rng = np.random.default_rng(3)
+    pos = np.zeros((n, 3))
+    pos[:, :n_dims] = rng.uniform(0, 1e4, (n, n_dims))
+    o.set_state(pos, np.zeros(n, dtype=np.int32), theta=rng.uniform(0, 2 * np.pi, n), quat=random_quats(n, rng))
+    x0 = o.pos.copy()
+    o.lv_steps(0, steps)
+    gt, gr = stokes(1.0)
+    m, I = sp[0]["mass"], sp[0]["rinertia"][0]
+    tol = 4 * np.sqrt(2.0 / (n * n_dims)) + a  # statistics + O(gamma dt / m) discretisation bias
+    v2 = np.mean(np.sum(o.velocities**2, axis=1))
+    assert abs(v2 / (n_dims * KT_300 / m) - 1) < tol
+    d_rot = 1 if n_dims == 2 else 3
+    w2 = np.mean(np.sum(o.omegas**2, axis=1))
+    assert abs(w2 / (d_rot * KT_300 / I) - 1) < 4 * np.sqrt(2.0 / (n * d_rot)) + a
+    t = steps * dt
+    msd = np.mean(np.sum((o.pos - x0) ** 2, axis=1))
+    want = 2 * n_dims * KT_300 / gt * (t - m / gt)
+    assert abs(msd / want - 1) < tol
+    if n_dims == 2:
+        assert np.all(o.pos[:, 2] == 0.0)
+
+
+def test_langevin_chunks_restart_with_a_force_recalculation():
+    """Every integrator.run() recomputes the forces at the current (x, v) (particle properties changed in
+    manage_forces): with kT = 0 the recalculated force equals the one that closed the previous chunk except
+    for the friction term, which now sees the full-step velocity -- a second-order difference."""
+    dt = 1e-3
+    sp = _langevin_species(a=0.02, dt=dt)
+    rng = np.random.default_rng(5)
+    pos = jittered_lattice(200, 60.0, 2, rng)
+    th = rng.uniform(0, 2 * np.pi, 200)
+    out = []
+    for chunks in ((0, 60),), ((0, 25), (25, 35)):
+        o = OracleSwarm(2, (60.0,) * 3, True, dt, 0.0, 1, sp, wca_for([1.0]))
+        o.set_state(pos, np.zeros(200, dtype=np.int32), theta=th)
+        o.f_swim[:] = 3.0 * stokes(1.0)[0]
+        for s0, k in chunks:
+            o.lv_steps(s0, k, mode=2)
+        out.append(o.pos.copy())
+    assert not np.array_equal(out[0], out[1])
+    assert np.abs(out[0] - out[1]).max() < 1e-4
