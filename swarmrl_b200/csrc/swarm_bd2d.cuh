@@ -287,7 +287,8 @@ __device__ __forceinline__ void sw_prefetch_l2(const void *p) { asm volatile("pr
 
 template <bool NOISE>
 __device__ __forceinline__ bool bd2d_step_stream(const DevParams &P, const DevArrays &A, const Bd2dSpecies *S, int cur, u64 step,
-                                                 bool last, long long i, long long i_next, double lim2) {
+                                                 bool last, long long i, long long i_next, double lim2, bool have_g,
+                                                 double pg0, double pg1, double pg3) {
   const int nxt = cur ^ 1;
   // every per-particle input is requested up front: without __restrict__ the compiler keeps each load
   // behind the stores of the previous particle and next to its first use, which serialised four DRAM
@@ -332,8 +333,8 @@ __device__ __forceinline__ bool bd2d_step_stream(const DevParams &P, const DevAr
   Fx += sf.wx; Fy += sf.wy;
   Fx += sf.sx; Fy += sf.sy;
   if (A.fex) { Fx += fxe; Fy += fye; }
-  double g0 = 0.0, g1 = 0.0, g3 = 0.0;
-  if (NOISE) swm_gaussians_xyt(P.seed, pid, step, g0, g1, g3);
+  double g0 = pg0, g1 = pg1, g3 = pg3;  // drawn behind the previous step's barrier for the thread's first particle
+  if (NOISE && !have_g) swm_gaussians_xyt(P.seed, pid, step, g0, g1, g3);
   const double dt = P.dt;
   double xn, yn, vx, vy;
   if (c.gt1 == c.gt2) {
@@ -372,6 +373,9 @@ __device__ __forceinline__ bool bd2d_step_stream(const DevParams &P, const DevAr
 #ifndef SW_STREAM_MINB
 #define SW_STREAM_MINB 3
 #endif
+#ifndef SW_STREAM_PRE
+#define SW_STREAM_PRE 1  // particles per thread whose next-step noise is drawn behind the grid barrier
+#endif
 template <bool NOISE>
 __global__ void __launch_bounds__(SW_STREAM_THREADS, SW_STREAM_MINB) k_bd2d_stream(const __grid_constant__ DevParams P, DevArrays A, RunArgs R) {
   Ctl *ctl = A.ctl;
@@ -401,10 +405,28 @@ __global__ void __launch_bounds__(SW_STREAM_THREADS, SW_STREAM_MINB) k_bd2d_stre
   // release word to poll, no fence.sc and no per-step flag traffic.
   __shared__ int s_need;
   unsigned int movers_seen = 0;
-  auto step_barrier = [&](bool moved) -> bool {
+  // Between arrive and poll every thread draws the NEXT step's noise of its first particle (depends on
+  // (seed, id, step) only): about one ninth of a step's instructions at 1M particles, which covers the
+  // barrier's L2 round trips and the arrival skew of the other CTAs.
+  const long long i0 = lo + threadIdx.x;
+  __shared__ double s_g[SW_STREAM_PRE][3][SW_STREAM_THREADS];  // a thread only touches its own column
+  bool have_g = false;
+  auto step_barrier = [&](bool moved, bool draw, u64 next_step) -> bool {
     const int any = __syncthreads_or(moved);
+    if (threadIdx.x == 0) grid_arrive64(&ctl->bar64, epoch, any != 0);
+    have_g = false;
+    if (NOISE && draw) {
+#pragma unroll 1
+      for (int k = 0; k < SW_STREAM_PRE; ++k) {
+        const long long i = i0 + k * gstride;
+        if (i >= hi) break;
+        double a, b, c;
+        swm_gaussians_xyt(P.seed, sw_pid(A, i), next_step, a, b, c);
+        s_g[k][0][threadIdx.x] = a; s_g[k][1][threadIdx.x] = b; s_g[k][2][threadIdx.x] = c;
+      }
+      have_g = true;
+    }
     if (threadIdx.x == 0) {
-      grid_arrive64(&ctl->bar64, epoch, any != 0);
       const unsigned int mv = (unsigned int)(grid_poll64(&ctl->bar64, epoch) >> 32);
       s_need = (mv != movers_seen);
       movers_seen = mv;
@@ -416,7 +438,7 @@ __global__ void __launch_bounds__(SW_STREAM_THREADS, SW_STREAM_MINB) k_bd2d_stre
   if (!R.force_rebuild) {
     bool moved = false;
     for (long long i = lo + threadIdx.x; i < hi; i += gstride) moved |= moved_since_build<2>(P, A, 0, i);
-    need = step_barrier(moved);
+    need = step_barrier(moved, R.n_steps > 0, R.step0);
   }
   long long s = 0;
   for (; s < R.n_steps; ++s) {
@@ -433,9 +455,14 @@ __global__ void __launch_bounds__(SW_STREAM_THREADS, SW_STREAM_MINB) k_bd2d_stre
     }
     const bool last = (s == R.n_steps - 1);
     bool moved = false;
-    for (long long i = lo + threadIdx.x; i < hi; i += gstride)
-      moved |= bd2d_step_stream<NOISE>(P, A, S, cur, R.step0 + (u64)s, last, i, (i + gstride < hi) ? i + gstride : -1, lim2);
-    need = step_barrier(moved);
+    int k = 0;
+    for (long long i = i0; i < hi; i += gstride, ++k) {
+      const bool pre = NOISE && have_g && k < SW_STREAM_PRE;
+      const int kk = pre ? k : 0;
+      moved |= bd2d_step_stream<NOISE>(P, A, S, cur, R.step0 + (u64)s, last, i, (i + gstride < hi) ? i + gstride : -1, lim2,
+                                       pre, s_g[kk][0][threadIdx.x], s_g[kk][1][threadIdx.x], s_g[kk][2][threadIdx.x]);
+    }
+    need = step_barrier(moved, !last, R.step0 + (u64)s + 1);
   }
   if (s & 1) {
     for (long long i = lo + threadIdx.x; i < hi; i += gstride) {
