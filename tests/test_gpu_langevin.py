@@ -139,6 +139,32 @@ def test_langevin_overflow_resumes_inside_the_step():
     _compare(o, d, tol=1e-7, tol_e=1e-7)
 
 
+def test_langevin_with_walls_and_constant_force():
+    """Non-periodic arena (espresso.py:667-711) and a constant external force (:834-851) under velocity Verlet:
+    inertial particles bounce off the WCA walls but stay inside; the device follows the oracle."""
+    rng = np.random.default_rng(4)
+    n, L = 100, 40.0
+    sp, wca = _species(), wca_for([1.0])
+    walls = dict(sigma=[1.0 * 2 ** (-1 / 6)], eps=[1.0], cut=[1.0])
+    pos = jittered_lattice(n, L, 2, rng)
+    pos[:, :2] = 2.0 + pos[:, :2] * (L - 4.0) / L
+    o, d = make_pair(2, (L,) * 3, False, 1e-3, 0.0, 1, sp, wca, pos, np.zeros(n, dtype=np.int32),
+                     theta=rng.uniform(0, 2 * np.pi, n), walls=walls)
+    d.set_integrator("langevin")
+    set_actions(o, d, np.full(n, 4.0 * stokes(1.0)[0]), np.zeros((n, 3)))
+    F = np.tile([0.5 * stokes(1.0)[0], 0.0, 0.0], (n, 1))
+    for a in range(3):
+        o.ext_force[a][:] = F[:, a]
+    d.set_ext_force_host(F)
+    o.lv_steps(0, 3000, mode=0)
+    st = d.run_checked(3000, 0)
+    assert st.steps_done == 3000
+    _compare(o, d, tol=1e-7, tol_e=1e-7)
+    p, _, _ = d.particle_data_host()
+    assert p[:, :2].min() > 0.0 and p[:, :2].max() < L
+    assert (p[:, :2].min() < 1.0) or (p[:, :2].max() > L - 1.0)
+
+
 def test_langevin_setup_errors():
     from swarmrl_b200.device import DeviceSwarm
 
