@@ -99,6 +99,8 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_resident(const __grid_c
   const double w = swm_div_r(Tz, gr0, r_gr0);  // omega_z: the torque is constant over the chunk
 
   __shared__ int s_need;
+  __shared__ volatile int s_moved;  // some particle of this CTA went beyond skin/2 in the current step
+  if (threadIdx.x == 0) s_moved = 0;
   unsigned int movers_seen = 0;  // thread 0: high word of the barrier counter at the last poll
   bool need = true;
   if (!R.force_rebuild) {
@@ -221,10 +223,14 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_resident(const __grid_c
       moved = (ddx * ddx + ddy * ddy) > lim2;
     }
     SW_TICK(1);
-    const int any = __syncthreads_or(moved);
-    SW_TICK(2);
     if (threadIdx.x < 32) {
-      // ---- barrier warp: arrive, then poll; publishes the rebuild decision -----------------------
+      // ---- barrier warp: waits for the particle warps' stores (named barrier 1: they only ARRIVE, so a warp
+      // that is done goes straight on to its local work instead of waiting for the slowest warp of the CTA),
+      // then arrives at the grid barrier and polls; publishes the rebuild decision -------------------------
+      asm volatile("barrier.cta.sync 1, %0;" ::"r"((int)blockDim.x) : "memory");
+      SW_TICK(2);
+      int any = 0;
+      if (threadIdx.x == 0) { any = s_moved; s_moved = 0; }
       grid_arrive64(&ctl->bar64, epoch, any != 0);
       SW_TICK(6);
       if (threadIdx.x == 0) {
@@ -233,11 +239,16 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_resident(const __grid_c
         movers_seen = mv;
       }
       SW_TICK(7);
-    } else if (act && !last) {
-      // ---- particle-local work of step s+1, overlapping the barrier ------------------------------
-      sincos(th, &ey, &ex);
-      sf = bd2d_self_forces(P, ti, xi, yi, ex, ey, fsw);
-      if (NOISE) swm_gaussians_xyt(P.seed, pid, R.step0 + (u64)(s + 1), g0, g1, g3);
+    } else {
+      if (moved) s_moved = 1;
+      asm volatile("barrier.cta.arrive 1, %0;" ::"r"((int)blockDim.x) : "memory");
+      SW_TICK(2);
+      if (act && !last) {
+        // ---- particle-local work of step s+1, overlapping the barrier ----------------------------
+        sincos(th, &ey, &ex);
+        sf = bd2d_self_forces(P, ti, xi, yi, ex, ey, fsw);
+        if (NOISE) swm_gaussians_xyt(P.seed, pid, R.step0 + (u64)(s + 1), g0, g1, g3);
+      }
     }
     SW_TICK(4);
     __syncthreads();
