@@ -123,7 +123,7 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_resident(const __grid_c
   double g0 = 0.0, g1 = 0.0, g3 = 0.0, ex = 1.0, ey = 0.0;
   Bd2dSelf sf = {0.0, 0.0, 0.0, 0.0};
   if (act) {
-    sincos(th, &ey, &ex);
+    swm_sincos(th, ey, ex);
     sf = bd2d_self_forces(P, ti, xi, yi, ex, ey, fsw);
     if (NOISE) swm_gaussians_xyt(P.seed, pid, R.step0, g0, g1, g3);
   }
@@ -245,7 +245,7 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_resident(const __grid_c
       SW_TICK(2);
       if (act && !last) {
         // ---- particle-local work of step s+1, overlapping the barrier ----------------------------
-        sincos(th, &ey, &ex);
+        swm_sincos(th, ey, ex);
         sf = bd2d_self_forces(P, ti, xi, yi, ex, ey, fsw);
         if (NOISE) swm_gaussians_xyt(P.seed, pid, R.step0 + (u64)(s + 1), g0, g1, g3);
       }
@@ -339,7 +339,7 @@ __device__ __forceinline__ bool bd2d_step_stream(const DevParams &P, const DevAr
       if (k0 + u < cnt) bd2d_pair(P, xi, yi, ti, en[u] >> SW_TYPE_SHIFT, xj[u], yj[u], Fx, Fy);
   }
   double ex, ey;
-  sincos(th, &ey, &ex);
+  swm_sincos(th, ey, ex);
   const Bd2dSelf sf = bd2d_self_forces(P, ti, xi, yi, ex, ey, fsw);
   Fx += sf.wx; Fy += sf.wy;
   Fx += sf.sx; Fy += sf.sy;
@@ -529,7 +529,7 @@ __global__ void __launch_bounds__(SW_ENV_THREADS) k_bd2d_env(const __grid_consta
   const float pref2 = pr * pr;
   for (long long s = 0; s < R.n_steps; ++s) {
     double ex, ey, g0 = 0.0, g1 = 0.0, g3 = 0.0;
-    sincos(th, &ey, &ex);
+    swm_sincos(th, ey, ex);
     const Bd2dSelf sf = bd2d_self_forces(P, ti, xi, yi, ex, ey, fsw);
     if (NOISE) swm_gaussians_xyt(P.seed, pid, R.step0 + (u64)s, g0, g1, g3);
     double Fx = 0.0, Fy = 0.0;

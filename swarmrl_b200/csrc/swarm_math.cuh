@@ -130,6 +130,35 @@ __device__ __forceinline__ void swm_gaussians_xyt(u64 seed, u64 id, u64 step, do
   g0 = m0 * c0; g1 = m0 * s0; g3 = m1 * s1;
 }
 
+// (sin, cos)(theta) of the 2-D director.  theta / (2 pi) with a two-term reciprocal (product error recovered by one
+// fma), quadrant by the round-to-nearest magic constant, then the polynomials of swm_sincos2pi on t in [-1/8, 1/8]
+// turns: <= 1.2e-16 absolute against mpmath for |theta| <= 1e6 (tools/gen_coeffs.py), no slow-path call in the hot
+// loop.  Beyond 2^30 rad the library routine takes over.
+__device__ __forceinline__ void swm_sincos(double th, double &sn, double &cs) {
+  if (!(fabs(th) < 1073741824.0)) { sincos(th, &sn, &cs); return; }
+  const double c_hi = 0.15915494309189535, c_lo = -9.839338337591243e-18;  // 1 / (2 pi)
+  const double turns = th * c_hi;
+  const double rem = fma(th, c_hi, -turns) + th * c_lo;
+  const double big = 6755399441055744.0;  // 1.5 * 2^52: (x + big) - big = rint(x)
+  const double qs = fma(4.0, turns, big);
+  const double qd = qs - big;
+  const unsigned q = (unsigned)__double2loint(qs);
+  const double t = fma(qd, -0.25, turns) + rem;
+  const double z = t * t;
+  double ps = SWM_SIN[8];
+#pragma unroll
+  for (int k = 7; k >= 0; --k) ps = fma(ps, z, SWM_SIN[k]);
+  ps *= t;
+  double pc = SWM_COS[9];
+#pragma unroll
+  for (int k = 8; k >= 0; --k) pc = fma(pc, z, SWM_COS[k]);
+  const bool swap = q & 1u;
+  double s0 = swap ? pc : ps, c0 = swap ? ps : pc;
+  if ((q + 1u) & 2u) c0 = -c0;
+  if (q & 2u) s0 = -s0;
+  sn = s0; cs = c0;
+}
+
 // four uniforms in (-1/2, 1/2): the Langevin thermostat's noise (oracle: orc_uniforms)
 __device__ __forceinline__ void swm_uniforms(u64 seed, u64 id, u64 step, u64 stream, double u[4]) {
   u64 r[4];

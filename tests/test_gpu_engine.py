@@ -341,3 +341,21 @@ def test_warp_per_environment_kernel_equals_the_list_kernels(monkeypatch):
     for u, v, w in zip(a[:3], b[:3], c[:3]):
         assert rel_err(u, v) < 1e-12
         assert np.array_equal(u, w)
+
+
+@pytest.mark.parametrize("scale", [1e3, 1e6, 3e9, 1e12])
+def test_director_of_large_angles(scale):
+    """The 2-D kernels reduce theta themselves (swm_sincos; library routine beyond 2^30 rad): wound-up angles,
+    as they accumulate under a constant torque, still give the oracle's director and trajectory."""
+    rng = np.random.default_rng(12)
+    n, L = 600, 120.0
+    sp, wca = species_for([1.0]), wca_for([1.0])
+    pos = jittered_lattice(n, L, 2, rng)
+    th = rng.uniform(-scale, scale, n)
+    o, d = make_pair(2, (L, L, L), True, 1e-3, 0.0, 42, sp, wca, pos, np.zeros(n, dtype=np.int32), theta=th)
+    set_actions(o, d, np.full(n, 5.0 * sp[0]["gamma_t"][0]), np.zeros((n, 3)))
+    o.bd_steps(0, 50, mode=2)
+    st = d.run_checked(50, 0)
+    assert st.steps_done == 50
+    p, v, e = d.particle_data_host()
+    assert rel_err(p, o.pos) < 1e-12 and rel_err(v, o.velocities) < 1e-9
