@@ -489,11 +489,12 @@ __global__ void __launch_bounds__(SW_STREAM_THREADS, SW_STREAM_MINB) k_bd2d_stre
 
 // ---------------------------------------------------------------------------------------------
 // k_bd2d_env -- batched independent environments (BASELINE config 3): ONE WARP PER ENVIRONMENT, one agent per
-// lane (env_size <= 32).  Environments never interact, so nothing here is grid-wide: no cell list, no Verlet
-// list, no barrier of any kind.  An agent's state stays in registers for the whole chunk of steps and its
-// neighbours' positions arrive by warp shuffle -- all pairs of the environment, visited in ascending agent
-// index, which is exactly the order of the (ascending) Verlet list the other kernels and the oracle sum in;
-// pairs beyond the cut-off add nothing, so the result equals the list kernels' up to FMA contraction (1e-13).
+// lane (env_size <= 32).  Environments never interact, so nothing here is grid-wide: no cell list, no barrier
+// of any kind, and the Verlet list of an agent is a 32-bit mask in a register.  An agent's state stays in
+// registers for the whole chunk of steps and its neighbours' positions arrive by warp shuffle, visited in
+// ascending agent index, which is exactly the order of the (ascending) Verlet list the other kernels and the
+// oracle sum in; pairs beyond the cut-off add nothing, so the result equals the list kernels' up to FMA
+// contraction (1e-13) and equals the all-pairs loop (SWARM_B200_ENV_EXACT_PAIRS) bit for bit.
 // ---------------------------------------------------------------------------------------------
 #define SW_ENV_THREADS 256
 // RunArgs.force_rebuild is meaningless for the list-free kernel: the launcher reuses it as "exact pairs only"
@@ -525,34 +526,58 @@ __global__ void __launch_bounds__(SW_ENV_THREADS) k_bd2d_env(const __grid_consta
   double vx_l = 0.0, vy_l = 0.0;
   const bool prefilter = P.periodic[0] && P.periodic[1] && !getenv_no_prefilter(R);
   const float bxf = (float)P.box[0], byf = (float)P.box[1], ibxf = (float)P.inv_box[0], ibyf = (float)P.inv_box[1];
-  const float pr = (float)(P.max_cut + 1e-4 * (1.0 + fmax(P.box[0], P.box[1])));
+  const float pr = (float)(P.max_cut + P.skin + 1e-4 * (1.0 + fmax(P.box[0], P.box[1])));
   const float pref2 = pr * pr;
+  const double lim2 = (0.5 * P.skin) * (0.5 * P.skin);
+  unsigned mask = 0u;
+  double xr = xi, yr = yi;
+  bool need = true;
   for (long long s = 0; s < R.n_steps; ++s) {
     double ex, ey, g0 = 0.0, g1 = 0.0, g3 = 0.0;
     swm_sincos(th, ey, ex);
     const Bd2dSelf sf = bd2d_self_forces(P, ti, xi, yi, ex, ey, fsw);
     if (NOISE) swm_gaussians_xyt(P.seed, pid, R.step0 + (u64)s, g0, g1, g3);
     double Fx = 0.0, Fy = 0.0;
-    // fp32 pre-filter on wrapped coordinates: all 32 x 31 pairs are screened at full fp32 rate with one shuffle per
-    // coordinate, and the exact fp64 pair (two shuffles per coordinate, half-rate arithmetic) runs only for the
-    // partners j that some lane of the warp may actually touch (about one in ten at the densities of config 3).
-    // The screen radius exceeds the cut-off by far more than the fp32 rounding of a wrapped coordinate, so it can
-    // only admit extra pairs, never drop one.
-    float xf = 0.0f, yf = 0.0f;
     if (prefilter) {
-      xf = (float)__dsub_rn(xi, __dmul_rn(P.box[0], rint(__dmul_rn(xi, P.inv_box[0]))));
-      yf = (float)__dsub_rn(yi, __dmul_rn(P.box[1], rint(__dmul_rn(yi, P.inv_box[1]))));
-    }
-    for (int j = 0; j < m; ++j) {
-      if (prefilter) {
-        float dxf = xf - __shfl_sync(0xffffffffu, xf, j), dyf = yf - __shfl_sync(0xffffffffu, yf, j);
-        dxf -= bxf * rintf(dxf * ibxf); dyf -= byf * rintf(dyf * ibyf);
-        const bool cand = act && j != lane && (dxf * dxf + dyf * dyf < pref2);
-        if (!__any_sync(0xffffffffu, cand)) continue;
+      // A Verlet list in one register: bit j of `mask` = agent j was within cut-off + skin of this agent when the
+      // environment was last screened.  The screen runs in fp32 on wrapped coordinates (all 32 x 31 pairs, one
+      // shuffle per coordinate; its radius exceeds cut-off + skin by far more than the fp32 rounding of a wrapped
+      // coordinate, so it can only admit extra pairs, never drop one) and is repeated when some agent of the
+      // environment has moved more than skin / 2 since -- every 20-30 steps instead of every step.
+      bool moved = false;
+      if (act) {
+        const double ddx = xi - xr, ddy = yi - yr;
+        moved = !(ddx * ddx + ddy * ddy <= lim2);
       }
-      const double xj = __shfl_sync(0xffffffffu, xi, j), yj = __shfl_sync(0xffffffffu, yi, j);
-      const int tj = __shfl_sync(0xffffffffu, ti, j);
-      if (j != lane) bd2d_pair(P, xi, yi, ti, tj, xj, yj, Fx, Fy);
+      if (need || __any_sync(0xffffffffu, moved)) {
+        const float xf = (float)__dsub_rn(xi, __dmul_rn(P.box[0], rint(__dmul_rn(xi, P.inv_box[0]))));
+        const float yf = (float)__dsub_rn(yi, __dmul_rn(P.box[1], rint(__dmul_rn(yi, P.inv_box[1]))));
+        unsigned nm = 0u;
+        for (int j = 0; j < m; ++j) {
+          float dxf = xf - __shfl_sync(0xffffffffu, xf, j), dyf = yf - __shfl_sync(0xffffffffu, yf, j);
+          dxf -= bxf * rintf(dxf * ibxf); dyf -= byf * rintf(dyf * ibyf);
+          if (dxf * dxf + dyf * dyf < pref2) nm |= 1u << j;
+        }
+        mask = act ? (nm & ~(1u << lane)) : 0u;
+        xr = xi; yr = yi;
+        need = false;
+      }
+      // the listed partners in ascending index (the summation order of the other kernels and of the oracle); a lane
+      // that has run out of partners shuffles with itself
+      unsigned rem = mask;
+      while (__any_sync(0xffffffffu, rem != 0u)) {
+        const int j = rem ? (__ffs((int)rem) - 1) : lane;
+        rem &= rem - 1u;
+        const double xj = __shfl_sync(0xffffffffu, xi, j), yj = __shfl_sync(0xffffffffu, yi, j);
+        const int tj = __shfl_sync(0xffffffffu, ti, j);
+        if (j != lane) bd2d_pair(P, xi, yi, ti, tj, xj, yj, Fx, Fy);
+      }
+    } else {
+      for (int j = 0; j < m; ++j) {
+        const double xj = __shfl_sync(0xffffffffu, xi, j), yj = __shfl_sync(0xffffffffu, yi, j);
+        const int tj = __shfl_sync(0xffffffffu, ti, j);
+        if (j != lane) bd2d_pair(P, xi, yi, ti, tj, xj, yj, Fx, Fy);
+      }
     }
     Fx += sf.wx; Fy += sf.wy;
     Fx += sf.sx; Fy += sf.sy;
