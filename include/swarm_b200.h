@@ -124,7 +124,8 @@ int swarm_set_thermostat(swarm_t *s, double kT, uint64_t seed);
  * integrator.set_vv (:1187-1201, without a lattice-Boltzmann fluid).  Under LANGEVIN swarm_run advances
  * velocity Verlet steps: v and omega of the bound state are INPUTS as well as outputs, every species
  * needs mass > 0 and rinertia > 0 (espresso.py:391-400; isotropic rinertia in 3-D), every run starts
- * with a force recalculation at the current (x, v) as ESPResSo does after particle properties change. */
+ * with a force recalculation at the current (x, v) as ESPResSo does after particle properties change.
+ * The domain exchange (swarm_dd_*) carries no velocities and refuses to run under LANGEVIN. */
 typedef enum { SWARM_INTEGRATOR_BROWNIAN = 0, SWARM_INTEGRATOR_LANGEVIN = 1 } swarm_integrator_t;
 int swarm_set_integrator(swarm_t *s, int32_t kind);
 

@@ -1159,10 +1159,28 @@ static int sw_launch_np(swarm *s, const RunArgs &R, cudaStream_t st) {
   return SWARM_OK;
 }
 
+// velocity Verlet divides by mass and rotational inertia (espresso.py:391-400 makes both mandatory)
+static int sw_check_inertial(const swarm *s) {
+  for (int k = 0; k < s->P.n_species; ++k) {
+    const double *ri = s->P.sp_rin[k];
+    bool ok = s->P.sp_mass[k] > 0.0 && ri[0] > 0.0;
+    if (s->P.n_dims == 3) ok = ok && ri[0] == ri[1] && ri[1] == ri[2];
+    if (!ok) {
+      sw_set_error("Langevin integrator: every species needs a positive mass and rotational inertia (isotropic in 3-D)");
+      return SWARM_ERR_INVALID;
+    }
+  }
+  return SWARM_OK;
+}
+
 static int sw_run_common(swarm *s, RunArgs R, cudaStream_t st) {
   int rc = sw_prepare(s, st);
   if (rc) return rc;
   if (R.n_steps < 0) { sw_set_error("n_steps must be >= 0"); return SWARM_ERR_INVALID; }
+  if (R.mode == MODE_LV) {  // the species table may have been replaced since swarm_set_integrator
+    rc = sw_check_inertial(s);
+    if (rc) return rc;
+  }
   s->steps_requested = R.n_steps;
   s->last_mode = R.mode;
   s->lv_was_resume = (R.mode == MODE_LV) && s->lv_resume;
@@ -1233,15 +1251,8 @@ extern "C" int swarm_set_integrator(swarm_t *s, int32_t kind) {
   }
   if (kind == SWARM_INTEGRATOR_LANGEVIN) {
     if (!s->species_set) { sw_set_error("set the species table before selecting the Langevin integrator"); return SWARM_ERR_STATE; }
-    for (int k = 0; k < s->P.n_species; ++k) {
-      const double *ri = s->P.sp_rin[k];
-      bool ok = s->P.sp_mass[k] > 0.0 && ri[0] > 0.0;
-      if (s->P.n_dims == 3) ok = ok && ri[0] == ri[1] && ri[1] == ri[2];
-      if (!ok) {
-        sw_set_error("Langevin integrator: every species needs a positive mass and rotational inertia (isotropic in 3-D)");
-        return SWARM_ERR_INVALID;
-      }
-    }
+    int rc = sw_check_inertial(s);
+    if (rc) return rc;
   }
   s->integrator = kind;
   s->lv_resume = false;

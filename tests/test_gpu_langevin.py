@@ -180,3 +180,20 @@ def test_langevin_setup_errors():
     with pytest.raises(ValueError):
         d3.set_integrator("langevin")
     d3.set_integrator("brownian")
+
+
+def test_domain_exchange_refuses_the_langevin_integrator():
+    """Halo records carry x, y, theta and aux channels only: velocities, state under velocity Verlet, do not
+    travel, so the exchange must fail loudly rather than integrate ghosts with stale velocities."""
+    from swarmrl_b200.domain import DomainSwarm
+
+    rng = np.random.default_rng(1)
+    n, L = 2000, 250.0
+    pos = jittered_lattice(n, L, 2, rng)
+    d = DomainSwarm((L, L), 1e-3, 0.0, 3, _species(), wca_for([1.0]), exchange_every=5)
+    d.scatter(pos[:, :2], rng.uniform(0, 2 * np.pi, n))
+    d.run(5, 0)
+    d.sync()
+    d.sw.set_integrator("langevin")
+    with pytest.raises(RuntimeError, match="Brownian"):
+        d.exchange()
