@@ -47,7 +47,7 @@ VISION = dict(range=10.0, half_angle=np.pi / 2, n_cones=5)
 BYTES_PER_AGENT_STEP = 68  # 2-D steady-state step, read 44 B + write 24 B
 # dram__bytes_read.sum + dram__bytes_write.sum of one k_bd2d_resident launch (100 steps), from the ncu --set full
 # capture profiles/r01_k_bd2d_resident.ncu-rep (10.70 MB + 0.12 MB): the state is register / L2 resident
-NCU_DRAM_BYTES_PER_LAUNCH = 10.82e6  # dram__bytes_read + write of one k_bd2d_resident launch, profiles/r01_ncu_k_bd2d_resident_summary.txt
+NCU_DRAM_BYTES_PER_LAUNCH = 10.70e6  # dram__bytes_read + write of one k_bd2d_resident launch, profiles/r01_ncu_k_bd2d_resident_summary.txt
 METRIC = "agent_steps_per_sec_100k_agents"
 UNIT = "agent-steps/s"
 
