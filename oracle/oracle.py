@@ -278,6 +278,19 @@ class OracleSwarm:
         return out
 
 
+def position_observable(pos, ptype, particle_type, box_length):
+    """PositionObservable (/root/reference/swarmrl/observables/position.py:32-60): pos / box_length of the colloids
+    of `particle_type`, in colloid order."""
+    sel = np.asarray(ptype) == int(particle_type)
+    return np.asarray(pos, dtype=float)[sel] / np.asarray(box_length, dtype=float)
+
+
+def director_observable(dirs, ptype, particle_type):
+    """Director (/root/reference/swarmrl/observables/director.py:30-58): a copy of the director of each colloid of
+    `particle_type`, in colloid order."""
+    return np.asarray(dirs, dtype=float)[np.asarray(ptype) == int(particle_type)].copy()
+
+
 def decay_eval(kind, c0, c1, d):
     """swarm_decay_t: 1 linear c0 + c1 d, 2 exponential c0 exp(-c1 d), 3 inverse c0 / (d + c1)."""
     d = np.asarray(d, dtype=np.float64)
