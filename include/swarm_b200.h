@@ -35,6 +35,7 @@ extern "C" {
 
 #define SWARM_MAX_SPECIES 16
 #define SWARM_MAX_TYPES 8
+#define SWARM_MAX_NEIGHBORS 128 /* hard ceiling of the Verlet-list capacity (swarm_set_max_neighbors) */
 #define SWARM_ABI_VERSION 1
 
 typedef enum {
@@ -113,7 +114,9 @@ int swarm_set_species(swarm_t *s, int32_t n_species, const int32_t *type, const 
  * cut = sigma * 2^(1/6). */
 int swarm_set_wca(swarm_t *s, int32_t n_types, const double *sigma, const double *eps, const double *cut);
 
-/* constraints.add(ShapeBasedConstraint(Wall...)) on the box faces (espresso.py:667-711). */
+/* constraints.add(ShapeBasedConstraint(Wall...)) on the box faces (espresso.py:667-711).  The three arrays hold
+ * n_types entries (wall interaction of every particle type): call swarm_set_wca FIRST, it fixes n_types --
+ * otherwise SWARM_ERR_STATE. */
 int swarm_set_walls(swarm_t *s, int32_t enabled, const double *sigma, const double *eps, const double *cut);
 
 /* thermostat.set_brownian(kT, seed) (espresso.py:1180-1186) -- may be changed between runs */

@@ -324,13 +324,16 @@ def pair_field(pos, ptype, particle_type, sensing_type, box_length, kind, c0, c1
     return np.array(out)
 
 
+PHILOX_DOMAIN_POLICY = 0x706F6C696379  # counter word c2 of the policy's Gumbel noise (swarm_common.cuh)
+
+
 def policy_forward(obs, params, seed=0, ids=None, call=0, sample=False):
     """fp32 restatement of the reference's action path for the network of its tests
     (CI/espresso_tests/integration_tests/test_rl_trainers.py:17-26):
         h = relu(obs @ w1 + b1); logits = h @ wa + ba; value = h @ wv + bv      (flax Dense: x @ kernel + bias)
         log_prob = log(softmax(logits) + 1e-8)[idx]                             (networks/flax_network.py:180-192)
         idx = argmax(logits - log(-log(u)))                                     (sampling_strategies/gumbel_distribution.py:37-40)
-    u comes from the engine's documented Philox layout -- counter (call, 4 + 16 * (a // 4), 0, 0), key (id, seed),
+    u comes from the engine's documented Philox layout -- counter (call, 4 + 16 * (a // 4), "policy", 0), key (id, seed),
     u = ((r >> 11) + 0.5) / 2^53 for action a = word a % 4 -- not from JAX's threefry (unavailable offline)."""
     f = np.float32
     x = np.asarray(obs, dtype=np.float64).astype(f)
@@ -344,7 +347,7 @@ def policy_forward(obs, params, seed=0, ids=None, call=0, sample=False):
         pert = np.empty_like(logits)
         for r in range(n):
             for a0 in range(0, A, 4):
-                w = philox4x64((call, 4 + 16 * (a0 // 4), 0, 0), (int(ids[r]), int(seed)))
+                w = philox4x64((call, 4 + 16 * (a0 // 4), PHILOX_DOMAIN_POLICY, 0), (int(ids[r]), int(seed)))
                 for u in range(min(4, A - a0)):
                     uu = (float(int(w[u]) >> 11) + 0.5) / 9007199254740992.0
                     pert[r, a0 + u] = logits[r, a0 + u] - f(np.log(-np.log(uu)))

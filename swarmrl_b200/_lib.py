@@ -17,6 +17,7 @@ LIB_PATH = pathlib.Path(os.environ.get("SWARM_B200_LIB", PKG / "libswarm_b200.so
 
 MAX_SPECIES = 16
 MAX_TYPES = 8
+MAX_NEIGHBORS = 128  # SWARM_MAX_NEIGHBORS: hard ceiling of the Verlet capacity
 
 OK, ERR_INVALID, ERR_STATE, ERR_CUDA, ERR_OVERFLOW, ERR_NOMEM = 0, -1, -2, -3, -4, -5
 DECAY_NONE, DECAY_LINEAR, DECAY_EXP, DECAY_INVERSE = 0, 1, 2, 3

@@ -278,7 +278,7 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_resident(const __grid_c
     }
   }
   if (leader) {
-    ctl->steps_done = s;
+    ctl->steps_done = R.steps_base + s;
     if (s < R.n_steps) ctl->halted = 1;
     ctl->rebuild_flag[0] = 0; ctl->rebuild_flag[1] = 0; ctl->rebuild_flag[2] = 0;
   }
@@ -481,7 +481,7 @@ __global__ void __launch_bounds__(SW_STREAM_THREADS, SW_STREAM_MINB) k_bd2d_stre
     }
   }
   if (leader) {
-    ctl->steps_done = s;
+    ctl->steps_done = R.steps_base + s;
     if (s < R.n_steps) ctl->halted = 1;
     ctl->rebuild_flag[0] = 0; ctl->rebuild_flag[1] = 0; ctl->rebuild_flag[2] = 0;
   }
@@ -616,5 +616,5 @@ __global__ void __launch_bounds__(SW_ENV_THREADS) k_bd2d_env(const __grid_consta
       A.wx[i] = 0.0; A.wy[i] = 0.0; A.wz[i] = w + sw * gw[0];
     }
   }
-  if (env == 0 && lane == 0) ctl->steps_done = R.n_steps;
+  if (env == 0 && lane == 0) ctl->steps_done = R.steps_base + R.n_steps;
 }

@@ -127,6 +127,11 @@ int sw_cuda_fail(cudaError_t e, const char *what);
 // Philox4x64-10 (Salmon et al., SC'11).  Layout (documented in DESIGN.md, checked by the parity tests):
 // counter = (step, stream, 0, 0), key = (particle id, seed).
 // ---------------------------------------------------------------------------------------------
+// Counter word c2 separates the consumers of the per-particle key (id, seed): 0 = the integrators' thermostat streams
+// (counter (step, stream 0..5, 0, 0)); the policy's Gumbel noise (counter (call, 4 + 16 k, DOMAIN_POLICY, 0)) can
+// therefore never read the words of a thermostat kick, whatever `call` and `step` are.  Stream map: DESIGN.md section 3.
+#define SW_PHILOX_DOMAIN_POLICY 0x706f6c696379ULL /* "policy" */
+
 __host__ __device__ __forceinline__ void sw_mulhilo(u64 a, u64 b, u64 &hi, u64 &lo) {
 #ifdef __CUDA_ARCH__
   hi = __umul64hi(a, b);

@@ -39,6 +39,7 @@ struct RunArgs {
   int force_rebuild;
   double sd_gamma, sd_maxd;
   int particles_per_cta;  // resident kernel only
+  long long steps_base;   // steps completed by the earlier sub-launches of this swarm_run (sw_run_common splits long runs)
   // MODE_LV (velocity Verlet): iteration 0 of the launch is the force recalculation at the start of a chunk
   // (no closing half kick); the last iteration only closes the final step (no drift)
   int lv_first, lv_close;
@@ -538,7 +539,7 @@ __global__ void __launch_bounds__(SW_THREADS) k_persist(const __grid_constant__ 
     }
   }
   if (leader) {
-    ctl->steps_done = s;
+    ctl->steps_done = R.steps_base + s;
     if (s < R.n_steps) ctl->halted = 1;
     ctl->rebuild_flag[0] = 0; ctl->rebuild_flag[1] = 0; ctl->rebuild_flag[2] = 0;
   }
@@ -597,10 +598,10 @@ __device__ __forceinline__ void grid_barrier64(unsigned long long *counter, unsi
 // boundaries instead of grid barriers.  Used as a cross-check of the persistent kernel.
 // ---------------------------------------------------------------------------------------------
 template <int DIM>
-__global__ void k_np_check(const __grid_constant__ DevParams P, DevArrays A, int force) {
+__global__ void k_np_check(const __grid_constant__ DevParams P, DevArrays A, int force, long long steps_base) {
   long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (ldcg(&A.ctl->halted)) return;
-  if (i == 0) A.ctl->steps_done = 0;
+  if (i == 0) A.ctl->steps_done = steps_base;
   if (force) { if (i == 0) A.ctl->rebuild_flag[0] = 1; return; }
   if (i < A.n && moved_since_build<DIM>(P, A, 0, i)) A.ctl->rebuild_flag[0] = 1;
 }
@@ -629,7 +630,7 @@ __global__ void k_np_step(const __grid_constant__ DevParams P, DevArrays A, RunA
   Ctl *ctl = A.ctl;
   if (ldcg(&ctl->halted)) return;
   if (ldcg(&ctl->overflow)) return;  // k_np_halt (next launch) latches `halted`
-  if (i == 0) { ctl->rebuild_flag[(s + 2) % 3] = 0; ctl->steps_done = s + 1; }
+  if (i == 0) { ctl->rebuild_flag[(s + 2) % 3] = 0; ctl->steps_done = R.steps_base + s + 1; }
   if (i >= A.n) return;
   if (phase_step<DIM, NOISE>(P, A, R, (int)(s & 1), R.step0 + (u64)s, s == R.n_steps - 1, i))
     ctl->rebuild_flag[(s + 1) % 3] = 1;
@@ -638,9 +639,9 @@ __global__ void k_np_halt(DevArrays A) {
   if (blockIdx.x == 0 && threadIdx.x == 0 && A.ctl->overflow) A.ctl->halted = 1;
 }
 template <int DIM>
-__global__ void k_np_finish(DevArrays A) {
+__global__ void k_np_finish(DevArrays A, long long steps_base) {
   long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  long long s = ldcg(&A.ctl->steps_done);
+  long long s = ldcg(&A.ctl->steps_done) - steps_base;   // steps of THIS sub-launch: its parity says where the result lies
   if (i == 0) { A.ctl->rebuild_flag[0] = 0; A.ctl->rebuild_flag[1] = 0; A.ctl->rebuild_flag[2] = 0; }
   if (!(s & 1) || i >= A.n) return;
   A.x[0][i] = A.x[1][i]; A.y[0][i] = A.y[1][i];
@@ -695,7 +696,9 @@ __global__ void k_apply_new_direction(int n_dims, long long n, const int *has_nd
       // axis = (0,0,round(cross_z/|cross|)); cross = old x new
       double cx = s * nz, cy = -c * nz, cz = c * ny - s * nx;
       double cn = sqrt(cx * cx + cy * cy + cz * cz);
-      double az = rint(cz / cn);
+      // exactly antiparallel: old x new = 0 and the reference's axis is 0/0 (its round(nan) raises, which the host
+      // side of manage_forces reproduces); the device never writes a NaN angle -- it turns by +pi
+      double az = (cn > 0.0) ? rint(cz / cn) : 1.0;
       theta[i] += az * ang;
     }
   } else {
@@ -878,11 +881,15 @@ extern "C" int swarm_set_wca(swarm_t *s, int32_t n_types, const double *sigma, c
 extern "C" int swarm_set_walls(swarm_t *s, int32_t enabled, const double *sigma, const double *eps, const double *cut) {
   if (!s) return SWARM_ERR_INVALID;
   DevParams &P = s->P;
-  P.walls = enabled ? 1 : 0;
-  if (enabled)
-    for (int a = 0; a < SW_T && a < (P.n_types > 0 ? P.n_types : SW_T); ++a) {
+  if (enabled) {
+    // the arrays hold one entry per particle type: their length is only known once the WCA table is
+    if (!s->wca_set) { sw_set_error("call swarm_set_wca before swarm_set_walls (it fixes the number of types)"); return SWARM_ERR_STATE; }
+    if (!sigma || !eps || !cut) { sw_set_error("wall tables must be given"); return SWARM_ERR_INVALID; }
+    for (int a = 0; a < P.n_types; ++a) {
       P.wall_sigma[a] = sigma[a]; P.wall_eps[a] = eps[a]; P.wall_cut[a] = cut[a];
     }
+  }
+  P.walls = enabled ? 1 : 0;
   return SWARM_OK;
 }
 
@@ -1143,7 +1150,7 @@ static int sw_launch_stream(swarm *s, const RunArgs &R, cudaStream_t st) {
 template <int DIM, bool NOISE>
 static int sw_launch_np(swarm *s, const RunArgs &R, cudaStream_t st) {
   const int T = SW_THREADS, B = sw_blocks(s->A.n > 0 ? s->A.n : 1, T);
-  k_np_check<DIM><<<B, T, 0, st>>>(s->P, s->A, R.force_rebuild);
+  k_np_check<DIM><<<B, T, 0, st>>>(s->P, s->A, R.force_rebuild, R.steps_base);
   s->launches += 1;
   for (long long k = 0; k < R.n_steps; ++k) {
     k_np_clear<DIM><<<B, T, 0, st>>>(s->P, s->A, k);
@@ -1153,7 +1160,7 @@ static int sw_launch_np(swarm *s, const RunArgs &R, cudaStream_t st) {
     k_np_step<DIM, NOISE><<<B, T, 0, st>>>(s->P, s->A, R, k);
     s->launches += 5;
   }
-  k_np_finish<DIM><<<B, T, 0, st>>>(s->A);
+  k_np_finish<DIM><<<B, T, 0, st>>>(s->A, R.steps_base);
   s->launches += 1;
   SW_CUDA(cudaGetLastError());
   return SWARM_OK;
@@ -1202,6 +1209,7 @@ static int sw_run_common(swarm *s, RunArgs R, cudaStream_t st) {
     RunArgs Rc = R;
     Rc.n_steps = (R.n_steps - done < max_chunk) ? R.n_steps - done : max_chunk;
     Rc.step0 = R.step0 + (u64)done;
+    Rc.steps_base = done;   // the kernels report steps_base + their own count: steps of the whole swarm_run
     if (done > 0) Rc.force_rebuild = 0;
     Rc.lv_first = (lv && done == 0 && !lv_resume) ? 1 : 0;
     Rc.lv_close = (lv && done + Rc.n_steps == R.n_steps) ? 1 : 0;
@@ -1333,17 +1341,17 @@ static int sw_force_rebuild(swarm *s, cudaStream_t st) {
   const int T = SW_THREADS, B = sw_blocks(s->A.n, T);
   // phases as separate launches; flag slot 0 forced
   if (s->P.n_dims == 2) {
-    k_np_check<2><<<B, T, 0, st>>>(s->P, s->A, 1);
+    k_np_check<2><<<B, T, 0, st>>>(s->P, s->A, 1, 0);
     k_np_clear<2><<<B, T, 0, st>>>(s->P, s->A, 0);
     k_np_insert<<<B, T, 0, st>>>(s->A, 0);
     k_np_search<2><<<B, T, 0, st>>>(s->P, s->A, 0);
-    k_np_finish<2><<<B, T, 0, st>>>(s->A);
+    k_np_finish<2><<<B, T, 0, st>>>(s->A, 0);
   } else {
-    k_np_check<3><<<B, T, 0, st>>>(s->P, s->A, 1);
+    k_np_check<3><<<B, T, 0, st>>>(s->P, s->A, 1, 0);
     k_np_clear<3><<<B, T, 0, st>>>(s->P, s->A, 0);
     k_np_insert<<<B, T, 0, st>>>(s->A, 0);
     k_np_search<3><<<B, T, 0, st>>>(s->P, s->A, 0);
-    k_np_finish<3><<<B, T, 0, st>>>(s->A);
+    k_np_finish<3><<<B, T, 0, st>>>(s->A, 0);
   }
   s->launches += 5;
   SW_CUDA(cudaGetLastError());

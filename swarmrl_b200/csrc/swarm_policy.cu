@@ -75,7 +75,7 @@ __global__ void __launch_bounds__(POL_THREADS) k_policy_forward(long long n, Pol
     float bv = -INFINITY;
     for (int a0 = 0; a0 < A; a0 += 4) {
       u64 r[4];
-      sw_philox4x64_10(call, 4ULL + (u64)(a0 >> 2) * 16ULL, 0ULL, 0ULL, pid, seed, r);
+      sw_philox4x64_10(call, 4ULL + (u64)(a0 >> 2) * 16ULL, SW_PHILOX_DOMAIN_POLICY, 0ULL, pid, seed, r);
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
         const int a = a0 + u;

@@ -206,7 +206,7 @@ class DeviceSwarm:
                 return st
             if not grow:
                 raise OverflowError("Verlet list capacity exceeded")
-            self.set_max_neighbors(min(128, max(2 * st.capacity, st.max_neighbors_seen + 8)))
+            self._grow_neighbors(st)
 
     def relax_checked(self, n_iter=1000, gamma=0.1, max_disp=0.1):
         done = 0
@@ -216,7 +216,16 @@ class DeviceSwarm:
             done += int(st.steps_done)
             if not st.overflow:
                 return st
-            self.set_max_neighbors(min(128, max(2 * st.capacity, st.max_neighbors_seen + 8)))
+            self._grow_neighbors(st)
+
+    def _grow_neighbors(self, st):
+        """Double the Verlet capacity after an overflow; at the hard ceiling there is nothing left to grow, and
+        retrying with the same capacity would overflow again at once (the run would never end)."""
+        if st.capacity >= _lib.MAX_NEIGHBORS:
+            raise OverflowError(
+                f"Verlet list capacity exceeded: a particle has more than {_lib.MAX_NEIGHBORS} neighbours within "
+                f"cut-off + skin (max_neighbors_seen >= {st.max_neighbors_seen}); lower the density or the skin")
+        self.set_max_neighbors(min(_lib.MAX_NEIGHBORS, max(2 * st.capacity, st.max_neighbors_seen + 8)))
 
     def set_max_neighbors(self, cap):
         _lib.check(self.lib.swarm_set_max_neighbors(self.h, int(cap)))

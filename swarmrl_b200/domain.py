@@ -278,6 +278,13 @@ class DomainSwarm:
                                     (4, "local capacity exceeded")) if err & bit]
             raise OverflowError("domain exchange failed: " + ", ".join(why))
         self.n, self.n_owned = int(self.counts_host[self.cur, 0]), int(self.counts_host[self.cur, 1])
+        # a Verlet-list overflow halts the integrator kernels of this rank (every later launch returns at once) while
+        # the exchanges would keep shipping the frozen slab: surface it here instead of returning stale positions
+        st = self.sw.stats()
+        if st.overflow:
+            raise OverflowError(
+                f"Verlet list capacity exceeded on rank {self.plan['rank']} (capacity {st.capacity}, "
+                f"max_neighbors_seen >= {st.max_neighbors_seen}): raise max_neighbors or lower the skin")
         return self.n
 
     # ------------------------------------------------------------ integration
@@ -293,6 +300,7 @@ class DomainSwarm:
             done += m
 
     def stats(self):
+        """Counters of the local handle; raises like `sync` when an exchange or a Verlet list overflowed."""
         self.sync()
         return self.sw.stats()
 

@@ -577,6 +577,15 @@ class SwarmEngine(Engine):
                 has[i] = 1
         self._backend.set_actions_host(f, tq)
         if has.any():
+            if self.n_dims == 2:
+                # espresso.py:1240-1248: an exactly antiparallel new_direction has old x new = 0, the rotation axis is
+                # 0/0 and `round(nan)` raises ValueError there; same here instead of an arbitrary turn
+                old = self.colloids._snapshot()[2]
+                sel = has.astype(bool)
+                ang = np.arccos(np.einsum("ij,ij->i", nd[sel], old[sel]))
+                cr = np.cross(old[sel], nd[sel])
+                if np.any((ang > 1e-6) & (np.linalg.norm(cr, axis=1) == 0.0)):
+                    raise ValueError("cannot convert float NaN to integer")
             self._backend.set_new_directions_host(nd, has)
             self._backend.apply_new_direction()
             self._state_version += 1

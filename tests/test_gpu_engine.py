@@ -359,3 +359,72 @@ def test_director_of_large_angles(scale):
     assert st.steps_done == 50
     p, v, e = d.particle_data_host()
     assert rel_err(p, o.pos) < 1e-12 and rel_err(v, o.velocities) < 1e-9
+
+
+def test_overflow_at_the_capacity_ceiling_raises_instead_of_looping():
+    """More than SWARM_MAX_NEIGHBORS particles within cut-off + skin of each other: the Verlet capacity cannot
+    grow past its ceiling, so relax_checked / run_checked must raise (they used to retry for ever)."""
+    rng = np.random.default_rng(4)
+    n, L = 200, 40.0
+    sp, wca = species_for([1.0]), wca_for([1.0])
+    pos = np.zeros((n, 3)); pos[:, :2] = 20.0 + rng.uniform(-0.4, 0.4, (n, 2))
+    _, d = make_pair(2, (L,) * 3, True, 1e-3, 0.0, 1, sp, wca, pos, np.zeros(n, dtype=np.int32), theta=np.zeros(n))
+    with pytest.raises(OverflowError, match="128"):
+        d.relax_checked(10)
+    _, d2 = make_pair(2, (L,) * 3, True, 1e-3, 0.0, 1, sp, wca, pos, np.zeros(n, dtype=np.int32), theta=np.zeros(n))
+    with pytest.raises(OverflowError):
+        d2.run_checked(5, 0)
+
+
+@pytest.mark.parametrize("persistent", [True, False])
+def test_steps_done_counts_the_whole_run_across_sub_launches(persistent):
+    """swarm_run splits long runs into sub-launches (8192 steps, 1024 without the persistent kernels); steps_done
+    is the count over the WHOLE run, and a run resumed after it equals one uninterrupted run."""
+    n_steps = 10000 if persistent else 2500
+    o, d, sp = _swarm2d(n=256, L=64.0, device_kw=dict(persistent=persistent))
+    set_actions(o, d, np.full(256, 5.0 * sp[0]["gamma_t"][0]), np.zeros((256, 3)))
+    d.run(n_steps, 0)
+    st = d.stats()
+    assert st.steps_done == n_steps and st.steps_requested == n_steps and not st.overflow
+    o.bd_steps(0, n_steps, mode=2)
+    p, _, _ = d.particle_data_host()
+    assert rel_err(p, o.pos) < 1e-8
+
+
+def test_overflow_in_a_later_sub_launch_resumes_at_the_right_step():
+    """A list overflow after the first sub-launch: steps_done must include the completed sub-launches so that
+    run_checked resumes at step0 + steps_done (it used to replay the first 8192 steps' noise)."""
+    rng = np.random.default_rng(31)
+    n, L = 128, 44.0
+    sp, wca = species_for([1.0]), wca_for([1.0])
+    pos = jittered_lattice(n, L, 2, rng, jitter=0.1)
+    # every particle swims towards the box centre: the swarm compacts and the 2-entry lists overflow late
+    th = np.arctan2(L / 2 - pos[:, 1], L / 2 - pos[:, 0])
+    o, d = make_pair(2, (L,) * 3, False, 1e-3, 0.0, 9, sp, wca, pos, np.zeros(n, dtype=np.int32), theta=th,
+                     device_kw=dict(max_neighbors=2, skin=0.4))
+    f = np.full(n, 0.15 * sp[0]["gamma_t"][0])   # first particle with 3 neighbours within 2.4 at step ~12 800 (oracle)
+    set_actions(o, d, f, np.zeros((n, 3)))
+    total = 20000
+    d.run(total, 0)
+    st = d.stats()
+    assert st.overflow == 1 and 0 < st.steps_done < total, (st.overflow, st.steps_done)
+    first = int(st.steps_done)
+    assert first > 8192, "the overflow was meant to happen after the first sub-launch; re-tune the test swarm"
+    o.bd_steps(0, first, mode=2)
+    p, _, _ = d.particle_data_host()
+    assert rel_err(p, o.pos) < 1e-8          # steps_done is the step the state actually stands at
+    d.set_max_neighbors(16)
+    st = d.run_checked(total - first, first)
+    o.bd_steps(first, total - first, mode=2)
+    p, _, _ = d.particle_data_host()
+    assert rel_err(p, o.pos) < 1e-7
+
+
+def test_antiparallel_new_direction_turns_by_pi_without_nan():
+    """espresso.py:1240-1248 has a 0/0 axis here; the device kernel turns by +pi and never stores a NaN angle."""
+    o, d, _ = _swarm2d(n=16)
+    e0 = d.directors().cpu().numpy().T.copy()
+    d.set_new_directions_host(-e0, np.ones(16, dtype=np.int32))
+    d.apply_new_direction()
+    e1 = d.directors().cpu().numpy().T
+    assert np.all(np.isfinite(e1)) and np.allclose(e1, -e0, atol=1e-12)
