@@ -17,6 +17,15 @@ e2e    = the same slice through the host-buffer C-ABI (swarm_set_actions_host ->
          D2H of the observable and the reward mean), actions coming from pinned host memory.
 N > 1  : ensemble sharding -- every rank advances its own independent 100k-agent swarm (weak scaling,
          no data-path collective; torch.distributed only for the barrier and the max-over-ranks time).
+Two more records ride on the same line, measured in the same invocation with the same timing rules, because
+north_star names them and they are what exercises the N GPUs TOGETHER:
+  c5_domain : BASELINE config 5, ONE 8,000,000-particle swarm slab-decomposed over the N GPUs (NCCL halo +
+              migration exchange every k steps, swarmrl_b200/domain.py) -- strong scaling; rank 0 also times
+              the same swarm on its GPU alone, so `efficiency_vs_n1` is measured inside one run on one box;
+              plus `parity_selfcheck` (a 20k-particle swarm over the live NCCL group against the single-GPU
+              engine, noise on) and, for N > 1, `parity_full` (all 8M particles against the one-GPU run).
+  c3_envs   : BASELINE config 3, 4,096 environments x 32 agents sharded E/N per GPU (strong, as BASELINE.json
+              states it) and 4,096 per GPU (weak); env-steps/s.
 --impl reference : ESPResSo is not installable here, so the reference arm times the CPU oracle
          (oracle/swarm_oracle.c, OpenMP, all host threads) on a bounded sample of the same workload.
 """
@@ -392,6 +401,12 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     dev_ms, e2e_ms = float(t[0]), float(t[1])
+    extras = None
+    if not args.no_extra:
+        del ro.flush_buf
+        ro.d.close()
+        torch.cuda.empty_cache()
+        extras = extra_records(args, world, rank, local)
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -428,9 +443,65 @@ def run_ours(args):
         line["cpu_baseline"]["single_thread_value"] = cb1["value"]
         from oracle import oracle as _orc
         _orc.set_num_threads(cb["cores"])
+    line.update(extras or {})
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+def extra_records(args, world, rank, local):
+    """c5_domain and c3_envs (see the module docstring); every rank takes part, rank 0 gets the records."""
+    import torch
+    import torch.distributed as dist
+
+    from tools import bench_domain, bench_envs
+
+    out = {}
+    # ---- C3: batched environments, ensemble-sharded --------------------------------------------------
+    strong = bench_envs.measure(world, rank, local, args.c3_envs, weak=False, slices=args.c3_slices)
+    weak = strong if world == 1 else bench_envs.measure(world, rank, local, args.c3_envs, weak=True, slices=args.c3_slices)
+    keys = ("value", "unit", "agent_steps_per_s", "envs", "envs_per_gpu", "ms_per_slice", "slices", "launches_per_slice")
+    out["c3_envs"] = {"workload": f"C3: {args.c3_envs} independent environments x 32 agents, 100 steps/slice, ConcentrationField "
+                                  "observable -> counter-RNG policy -> 4-action table -> Brownian steps + WCA -> GradientSensing mean",
+                      "metric": "env_steps_per_sec_batched_rollouts", "n_gpus": world,
+                      "strong": {k: strong[k] for k in keys}, "weak": {k: weak[k] for k in keys},
+                      "collective": "none on the data path (one all-reduce of the reward sum per measurement)"}
+    # ---- C5: one large swarm, domain-decomposed ------------------------------------------------------
+    swarm = bench_domain.build_swarm(args.c5_agents, 0.10)
+    kw = dict(steps=STEPS_PER_SLICE, slices=args.c5_slices, warmup=2, k=args.c5_k, skin=args.c5_skin, margin=0.15)
+    rec, dom = bench_domain.measure(world, rank, local, swarm, keep=True, **kw)
+    rec["workload"] = (f"C5: {args.c5_agents:,}-particle single swarm, 2-D periodic phi=0.10, WCA + Brownian dynamics kT=300K dt=1e-3, "
+                       f"{STEPS_PER_SLICE} steps/slice + GradientSensing reward mean; {world} slab(s), redundant-halo exchange every k steps")
+    if world > 1:
+        full_n, owned = bench_domain.gather_owned(dom, world, rank)
+        dom.close()
+        del dom
+        torch.cuda.empty_cache()
+        dist.barrier()
+        if rank == 0:
+            # the same swarm on this GPU alone, same parameters: the N = 1 point of the strong-scaling curve
+            one, dom1 = bench_domain.measure(1, 0, local, swarm, keep=True, **kw)
+            full_1, _ = bench_domain.gather_owned(dom1, 1, 0)
+            dom1.close()
+            rec["n1_same_run"] = {k: one[k] for k in ("value", "ms_per_slice", "rebuilds", "redundancy")}
+            rec["efficiency_vs_n1"] = rec["value"] / (world * one["value"])
+            err = max(bench_domain.rel_err(full_n[c], full_1[c]) for c in range(3))
+            rec["parity_full"] = {"n_agents": args.c5_agents, "steps": (2 + args.c5_slices) * STEPS_PER_SLICE, "noise": True,
+                                  "against": "the same swarm on one GPU (self-exchanging slab), same kernels",
+                                  "max_rel_err_x_y_theta": err, "every_particle_owned_once": bool(owned == args.c5_agents),
+                                  "note": "chaotic growth of rounding differences between local frames over 700 steps of contacts "
+                                          "is expected above 1e-12; the per-step bound (1e-9) is what parity_selfcheck pins"}
+        dist.barrier()
+    else:
+        dom.close()
+        rec["efficiency_vs_n1"] = 1.0
+    chk = bench_domain.parity_selfcheck(world, rank, local)
+    if rank == 0:
+        rec["parity_selfcheck"] = chk
+        tl = rec["timeline_ms_per_slice_max_over_ranks"]
+        rec["limiting_term"] = max(tl, key=tl.get)
+    out["c5_domain"] = rec
+    return out if rank == 0 else None
 
 
 def main():
@@ -442,6 +513,13 @@ def main():
     ap.add_argument("--skin", type=float, default=2.0, help="Verlet skin (performance only; espresso.py:269 uses 0.4)")
     ap.add_argument("--cpu-steps", type=int, default=100, help="BD steps of the cpu_baseline sample")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="skip the c5_domain / c3_envs records")
+    ap.add_argument("--c5-agents", type=int, default=8_000_000)
+    ap.add_argument("--c5-slices", type=int, default=5)
+    ap.add_argument("--c5-k", type=int, default=33, help="steps between halo exchanges (halo = k * r_cut * 1.15)")
+    ap.add_argument("--c5-skin", type=float, default=2.0)
+    ap.add_argument("--c3-envs", type=int, default=4096)
+    ap.add_argument("--c3-slices", type=int, default=50)
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -67,8 +67,12 @@ __device__ __forceinline__ Bd2dSelf bd2d_self_forces(const DevParams &P, int ti,
   return o;
 }
 
-template <bool NOISE>
-__global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_resident(const __grid_constant__ DevParams P, DevArrays A, RunArgs R) {
+// PIPE = 1 (default): the Philox words of step s+1 are drawn between the ISSUE of step s's neighbour loads and their
+// first use, and turned into normals (Box-Muller) behind the grid barrier -- so both waits of a step, the L2 round trip
+// of the neighbour positions and the barrier, are covered by work that depends on the particle alone.  PIPE = 0 keeps
+// the whole draw behind the barrier (round 1's order; SWARM_B200_RES_PIPE=0 selects it for A/B runs).
+template <bool NOISE, int PIPE>
+__global__ void __maxnreg__(SW_RES_MAXREG) k_bd2d_resident(const __grid_constant__ DevParams P, DevArrays A, RunArgs R) {
   Ctl *ctl = A.ctl;
   if (ldcg(&ctl->halted)) return;
   unsigned int epoch = 0;
@@ -127,6 +131,7 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_resident(const __grid_c
     sf = bd2d_self_forces(P, ti, xi, yi, ex, ey, fsw);
     if (NOISE) swm_gaussians_xyt(P.seed, pid, R.step0, g0, g1, g3);
   }
+  u64 rw[4] = {0, 0, 0, 0};   // PIPE: Philox words of the next step, carried from the load shadow to the barrier shadow
   int cnt = 0, nb[SW_RES_NBR];
   const int self_entry = act ? (int)i : 0;
 #pragma unroll
@@ -174,6 +179,8 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_resident(const __grid_c
         const int j = nb[k] & SW_IDX_MASK;
         xj[k] = ldcg(&A.x[cur][j]); yj[k] = ldcg(&A.y[cur][j]);
       }
+      // ---- shadow of those loads: the next step's Philox block (integer pipe, depends on (seed, id, step) only) ----
+      if (NOISE && PIPE && !last) swm_philox_xyt(P.seed, pid, R.step0 + (u64)(s + 1), rw);
       double Fx = 0.0, Fy = 0.0;
 #pragma unroll
       for (int k = 0; k < SW_RES_NBR; ++k)
@@ -247,7 +254,10 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_resident(const __grid_c
         // ---- particle-local work of step s+1, overlapping the barrier ----------------------------
         swm_sincos(th, ey, ex);
         sf = bd2d_self_forces(P, ti, xi, yi, ex, ey, fsw);
-        if (NOISE) swm_gaussians_xyt(P.seed, pid, R.step0 + (u64)(s + 1), g0, g1, g3);
+        if (NOISE) {
+          if (PIPE) swm_boxmuller_xyt(rw, g0, g1, g3);
+          else swm_gaussians_xyt(P.seed, pid, R.step0 + (u64)(s + 1), g0, g1, g3);
+        }
       }
     }
     SW_TICK(4);

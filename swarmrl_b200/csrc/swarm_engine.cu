@@ -588,7 +588,8 @@ __device__ __forceinline__ void grid_barrier64(unsigned long long *counter, unsi
   __syncthreads();
 }
 
-#define SW_RES_MAXT 768  // resident kernel: at most 768 threads per SM (<= 85 registers each)
+#define SW_RES_MAXT 736  // resident kernel: at most 23 warps per SM (22 particle warps = 104k particles on 148 SMs): 88 registers each
+#define SW_RES_MAXREG 88  // 65536 registers / 736 threads, rounded down to the allocation unit of 8
 #define SW_RES_NBR 4  // neighbour entries of the Verlet list kept in registers by the resident kernel
 
 #include "swarm_bd2d.cuh"  // k_bd2d_resident: the hot kernel of the 2-D rollout
@@ -691,6 +692,7 @@ __global__ void k_apply_new_direction(int n_dims, long long n, const int *has_nd
     double s, c;
     sincos(theta[i], &s, &c);
     double dot = nx * c + ny * s;  // old director z = 0
+    dot = fmin(1.0, fmax(-1.0, dot));   // rounding may leave |dot| = 1 + 1 ulp, whose acos is NaN (= "no turn" above)
     double ang = acos(dot);
     if (ang > 1e-6) {
       // axis = (0,0,round(cross_z/|cross|)); cross = old x new
@@ -1080,9 +1082,9 @@ static int sw_launch_persist(swarm *s, const RunArgs &R, cudaStream_t st) {
 }
 
 // resident 2-D kernel: one particle per thread, every CTA co-resident
-template <bool NOISE>
+template <bool NOISE, int PIPE>
 static int sw_launch_resident(swarm *s, const RunArgs &R, cudaStream_t st, bool *fits) {
-  auto kern = k_bd2d_resident<NOISE>;
+  auto kern = k_bd2d_resident<NOISE, PIPE>;
   // one CTA per SM (or fewer, larger ones): the grid barrier sees <= num_sms arrivals and the
   // particles are spread over the SMs to within one warp
   // one CTA per SM, the particles spread evenly over them; + 32: warp 0 of every CTA is the barrier warp
@@ -1224,7 +1226,9 @@ static int sw_run_common(swarm *s, RunArgs R, cudaStream_t st) {
       continue;
     }
     if (s->persistent && s->P.n_dims == 2 && R.mode == MODE_BD && !getenv("SWARM_B200_NO_RESIDENT")) {
-      rc = noise ? sw_launch_resident<true>(s, Rc, st, &done_resident) : sw_launch_resident<false>(s, Rc, st, &done_resident);
+      static const bool pipe = !(getenv("SWARM_B200_RES_PIPE") && atoi(getenv("SWARM_B200_RES_PIPE")) == 0);
+      rc = !noise ? sw_launch_resident<false, 0>(s, Rc, st, &done_resident)
+                  : (pipe ? sw_launch_resident<true, 1>(s, Rc, st, &done_resident) : sw_launch_resident<true, 0>(s, Rc, st, &done_resident));
       if (rc) return rc;
     }
     if (done_resident) {

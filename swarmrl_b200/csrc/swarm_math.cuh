@@ -130,6 +130,20 @@ __device__ __forceinline__ void swm_gaussians_xyt(u64 seed, u64 id, u64 step, do
   g0 = m0 * c0; g1 = m0 * s0; g3 = m1 * s1;
 }
 
+// The same three normals from Philox words drawn earlier (swm_philox_xyt): the resident kernel draws the words of
+// step s+1 in the shadow of step s's neighbour loads and transforms them in the shadow of the grid barrier.
+__device__ __forceinline__ void swm_philox_xyt(u64 seed, u64 id, u64 step, u64 r[4]) {
+  swm_philox4x64_10(step, 0ULL, 0ULL, 0ULL, id, seed, r);
+}
+__device__ __forceinline__ void swm_boxmuller_xyt(const u64 r[4], double &g0, double &g1, double &g3) {
+  const double m0 = swm_sqrt(-2.0 * swm_log01(swm_u01(r[0])));
+  const double m1 = swm_sqrt(-2.0 * swm_log01(swm_u01(r[2])));
+  double s0, c0, s1, c1;
+  swm_sincos2pi(r[1], s0, c0);
+  swm_sincos2pi(r[3], s1, c1);
+  g0 = m0 * c0; g1 = m0 * s0; g3 = m1 * s1;
+}
+
 // (sin, cos)(theta) of the 2-D director.  theta / (2 pi) with a two-term reciprocal (product error recovered by one
 // fma), quadrant by the round-to-nearest magic constant, then the polynomials of swm_sincos2pi on t in [-1/8, 1/8]
 // turns: <= 1.2e-16 absolute against mpmath for |theta| <= 1e6 (tools/gen_coeffs.py), no slow-path call in the hot

@@ -153,6 +153,11 @@ class DomainSwarm:
         self.since_exchange = 0
         self.exchanges = 0
         self.cur = 0
+        # profile = True brackets every phase with CUDA events (asynchronous, no host sync): `timeline()` then tells
+        # how a slice splits into integration, exchange (pack + transport + merge, i.e. including the wait for the
+        # slab neighbours) and reward evaluation
+        self.profile = False
+        self._events = []
 
     # ---------------------------------------------------------------- storage
     def _alloc(self, cap, buf_cap):
@@ -248,6 +253,35 @@ class DomainSwarm:
     def _stream(self):
         return self.sw._stream()
 
+    # --------------------------------------------------------------- timeline
+    def _timed(self, kind):
+        swarm = self
+
+        class _Span:
+            def __enter__(self):
+                if swarm.profile:
+                    self.e0 = swarm.torch.cuda.Event(enable_timing=True)
+                    self.e1 = swarm.torch.cuda.Event(enable_timing=True)
+                    self.e0.record()
+
+            def __exit__(self, *exc):
+                if swarm.profile:
+                    self.e1.record()
+                    swarm._events.append((kind, self.e0, self.e1))
+
+        return _Span()
+
+    def timeline_reset(self):
+        self._events = []
+
+    def timeline(self):
+        """Milliseconds per phase since `timeline_reset` (synchronises)."""
+        self.torch.cuda.current_stream(self.dev).synchronize()
+        out = {"run_ms": 0.0, "exchange_ms": 0.0, "obs_ms": 0.0}
+        for kind, e0, e1 in self._events:
+            out[kind + "_ms"] += e0.elapsed_time(e1)
+        return out
+
     # --------------------------------------------------------------- exchange
     def exchange(self):
         """halo refresh + migration, enqueued only: the new particle count stays on the device (see `sync`)."""
@@ -293,9 +327,11 @@ class DomainSwarm:
         done, k = 0, self.plan["k"]
         while done < n_steps:
             if self.since_exchange >= k:
-                self.exchange()
+                with self._timed("exchange"):
+                    self.exchange()
             m = min(k - self.since_exchange, n_steps - done)
-            _lib.check(self.lib.swarm_run(self.h, int(m), int(step0 + done), self._stream()))
+            with self._timed("run"):
+                _lib.check(self.lib.swarm_run(self.h, int(m), int(step0 + done), self._stream()))
             self.since_exchange += m
             done += m
 
@@ -324,12 +360,13 @@ class DomainSwarm:
         a = self._dd(self.local)
         s3 = (C.c_double * 3)(*[float(v) for v in src])
         b2 = (C.c_double * 2)(float(box_length[0]), float(box_length[1]))
-        _lib.check(self.lib.swarm_dd_obs_field(self.h, self.cap, self.counts[self.cur].data_ptr(), C.byref(a), self.plan["x_offset"], self.plan["box_x"], s3, b2,
-                                               int(decay), float(c0), float(c1), float(scale), int(bool(clip)),
-                                               int(bool(init_only)), self.out.data_ptr(), self._stream()))
-        red = self.sw.reduce_mean(self.out)      # slots past the live count were written as 0
-        tot = red[:1].clone()
-        self.transport.all_reduce_sum(tot)
+        with self._timed("obs"):
+            _lib.check(self.lib.swarm_dd_obs_field(self.h, self.cap, self.counts[self.cur].data_ptr(), C.byref(a), self.plan["x_offset"], self.plan["box_x"], s3, b2,
+                                                   int(decay), float(c0), float(c1), float(scale), int(bool(clip)),
+                                                   int(bool(init_only)), self.out.data_ptr(), self._stream()))
+            red = self.sw.reduce_mean(self.out)      # slots past the live count were written as 0
+            tot = red[:1].clone()
+            self.transport.all_reduce_sum(tot)
         return self.out, torch.cat([tot, tot / float(self.n_global)])
 
     def close(self):
