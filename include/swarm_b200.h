@@ -156,6 +156,22 @@ int swarm_sync_stats(swarm_t *s, void *stream, swarm_stats_t *out);
  * library was built with -DSW_TIMING, `python -m swarmrl_b200.build --timing`); synchronises the device. */
 int swarm_debug_timing(swarm_t *s, int64_t out8[8]);
 
+/* Spatial tiling of the 2-D Brownian chunk (csrc/swarm_tiled.cuh, csrc/swarm_sort.cuh).  ESPResSo stores its
+ * particles by cell of the regular decomposition selected at espresso.py:267-270; here the library keeps a spatially
+ * sorted slot order (cell hash, counting sort, cell-start scan) beside the caller's id-indexed arrays and gives every
+ * CTA a compact tile.  mode: 0 = off, 1 = automatic (swarms of >= 4096 particles; the default), 2 = whenever the swarm
+ * fits one particle per thread.  resort_interval: launches between two sorts (<= 0 keeps the current value).
+ * Trajectories do not depend on any of this (forces are summed in ascending particle id, noise is keyed by id). */
+int swarm_set_tiling(swarm_t *s, int32_t mode, int32_t resort_interval);
+/* out8: [0] 1 if the Verlet list currently lives in the tiled kernel's slot space (the last Brownian run was tiled),
+ * [1] rebuild cadence K, [2] steps integrated on the current list, [3] periods rolled back so far, [4] sum of
+ * partner CTAs over all rebuilds, [5] spatial sorts so far, [6] CTAs, [7] slots per CTA.  Synchronises the device. */
+int swarm_tiling_stats(swarm_t *s, int64_t out8[8]);
+/* The tiled kernel's OWN Verlet list as it stands (built at the last in-kernel rebuild, slots mapped back to particle
+ * ids), every ordered pair sorted by (i,j) -- for the bit-exact list check of that path.  SWARM_ERR_STATE unless the
+ * last run was tiled. */
+int swarm_tiled_neighbors_dump(swarm_t *s, int32_t *pairs_host, int64_t cap, int64_t *count);
+
 /* Grow the Verlet capacity after an overflow (invalidates the current list). */
 int swarm_set_max_neighbors(swarm_t *s, int32_t max_neighbors);
 
@@ -171,8 +187,12 @@ int swarm_cell_index(swarm_t *s, const int32_t nc[3], int32_t *cell_host);
 /* total force on every particle at the current state (debug / parity), device out */
 int swarm_forces(swarm_t *s, double *fx_dev, double *fy_dev, double *fz_dev, void *stream);
 
-/* Philox4x64-10 block and the 4 Gaussians of (seed, id, step, stream) -- parity hooks */
+/* Parity hooks of the noise (ESPResSo: thermostat RNG seeded at espresso.py:1184).  swarm_philox_host: one
+ * Philox4x64-10 block (the policy's Gumbel noise).  swarm_noise_words_host: the thermostat's four 64-bit words of
+ * (seed, id, step, stream) -- two Philox4x32-10 blocks, layout in csrc/swarm_common.cuh -- pure host code.
+ * swarm_gaussians: the 4 normals Box-Muller makes of those words, per id 0..n-1, on the device. */
 int swarm_philox_host(const uint64_t ctr[4], const uint64_t key[2], uint64_t out[4]);
+int swarm_noise_words_host(uint64_t seed, uint64_t id, uint64_t step, uint64_t stream_id, uint64_t out[4]);
 int swarm_gaussians(swarm_t *s, int64_t n, uint64_t step, uint64_t stream_id, double *out4n_dev, void *stream);
 
 /* Scratch capacity: later swarm_bind_state calls with n <= n_max keep the library's scratch (Verlet

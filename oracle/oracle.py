@@ -76,6 +76,8 @@ def lib():
         L = C.CDLL(str(_LIB_PATH))
         L.orc_philox4x64_10.argtypes = [C.POINTER(C.c_uint64)] * 3
         L.orc_gaussians.argtypes = [C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, _DP]
+        L.orc_philox4x32_10.argtypes = [C.POINTER(C.c_uint32)] * 3
+        L.orc_noise_words.argtypes = [C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64)]
         L.orc_forces.argtypes = [C.POINTER(Params), C.POINTER(State), C.c_int, C.c_int, _DP, _DP, _DP]
         L.orc_bd_steps.argtypes = [C.POINTER(Params), C.POINTER(State), C.c_uint64, C.c_int64, C.c_int]
         L.orc_lv_steps.argtypes = [C.POINTER(Params), C.POINTER(State), C.c_uint64, C.c_int64, C.c_int]
@@ -110,6 +112,21 @@ def philox4x64(ctr, key):
     k = (C.c_uint64 * 2)(*[int(v) for v in key])
     o = (C.c_uint64 * 4)()
     lib().orc_philox4x64_10(c, k, o)
+    return np.array(list(o), dtype=np.uint64)
+
+
+def philox4x32(ctr, key):
+    c = (C.c_uint32 * 4)(*[int(v) for v in ctr])
+    k = (C.c_uint32 * 2)(*[int(v) for v in key])
+    o = (C.c_uint32 * 4)()
+    lib().orc_philox4x32_10(c, k, o)
+    return np.array(list(o), dtype=np.uint32)
+
+
+def noise_words(seed, pid, step, stream):
+    """The thermostat's four 64-bit noise words (orc_noise_words)."""
+    o = (C.c_uint64 * 4)()
+    lib().orc_noise_words(int(seed), int(pid), int(step), int(stream), o)
     return np.array(list(o), dtype=np.uint64)
 
 

@@ -110,11 +110,15 @@ SYMBOLS = {
     "swarm_sync_stats": (C.c_int, [_V, _V, C.POINTER(Stats)]),
     "swarm_set_max_neighbors": (C.c_int, [_V, C.c_int32]),
     "swarm_debug_timing": (C.c_int, [_V, C.POINTER(C.c_int64)]),
+    "swarm_set_tiling": (C.c_int, [_V, C.c_int32, C.c_int32]),
+    "swarm_tiling_stats": (C.c_int, [_V, C.POINTER(C.c_int64)]),
+    "swarm_tiled_neighbors_dump": (C.c_int, [_V, _IP, C.c_int64, C.POINTER(C.c_int64)]),
     "swarm_directors": (C.c_int, [_V, _V, _V, _V, _V]),
     "swarm_neighbors_dump": (C.c_int, [_V, _IP, C.c_int64, C.POINTER(C.c_int64)]),
     "swarm_cell_index": (C.c_int, [_V, C.POINTER(C.c_int32), _IP]),
     "swarm_forces": (C.c_int, [_V, _V, _V, _V, _V]),
     "swarm_philox_host": (C.c_int, [C.POINTER(C.c_uint64)] * 3),
+    "swarm_noise_words_host": (C.c_int, [C.c_uint64] * 4 + [C.POINTER(C.c_uint64)]),
     "swarm_gaussians": (C.c_int, [_V, C.c_int64, C.c_uint64, C.c_uint64, _V, _V]),
     "swarm_obs_field": (C.c_int, [_V, _V, _DP, _DP, _V, C.c_int32, C.c_double, C.c_double, C.c_double, C.c_int32, _V, _V, _V, _V]),
     "swarm_obs_vision": (C.c_int, [_V, _V, C.c_int64, C.c_double, C.c_double, C.c_int32, _V, _V, C.c_int32, C.c_int32, _V, _V, _V]),

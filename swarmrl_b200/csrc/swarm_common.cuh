@@ -47,9 +47,16 @@ struct Ctl {
   long long rebuilds;
   long long tprof[8];         // SW_TIMING builds: clock64 sums of the resident kernel's phases (CTA 0, thread 0)
   unsigned long long bar64;
-  unsigned long long pad1[15];   // keep the release word on its own 128-byte line
+  unsigned long long tile_dmax;  // tiled kernel: (validation index << 32) | float bits of the largest displacement^2 of the period;
+                                 // monotone within a launch, zeroed with bar64 (same memset, same line as the arrival counter)
+  unsigned long long pad1[14];   // keep the release word on its own 128-byte line
   unsigned long long rel64;      // published by the last arriver: same encoding as bar64
   unsigned long long pad2[15];  // resident kernel's barrier: low 32 bits arrivals, high 32 bits CTAs with a mover
+  // tiled kernel (swarm_tiled.cuh): rebuild cadence carried from launch to launch, and its statistics
+  int tile_K;                    // steps between Verlet rebuilds chosen by the last launch (0: not chosen yet)
+  int tile_since;                // steps integrated on the current list
+  long long tile_rollbacks;      // periods replayed because a particle left skin/2 before the scheduled rebuild
+  long long tile_partners;       // sum over CTAs of neighbour-flag partners at the last rebuild
 };
 
 struct DevArrays {
@@ -62,6 +69,8 @@ struct DevArrays {
   const int *species;
   const int *n_dev;           // live particle count on the device (<= n), or NULL; see swarm_bind_count
   const long long *gid;       // Philox id of every slot (domain decomposition); NULL => the slot index
+  const long long *okey;      // Verlet entries of a particle are kept in ascending okey[slot] (NULL => ascending slot): the force
+                              // summation order when slots are spatially sorted and no longer the particle ids
   double *xr, *yr, *zr;        // positions at the last Verlet rebuild
   int *head, *next, *cellof;   // linked cells
   int *nbr, *nbr_cnt;          // Verlet list: nbr[k * n_pad + i], k < cap
@@ -82,6 +91,22 @@ __device__ __forceinline__ u64 sw_pid(const DevArrays &A, long long i) { return 
 // ---------------------------------------------------------------------------------------------
 // host handle
 // ---------------------------------------------------------------------------------------------
+// spatial slot order + tile scratch of the tiled 2-D kernel (swarm_sort.cuh, swarm_tiled.cuh); library-owned
+struct TileHost {
+  long long n = 0;             // particle count the arrays were sized / sorted for (0: nothing allocated)
+  bool sorted = false;         // perm / species_s / gid_s describe the bound particles
+  int launches_since_sort = 0;
+  int *perm = nullptr, *key = nullptr, *hist = nullptr, *start = nullptr, *cursor = nullptr, *species_s = nullptr;
+  long long *gid_s = nullptr;
+  double *xs[2] = {nullptr, nullptr}, *ys[2] = {nullptr, nullptr};
+  unsigned int *flags = nullptr, *pbits = nullptr;
+  int nbins_alloc = 0;
+  int mode = 1;                // swarm_set_tiling: 0 off, 1 automatic
+  int resort_interval = 16;    // launches between two spatial sorts
+  long long sorts = 0;
+  long long launches_total = 0;  // tiled launches of this scratch: the flag epochs of a launch start above the previous launch's
+};
+
 struct swarm {
   swarm_config_t cfg;
   DevParams P;
@@ -90,6 +115,8 @@ struct swarm {
   swarm_actions_dev_t act{};
   swarm_state_dev_t st{};
   bool list_valid = false;
+  int list_space = 0;        // index space of the Verlet list in A.nbr: 0 = particle ids, 1 = the tiled kernel's sorted slots
+  TileHost tile;
   int integrator = 0;        // swarm_integrator_t
   int last_mode = 0;         // mode of the last run (steps_done bookkeeping)
   bool lv_resume = false;    // next Langevin run continues an interrupted chunk
@@ -124,12 +151,10 @@ int sw_cuda_fail(cudaError_t e, const char *what);
   } while (0)
 
 // ---------------------------------------------------------------------------------------------
-// Philox4x64-10 (Salmon et al., SC'11).  Layout (documented in DESIGN.md, checked by the parity tests):
-// counter = (step, stream, 0, 0), key = (particle id, seed).
+// Philox (Salmon et al., SC'11).  The thermostat draws from Philox4x32-10 (sw_noise_words below); the policy's
+// Gumbel noise from Philox4x64-10 with counter (call, 4 + 16 k, DOMAIN_POLICY, 0), key (particle id, seed) -- a
+// different generator, so action sampling can never read the words of a thermostat kick.  Stream map: DESIGN.md section 3.
 // ---------------------------------------------------------------------------------------------
-// Counter word c2 separates the consumers of the per-particle key (id, seed): 0 = the integrators' thermostat streams
-// (counter (step, stream 0..5, 0, 0)); the policy's Gumbel noise (counter (call, 4 + 16 k, DOMAIN_POLICY, 0)) can
-// therefore never read the words of a thermostat kick, whatever `call` and `step` are.  Stream map: DESIGN.md section 3.
 #define SW_PHILOX_DOMAIN_POLICY 0x706f6c696379ULL /* "policy" */
 
 __host__ __device__ __forceinline__ void sw_mulhilo(u64 a, u64 b, u64 &hi, u64 &lo) {
@@ -158,6 +183,37 @@ __host__ __device__ __forceinline__ void sw_philox4x64_10(u64 c0, u64 c1, u64 c2
   out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
 }
 
+// Philox4x32-10 (Random123 philox4x32, 10 rounds).  A round is two 32 x 32 -> 64 multiplies (one IMAD.WIDE each on the
+// GPU, both halves at once), two three-input XORs and the key bump.
+__host__ __device__ __forceinline__ void sw_philox4x32_10(unsigned int c0, unsigned int c1, unsigned int c2, unsigned int c3,
+                                                         unsigned int k0, unsigned int k1, unsigned int out[4]) {
+  const unsigned int M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const u64 p0 = (u64)M0 * (u64)c0, p1 = (u64)M1 * (u64)c2;
+    const unsigned int n0 = (unsigned int)(p1 >> 32) ^ c1 ^ k0, n2 = (unsigned int)(p0 >> 32) ^ c3 ^ k1;
+    c0 = n0; c1 = (unsigned int)p1; c2 = n2; c3 = (unsigned int)p0;
+    k0 += W0; k1 += W1;
+  }
+  out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+
+// The thermostat's four 64-bit noise words of (seed, particle id, step, stream) -- oracle: orc_noise_words.  Two
+// Philox4x32-10 blocks b = 0, 1: key = (seed lo, seed hi), counter = (step lo, step hi, id lo,
+// id[32..55] << 8 | stream << 1 | b); word k = block0[k] << 32 | block1[k].  The key is the SEED, uniform over the
+// swarm, so its ten-round schedule costs nothing per particle; the 20 rounds are ~85 instructions where the
+// Philox4x64-10 block of round 1 (64-bit multiplies out of 32-bit ones) took 248.  Stream map: DESIGN.md section 3.
+__host__ __device__ __forceinline__ void sw_noise_words(u64 seed, u64 id, u64 step, u64 stream, u64 r[4]) {
+  const unsigned int k0 = (unsigned int)seed, k1 = (unsigned int)(seed >> 32);
+  const unsigned int c0 = (unsigned int)step, c1 = (unsigned int)(step >> 32), c2 = (unsigned int)id;
+  const unsigned int c3 = ((unsigned int)((id >> 32) & 0xFFFFFFULL) << 8) | ((unsigned int)(stream & 0x7FULL) << 1);
+  unsigned int a[4], b[4];
+  sw_philox4x32_10(c0, c1, c2, c3, k0, k1, a);
+  sw_philox4x32_10(c0, c1, c2, c3 | 1u, k0, k1, b);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) r[k] = ((u64)a[k] << 32) | (u64)b[k];
+}
+
 __device__ __forceinline__ double sw_u01(u64 r) {
   return ((double)(r >> 12) + 0.5) * (1.0 / 4503599627370496.0);
 }
@@ -165,7 +221,7 @@ __device__ __forceinline__ double sw_u01(u64 r) {
 // four standard normals for (seed, id, step, stream): Box-Muller on (u0,u1), (u2,u3)
 __device__ __forceinline__ void sw_gaussians(u64 seed, u64 id, u64 step, u64 stream, double g[4]) {
   u64 r[4];
-  sw_philox4x64_10(step, stream, 0ULL, 0ULL, id, seed, r);
+  sw_noise_words(seed, id, step, stream, r);
   double m0 = sqrt(-2.0 * log(sw_u01(r[0])));
   double m1 = sqrt(-2.0 * log(sw_u01(r[2])));
   double s0, c0, s1, c1;

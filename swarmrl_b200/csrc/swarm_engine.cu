@@ -20,7 +20,9 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <algorithm>
 #include <mutex>
+#include <utility>
 
 #include "swarm_common.cuh"
 #include "swarm_math.cuh"
@@ -164,6 +166,17 @@ __device__ __forceinline__ void phase_search(const DevParams &P, const DevArrays
           j = ldcg(&A.next[j]);
         }
       }
+  if (A.okey) {
+    // spatially sorted slots: the summation order stays "ascending particle id", whatever slot a particle sits in
+    // (keys re-read per comparison: the lists are short and a rebuild is rare; no second local array)
+    for (int k = 1; k < cnt; ++k) {
+      const int e = loc[k];
+      const long long key = A.okey[e & SW_IDX_MASK];
+      int m = k;
+      while (m > 0 && A.okey[loc[m - 1] & SW_IDX_MASK] > key) { loc[m] = loc[m - 1]; --m; }
+      loc[m] = e;
+    }
+  }
   for (int k = 0; k < cnt; ++k) A.nbr[(long long)k * A.n_pad + i] = loc[k];
   A.nbr_cnt[i] = cnt;
   A.xr[i] = xi; A.yr[i] = yi;
@@ -593,6 +606,8 @@ __device__ __forceinline__ void grid_barrier64(unsigned long long *counter, unsi
 #define SW_RES_NBR 4  // neighbour entries of the Verlet list kept in registers by the resident kernel
 
 #include "swarm_bd2d.cuh"  // k_bd2d_resident: the hot kernel of the 2-D rollout
+#include "swarm_sort.cuh"  // spatial slot order (cell hash, counting sort, cell-start scan, permutation)
+#include "swarm_tiled.cuh" // k_bd2d_tiled: the same chunk on spatial CTA tiles, neighbourhood barrier instead of the grid barrier
 
 // ---------------------------------------------------------------------------------------------
 // one-launch-per-phase variant (SWARM_FLAG_NO_PERSISTENT): same device functions, kernel
@@ -926,7 +941,11 @@ extern "C" int swarm_bind_state(swarm_t *s, int64_t n, const swarm_state_dev_t *
     memset(&A, 0, sizeof(A));
     A.ctl = ctl; A.cap = cap;
     A.n_pad = need_pad;
+    const int tmode = s->tile.mode, tint = s->tile.resort_interval;
+    s->tile = TileHost();   // its arrays were in `owned`
+    s->tile.mode = tmode; s->tile.resort_interval = tint;
   }
+  s->tile.sorted = false;   // other particles: the slot order has to be computed again
   A.n = n;
   s->st = *st;
   A.x[0] = st->x; A.y[0] = st->y; A.z[0] = st->z;
@@ -1000,6 +1019,7 @@ extern "C" int swarm_bind_ids(swarm_t *s, const int64_t *gid_dev) {
   if (!s) return SWARM_ERR_INVALID;
   if (!s->state_bound) { sw_set_error("bind the state first"); return SWARM_ERR_STATE; }
   s->A.gid = (const long long *)gid_dev;
+  s->tile.sorted = false;   // the sorted copy of the ids is stale
   return SWARM_OK;
 }
 
@@ -1110,6 +1130,157 @@ static int sw_launch_resident(swarm *s, const RunArgs &R, cudaStream_t st, bool 
   void *args[] = {(void *)&P, (void *)&A, (void *)&Rr};
   SW_CUDA(cudaLaunchCooperativeKernel((void *)kern, dim3((unsigned)want), dim3(threads), args, 0, st));
   s->launches += 1;
+  return SWARM_OK;
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// tiled 2-D kernel (swarm_tiled.cuh): eligibility, spatial sort, launch
+// ---------------------------------------------------------------------------------------------
+#define SW_TILE_MIN_N 4096   // below this a swarm is a handful of CTAs and the grid barrier is cheap
+
+static bool sw_wca_symmetric(const swarm *s) {
+  const DevParams &P = s->P;
+  for (int a = 0; a < P.n_types; ++a)
+    for (int b = 0; b < a; ++b)
+      if (P.wca_cut[a][b] != P.wca_cut[b][a]) return false;
+  return true;
+}
+
+// CTAs and slots per CTA of the tiled (and resident) layout
+static void sw_tile_shape(const swarm *s, long long *ctas_out, int *ppc_out, int *threads_out) {
+  long long ctas = s->num_sms;
+  if (s->A.n < ctas * 128) ctas = (s->A.n + 127) / 128;   // small swarms: at least 4 particle warps per CTA
+  if (ctas < 1) ctas = 1;
+  const int ppc = (int)((s->A.n + ctas - 1) / ctas);
+  *ppc_out = ppc;
+  *threads_out = 32 + ((ppc + 31) / 32) * 32;
+  *ctas_out = (s->A.n + ppc - 1) / ppc;
+}
+
+static bool sw_tile_eligible(const swarm *s, const RunArgs &R) {
+  if (!s->persistent || s->P.n_dims != 2 || R.mode != MODE_BD || s->P.n_envs != 1 || s->A.n_dev) return false;
+  if (s->tile.mode == 0 || getenv("SWARM_B200_NO_TILED")) return false;
+  long long min_n = SW_TILE_MIN_N;
+  if (const char *e = getenv("SWARM_B200_TILED_MIN_N")) min_n = atoll(e);
+  if (s->tile.mode == 1 && s->A.n < min_n) return false;
+  if (s->A.n < 1 || !sw_wca_symmetric(s)) return false;
+  long long ctas; int ppc, threads;
+  sw_tile_shape(s, &ctas, &ppc, &threads);
+  return threads <= SW_RES_MAXT && ctas <= SW_TILE_MAXCTA && ctas <= s->num_sms;
+}
+
+// (re)allocate the tile scratch for the bound particle count and, when due, recompute the slot order
+static int sw_tile_prepare(swarm *s, cudaStream_t st, bool *resorted) {
+  TileHost &t = s->tile;
+  DevArrays &A = s->A;
+  const long long n = A.n;
+  *resorted = false;
+  if (t.n != A.n_pad) {
+    // sized for the padded capacity, so a rebind within the same scratch keeps them
+    const size_t np = (size_t)A.n_pad;
+    int rc;
+    if ((rc = sw_alloc(s, (void **)&t.perm, sizeof(int) * np))) return rc;
+    if ((rc = sw_alloc(s, (void **)&t.key, sizeof(int) * np))) return rc;
+    if ((rc = sw_alloc(s, (void **)&t.species_s, sizeof(int) * np))) return rc;
+    if ((rc = sw_alloc(s, (void **)&t.gid_s, sizeof(long long) * np))) return rc;
+    for (int b = 0; b < 2; ++b) {
+      if ((rc = sw_alloc(s, (void **)&t.xs[b], sizeof(double) * np))) return rc;
+      if ((rc = sw_alloc(s, (void **)&t.ys[b], sizeof(double) * np))) return rc;
+    }
+    if ((rc = sw_alloc(s, (void **)&t.flags, sizeof(unsigned int) * 32 * SW_TILE_MAXCTA))) return rc;
+    if ((rc = sw_alloc(s, (void **)&t.pbits, sizeof(unsigned int) * (SW_TILE_MAXCTA / 32) * SW_TILE_MAXCTA))) return rc;
+    t.n = A.n_pad;
+    t.sorted = false;
+    t.nbins_alloc = 0;
+  }
+  const bool due = !t.sorted || (t.resort_interval > 0 && t.launches_since_sort >= t.resort_interval);
+  if (!due) return SWARM_OK;
+  // strips of width ~ sqrt(particles per CTA / density), rows of ~8 particles
+  long long ctas; int ppc, threads;
+  sw_tile_shape(s, &ctas, &ppc, &threads);
+  const double Lx = s->P.box[0], Ly = s->P.box[1];
+  const double density = (double)n / (Lx * Ly);
+  SortGeom G;
+  double W = sqrt((double)ppc / density);
+  G.n_strips = (int)floor(Lx / W + 0.5);
+  if (G.n_strips < 1) G.n_strips = 1;
+  if (G.n_strips > 4096) G.n_strips = 4096;
+  W = Lx / G.n_strips;
+  double h = 8.0 / (density * W);
+  double nr = ceil(Ly / h);
+  if (nr < 1.0) nr = 1.0;
+  if (nr > 65536.0) nr = 65536.0;
+  while ((double)G.n_strips * nr > 4194304.0) nr = floor(nr / 2.0);
+  G.n_rows = (int)nr;
+  G.inv_w = 1.0 / W;
+  G.inv_h = (double)G.n_rows / Ly;
+  const int nbins = G.n_strips * G.n_rows;
+  if (nbins + 1 > t.nbins_alloc) {
+    int rc;
+    if ((rc = sw_alloc(s, (void **)&t.hist, sizeof(int) * (size_t)(nbins + 1)))) return rc;
+    if ((rc = sw_alloc(s, (void **)&t.start, sizeof(int) * (size_t)(nbins + 1)))) return rc;
+    if ((rc = sw_alloc(s, (void **)&t.cursor, sizeof(int) * (size_t)(nbins + 1)))) return rc;
+    t.nbins_alloc = nbins + 1;
+  }
+  SW_CUDA(cudaMemsetAsync(t.hist, 0, sizeof(int) * (size_t)(nbins + 1), st));
+  const int B = sw_blocks(n, 256);
+  k_sort_key<<<B, 256, 0, st>>>(s->P, G, n, A.x[0], A.y[0], t.key, t.hist);
+  k_sort_scan<<<1, 1024, 0, st>>>(nbins, t.hist, t.start, t.cursor);
+  k_sort_place<<<B, 256, 0, st>>>(n, t.key, t.cursor, t.perm);
+  k_sort_fix<<<sw_blocks(nbins, 128), 128, 0, st>>>(nbins, t.start, t.perm);
+  k_sort_gather<<<B, 256, 0, st>>>(n, t.perm, A.species, A.gid, t.species_s, t.gid_s);
+  s->launches += 5;
+  SW_CUDA(cudaGetLastError());
+  t.sorted = true;
+  t.launches_since_sort = 0;
+  t.sorts += 1;
+  *resorted = true;
+  return SWARM_OK;
+}
+
+template <bool NOISE>
+static int sw_launch_tiled(swarm *s, const RunArgs &R, cudaStream_t st, bool *fits) {
+  auto kern = k_bd2d_tiled<NOISE>;
+  long long ctas; int ppc, threads;
+  sw_tile_shape(s, &ctas, &ppc, &threads);
+  int bpsm = 0;
+  const size_t dsm = sizeof(double) * SW_TILE_COLS * SW_TILE_MAXP;
+  SW_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dsm));
+  SW_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bpsm, kern, threads, dsm));
+  *fits = bpsm >= 1 && ctas <= (long long)s->num_sms * bpsm;
+  if (!*fits) return SWARM_OK;
+  bool resorted = false;
+  int rc = sw_tile_prepare(s, st, &resorted);
+  if (rc) return rc;
+  TileHost &t = s->tile;
+  RunArgs Rr = R;
+  Rr.particles_per_cta = ppc;
+  if (resorted) {
+    // new slot order (or other particles): restart the flag epochs, so no CTA index carries a stale flag
+    SW_CUDA(cudaMemsetAsync(t.flags, 0, sizeof(unsigned int) * 32 * SW_TILE_MAXCTA, st));
+    t.launches_total = 0;
+  }
+  if (resorted || s->list_space != 1) Rr.force_rebuild = 1;   // the list in A.nbr is in another index space
+  s->list_space = 1;
+  s->coop_blocks_per_sm = bpsm;
+  SW_CUDA(cudaMemsetAsync(&s->A.ctl->bar64, 0, sizeof(unsigned long long) * 32, st));
+  DevParams P = s->P;
+  DevArrays A = s->A;
+  DevArrays T = s->A;   // slot space: same scratch (cells, lists, references), sorted positions / species / ids
+  T.x[0] = t.xs[0]; T.x[1] = t.xs[1]; T.y[0] = t.ys[0]; T.y[1] = t.ys[1];
+  T.species = t.species_s;
+  T.gid = t.gid_s;
+  T.okey = t.gid_s;
+  TileArgs G;
+  G.perm = t.perm; G.flags = t.flags; G.pbits = t.pbits; G.ppc = ppc; G.k_init = 8;
+  G.epoch0 = (unsigned int)((t.launches_total + 1) & 0xFFF) << 20;
+  if (const char *e = getenv("SWARM_B200_TILE_KINIT")) { const int k = atoi(e); if (k >= 1 && k <= SW_TILE_KMAX) G.k_init = k; }
+  void *args[] = {(void *)&P, (void *)&A, (void *)&T, (void *)&G, (void *)&Rr};
+  SW_CUDA(cudaLaunchCooperativeKernel((void *)kern, dim3((unsigned)ctas), dim3(threads), args, dsm, st));
+  s->launches += 1;
+  t.launches_since_sort += 1;
+  t.launches_total += 1;
   return SWARM_OK;
 }
 
@@ -1225,7 +1396,16 @@ static int sw_run_common(swarm *s, RunArgs R, cudaStream_t st) {
       done += Rc.n_steps;
       continue;
     }
-    if (s->persistent && s->P.n_dims == 2 && R.mode == MODE_BD && !getenv("SWARM_B200_NO_RESIDENT")) {
+    if (sw_tile_eligible(s, Rc)) {
+      rc = noise ? sw_launch_tiled<true>(s, Rc, st, &done_resident) : sw_launch_tiled<false>(s, Rc, st, &done_resident);
+      if (rc) return rc;
+    }
+    if (!done_resident && s->list_space != 0) {   // the list in A.nbr is in the tiled kernel's slot space
+      Rc.force_rebuild = 1;
+      s->list_space = 0;
+    }
+    if (done_resident) {
+    } else if (s->persistent && s->P.n_dims == 2 && R.mode == MODE_BD && !getenv("SWARM_B200_NO_RESIDENT")) {
       static const bool pipe = !(getenv("SWARM_B200_RES_PIPE") && atoi(getenv("SWARM_B200_RES_PIPE")) == 0);
       rc = !noise ? sw_launch_resident<false, 0>(s, Rc, st, &done_resident)
                   : (pipe ? sw_launch_resident<true, 1>(s, Rc, st, &done_resident) : sw_launch_resident<true, 0>(s, Rc, st, &done_resident));
@@ -1360,6 +1540,7 @@ static int sw_force_rebuild(swarm *s, cudaStream_t st) {
   s->launches += 5;
   SW_CUDA(cudaGetLastError());
   s->list_valid = true;
+  s->list_space = 0;
   return SWARM_OK;
 }
 
@@ -1386,6 +1567,50 @@ extern "C" int swarm_neighbors_dump(swarm_t *s, int32_t *pairs, int64_t cap, int
       }
       ++c;
     }
+  *count = c;
+  return SWARM_OK;
+}
+
+extern "C" int swarm_set_tiling(swarm_t *s, int32_t mode, int32_t resort_interval) {
+  if (!s || mode < 0 || mode > 2) { sw_set_error("tiling mode must be 0 (off), 1 (automatic) or 2 (always)"); return SWARM_ERR_INVALID; }
+  s->tile.mode = mode;
+  if (resort_interval > 0) s->tile.resort_interval = resort_interval;
+  return SWARM_OK;
+}
+
+extern "C" int swarm_tiling_stats(swarm_t *s, int64_t out8[8]) {
+  if (!s || !out8) return SWARM_ERR_INVALID;
+  SW_CUDA(cudaSetDevice(s->cfg.device));
+  SW_CUDA(cudaDeviceSynchronize());
+  SW_CUDA(cudaMemcpy(s->ctl_host, s->A.ctl, sizeof(Ctl), cudaMemcpyDeviceToHost));
+  long long ctas = 0; int ppc = 0, threads = 0;
+  if (s->state_bound && s->A.n > 0) sw_tile_shape(s, &ctas, &ppc, &threads);
+  out8[0] = s->list_space == 1; out8[1] = s->ctl_host->tile_K; out8[2] = s->ctl_host->tile_since;
+  out8[3] = s->ctl_host->tile_rollbacks; out8[4] = s->ctl_host->tile_partners; out8[5] = s->tile.sorts;
+  out8[6] = ctas; out8[7] = ppc;
+  return SWARM_OK;
+}
+
+extern "C" int swarm_tiled_neighbors_dump(swarm_t *s, int32_t *pairs, int64_t cap, int64_t *count) {
+  if (!s || !count) return SWARM_ERR_INVALID;
+  if (!s->state_bound || s->list_space != 1 || !s->tile.sorted) { sw_set_error("the last run did not use the tiled kernel"); return SWARM_ERR_STATE; }
+  SW_CUDA(cudaSetDevice(s->cfg.device));
+  SW_CUDA(cudaDeviceSynchronize());
+  const long long n = s->A.n;
+  std::vector<int> cnt((size_t)n), perm((size_t)n), nbr((size_t)s->A.n_pad * (size_t)s->A.cap);
+  SW_CUDA(cudaMemcpy(cnt.data(), s->A.nbr_cnt, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost));
+  SW_CUDA(cudaMemcpy(perm.data(), s->tile.perm, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost));
+  SW_CUDA(cudaMemcpy(nbr.data(), s->A.nbr, sizeof(int) * nbr.size(), cudaMemcpyDeviceToHost));
+  std::vector<std::pair<int, int>> out;
+  for (long long sl = 0; sl < n; ++sl)
+    for (int k = 0; k < cnt[(size_t)sl]; ++k)
+      out.emplace_back(perm[(size_t)sl], perm[(size_t)(nbr[(size_t)k * (size_t)s->A.n_pad + (size_t)sl] & SW_IDX_MASK)]);
+  std::sort(out.begin(), out.end());
+  int64_t c = 0;
+  for (const auto &pr : out) {
+    if (c < cap && pairs) { pairs[2 * c] = pr.first; pairs[2 * c + 1] = pr.second; }
+    ++c;
+  }
   *count = c;
   return SWARM_OK;
 }
@@ -1422,6 +1647,14 @@ extern "C" int swarm_forces(swarm_t *s, double *fx, double *fy, double *fz, void
 extern "C" int swarm_philox_host(const uint64_t ctr[4], const uint64_t key[2], uint64_t out[4]) {
   u64 o[4];
   sw_philox4x64_10(ctr[0], ctr[1], ctr[2], ctr[3], key[0], key[1], o);
+  for (int k = 0; k < 4; ++k) out[k] = o[k];
+  return SWARM_OK;
+}
+
+extern "C" int swarm_noise_words_host(uint64_t seed, uint64_t id, uint64_t step, uint64_t stream_id, uint64_t out[4]) {
+  if (!out) return SWARM_ERR_INVALID;
+  u64 o[4];
+  sw_noise_words(seed, id, step, stream_id, o);
   for (int k = 0; k < 4; ++k) out[k] = o[k];
   return SWARM_OK;
 }

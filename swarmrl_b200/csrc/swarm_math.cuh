@@ -24,11 +24,6 @@ static __constant__ double SWM_COS[10] = {1.0, -19.739208802178716, 64.939394022
 static __constant__ double SWM_K[4] = {0.99999999999999988897769753748 /* 1 - 2^-53 */, 0.6931471805599453 /* ln2 hi */,
                                        2.3190468138462996e-17 /* ln2 lo */, 0.5};
 
-// nvcc's mul.hi.u64 + mul.lo.u64 pair is the shortest SASS for the Philox multiply (measured against a
-// shared-partial-product IMAD.WIDE version and a PTX carry chain: 248 vs 336 vs 256 instructions).
-__device__ __forceinline__ void swm_philox4x64_10(u64 c0, u64 c1, u64 c2, u64 c3, u64 k0, u64 k1, u64 out[4]) {
-  sw_philox4x64_10(c0, c1, c2, c3, k0, k1, out);
-}
 
 // 1/d and sqrt(x) for normal positive arguments: MUFU seed + Newton steps, no special-case branches.
 __device__ __forceinline__ double swm_rcp(double d) {
@@ -121,7 +116,7 @@ __device__ __forceinline__ void swm_sincos2pi(u64 r, double &sn, double &cs) {
 // what a 2-D Brownian step consumes (x, y, theta).  Same values as sw_gaussians()[0,1,3] to ~1e-15.
 __device__ __forceinline__ void swm_gaussians_xyt(u64 seed, u64 id, u64 step, double &g0, double &g1, double &g3) {
   u64 r[4];
-  swm_philox4x64_10(step, 0ULL, 0ULL, 0ULL, id, seed, r);
+  sw_noise_words(seed, id, step, 0ULL, r);
   const double m0 = swm_sqrt(-2.0 * swm_log01(swm_u01(r[0])));
   const double m1 = swm_sqrt(-2.0 * swm_log01(swm_u01(r[2])));
   double s0, c0, s1, c1;
@@ -133,7 +128,7 @@ __device__ __forceinline__ void swm_gaussians_xyt(u64 seed, u64 id, u64 step, do
 // The same three normals from Philox words drawn earlier (swm_philox_xyt): the resident kernel draws the words of
 // step s+1 in the shadow of step s's neighbour loads and transforms them in the shadow of the grid barrier.
 __device__ __forceinline__ void swm_philox_xyt(u64 seed, u64 id, u64 step, u64 r[4]) {
-  swm_philox4x64_10(step, 0ULL, 0ULL, 0ULL, id, seed, r);
+  sw_noise_words(seed, id, step, 0ULL, r);
 }
 __device__ __forceinline__ void swm_boxmuller_xyt(const u64 r[4], double &g0, double &g1, double &g3) {
   const double m0 = swm_sqrt(-2.0 * swm_log01(swm_u01(r[0])));
@@ -176,7 +171,7 @@ __device__ __forceinline__ void swm_sincos(double th, double &sn, double &cs) {
 // four uniforms in (-1/2, 1/2): the Langevin thermostat's noise (oracle: orc_uniforms)
 __device__ __forceinline__ void swm_uniforms(u64 seed, u64 id, u64 step, u64 stream, double u[4]) {
   u64 r[4];
-  swm_philox4x64_10(step, stream, 0ULL, 0ULL, id, seed, r);
+  sw_noise_words(seed, id, step, stream, r);
 #pragma unroll
   for (int k = 0; k < 4; ++k) u[k] = swm_u01(r[k]) - 0.5;
 }
@@ -184,7 +179,7 @@ __device__ __forceinline__ void swm_uniforms(u64 seed, u64 id, u64 step, u64 str
 // all four normals with the fast kernels (parity hook / 3-D)
 __device__ __forceinline__ void swm_gaussians(u64 seed, u64 id, u64 step, u64 stream, double g[4]) {
   u64 r[4];
-  swm_philox4x64_10(step, stream, 0ULL, 0ULL, id, seed, r);
+  sw_noise_words(seed, id, step, stream, r);
   const double m0 = swm_sqrt(-2.0 * swm_log01(swm_u01(r[0])));
   const double m1 = swm_sqrt(-2.0 * swm_log01(swm_u01(r[2])));
   double s0, c0, s1, c1;

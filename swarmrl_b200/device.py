@@ -230,6 +230,28 @@ class DeviceSwarm:
     def set_max_neighbors(self, cap):
         _lib.check(self.lib.swarm_set_max_neighbors(self.h, int(cap)))
 
+    def set_tiling(self, mode, resort_interval=0):
+        """Spatial tiling of the 2-D Brownian chunk (swarm_set_tiling): 0 off, 1 automatic, 2 whenever it fits."""
+        _lib.check(self.lib.swarm_set_tiling(self.h, int(mode), int(resort_interval)))
+
+    def tiling_stats(self):
+        """dict of the tiled kernel's counters (swarm_tiling_stats); synchronises."""
+        out = (C.c_int64 * 8)()
+        _lib.check(self.lib.swarm_tiling_stats(self.h, out))
+        keys = ("tiled", "cadence", "steps_on_list", "rollbacks", "partner_sum", "sorts", "ctas", "slots_per_cta")
+        return dict(zip(keys, [int(v) for v in out]))
+
+    def tiled_neighbors(self):
+        """Sorted (i, j) id pairs of the tiled kernel's own Verlet list, as it stands."""
+        cnt = C.c_int64(0)
+        cap = max(64, 32 * self.n)
+        while True:
+            buf = np.zeros((cap, 2), dtype=np.int32)
+            _lib.check(self.lib.swarm_tiled_neighbors_dump(self.h, _lib.ip(buf), cap, C.byref(cnt)))
+            if cnt.value <= cap:
+                return buf[: cnt.value].copy()
+            cap = int(cnt.value)
+
     def apply_new_direction(self):
         _lib.check(self.lib.swarm_apply_new_direction(self.h, self._stream()))
 

@@ -46,6 +46,10 @@ def test_philox_host_entry_point_matches_oracle():
     o = (ctypes.c_uint64 * 4)()
     assert L.swarm_philox_host(c, k, o) == 0
     assert np.array_equal(np.array(list(o), dtype=np.uint64), oracle.philox4x64([5, 6, 7, 8], [11, 12]))
+    # the thermostat's noise words (two Philox4x32-10 blocks): library == oracle, bit for bit
+    for seed, pid, step, stream in ((42, 7, 1000, 3), (2**64 - 1, 2**40 + 9, 2**40 + 5, 5), (0, 0, 0, 0)):
+        assert L.swarm_noise_words_host(seed, pid, step, stream, o) == 0
+        assert np.array_equal(np.array(list(o), dtype=np.uint64), oracle.noise_words(seed, pid, step, stream))
 
 
 def test_no_cpu_fallback_without_a_device():

@@ -1,5 +1,6 @@
-"""Pins the oracle's Philox4x64-10 bit-exactly against numpy.random.Philox (Random123's
-Philox4x64-10; numpy increments the counter BEFORE producing a block)."""
+"""Pins the oracle's Philox generators bit-exactly: Philox4x64-10 against numpy.random.Philox (Random123's
+Philox4x64-10; numpy increments the counter BEFORE producing a block) and Philox4x32-10 -- the thermostat's --
+against Random123's published known answers and an independent pure-Python restatement."""
 import numpy as np
 import pytest
 
@@ -26,10 +27,55 @@ def test_random123_known_answer():
                                           "0x7e68b68aec7ba23b"]
 
 
+def _philox4x32_py(ctr, key):
+    M0, M1, W0, W1 = 0xD2511F53, 0xCD9E8D57, 0x9E3779B9, 0xBB67AE85
+    c, k = list(ctr), list(key)
+    for _ in range(10):
+        p0, p1 = M0 * c[0], M1 * c[2]
+        c = [(p1 >> 32) ^ c[1] ^ k[0], p1 & 0xFFFFFFFF, (p0 >> 32) ^ c[3] ^ k[1], p0 & 0xFFFFFFFF]
+        k = [(k[0] + W0) & 0xFFFFFFFF, (k[1] + W1) & 0xFFFFFFFF]
+    return c
+
+
+@pytest.mark.parametrize("ctr,key,want", [
+    # Random123 kat_vectors, "philox4x32 10"
+    ([0, 0, 0, 0], [0, 0], [0x6627E8D5, 0xE169C58D, 0xBC57AC4C, 0x9B00DBD8]),
+    ([0xFFFFFFFF] * 4, [0xFFFFFFFF] * 2, [0x408F276D, 0x41C83B0E, 0xA20BC7C6, 0x6D5451FD]),
+    ([0x243F6A88, 0x85A308D3, 0x13198A2E, 0x03707344], [0xA4093822, 0x299F31D0],
+     [0xD16CFE09, 0x94FDCCEB, 0x5001E420, 0x24126EA1]),
+])
+def test_philox4x32_random123_known_answers(ctr, key, want):
+    assert [int(v) for v in oracle.philox4x32(ctr, key)] == want
+    assert _philox4x32_py(ctr, key) == want
+
+
+def test_noise_words_layout():
+    """key = (seed lo, seed hi); counter = (step lo, step hi, id lo, id[32..55] << 8 | stream << 1 | block);
+    word k = block0[k] << 32 | block1[k]."""
+    rng = np.random.default_rng(5)
+    for _ in range(50):
+        seed, step = (int(v) for v in rng.integers(0, 2**63, 2, dtype=np.uint64) * 2 + 1)
+        pid = int(rng.integers(0, 2**56, dtype=np.uint64))
+        stream = int(rng.integers(0, 6))
+        key = [seed & 0xFFFFFFFF, seed >> 32]
+        c3 = (((pid >> 32) & 0xFFFFFF) << 8) | (stream << 1)
+        a = _philox4x32_py([step & 0xFFFFFFFF, step >> 32, pid & 0xFFFFFFFF, c3], key)
+        b = _philox4x32_py([step & 0xFFFFFFFF, step >> 32, pid & 0xFFFFFFFF, c3 | 1], key)
+        want = [(x << 32) | y for x, y in zip(a, b)]
+        assert [int(v) for v in oracle.noise_words(seed, pid, step, stream)] == want
+    # neighbouring ids / steps / streams never share a word
+    seen = set()
+    for pid in range(4):
+        for step in range(4):
+            for stream in range(6):
+                seen.update(int(v) for v in oracle.noise_words(42, pid, step, stream))
+    assert len(seen) == 4 * 4 * 6 * 4
+
+
 def test_gaussians_layout_and_moments():
-    """counter = (step, stream, 0, 0), key = (id, seed); u = (r>>12 + 1/2) 2^-52; Box-Muller."""
+    """u = (word >> 12 + 1/2) 2^-52 of the four noise words; Box-Muller on (u0, u1), (u2, u3)."""
     seed, pid, step, stream = 42, 7, 1000, 3
-    r = oracle.philox4x64([step, stream, 0, 0], [pid, seed])
+    r = oracle.noise_words(seed, pid, step, stream)
     u = ((r >> np.uint64(12)).astype(np.float64) + 0.5) / 2.0**52
     m0, m1 = np.sqrt(-2 * np.log(u[0])), np.sqrt(-2 * np.log(u[2]))
     want = [m0 * np.cos(2 * np.pi * u[1]), m0 * np.sin(2 * np.pi * u[1]), m1 * np.cos(2 * np.pi * u[3]),
