@@ -56,7 +56,33 @@ VISION = dict(range=10.0, half_angle=np.pi / 2, n_cones=5)
 BYTES_PER_AGENT_STEP = 68  # 2-D steady-state step, read 44 B + write 24 B
 # dram__bytes_read.sum + dram__bytes_write.sum of one k_bd2d_resident launch (100 steps), from the ncu --set full
 # capture profiles/r01_k_bd2d_resident.ncu-rep (10.70 MB + 0.12 MB): the state is register / L2 resident
-NCU_DRAM_BYTES_PER_LAUNCH = 10.70e6  # dram__bytes_read + write of one k_bd2d_resident launch, profiles/r01_ncu_k_bd2d_resident_summary.txt
+ISSUE_SLOTS_PER_CLOCK = 148 * 4      # warp instructions a B200 can issue per SM clock (one per scheduler)
+
+
+def ncu_profile(kernel):
+    """Per-launch figures of the run kernel from the committed ncu --set full summary (tools/ncu_summary.py), scaled to
+    the bench's 100-step launch: DRAM bytes (dram__bytes_read + write) and warp instructions.  Returns None when no
+    summary of that kernel is committed -- nothing is hard-coded here."""
+    for rnd in ("r02", "r01"):
+        f = ROOT / "profiles" / f"{rnd}_ncu_{kernel}_summary.txt"
+        if not f.exists():
+            continue
+        vals = {}
+        for ln in f.read_text().splitlines():
+            p = ln.split()
+            if len(p) >= 2 and p[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum", "smsp__inst_executed.sum", "profiled_launch_steps",
+                                        "gpu__time_duration.sum"):
+                mult = {"Mbyte": 1e6, "Kbyte": 1e3, "Gbyte": 1e9, "byte": 1.0}.get(p[2] if len(p) > 2 else "", 1.0)
+                vals[p[0]] = float(p[1]) * mult
+        steps = vals.get("profiled_launch_steps", 100.0)   # round 1's summaries profiled 100-step launches
+        if "dram__bytes_read.sum" not in vals:
+            continue
+        k = STEPS_PER_SLICE / steps
+        return {"file": f"profiles/{f.name}", "dram_bytes_per_launch": (vals["dram__bytes_read.sum"] + vals.get("dram__bytes_write.sum", 0.0)) * k,
+                "warp_instr_per_launch": vals.get("smsp__inst_executed.sum", 0.0) * k}
+    return None
+
+
 METRIC = "agent_steps_per_sec_100k_agents"
 UNIT = "agent-steps/s"
 
@@ -401,6 +427,15 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     dev_ms, e2e_ms = float(t[0]), float(t[1])
+    tiling = ro.d.tiling_stats()
+    eng = None
+    if not args.no_engine:
+        eng = engine_record(args, local, K, W)
+        if world > 1:
+            te = torch.tensor([eng["ms_per_step"]], dtype=torch.float64, device="cuda")
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+            eng["ms_per_step"] = float(te[0])
+            eng["value"] = N_AGENTS * STEPS_PER_SLICE * n_gpus / (eng["ms_per_step"] * 1e-3)
     extras = None
     if not args.no_extra:
         del ro.flush_buf
@@ -422,6 +457,16 @@ def run_ours(args):
     peak = float(peaks.get("hbm_gbs", 6554.6))
     run_avg_ms = float(np.mean(run_ms))
     achieved = N_AGENTS * STEPS_PER_SLICE * BYTES_PER_AGENT_STEP / (run_avg_ms * 1e-3) / 1e9
+    kname = "k_bd2d_tiled" if tiling["tiled"] else "k_bd2d_resident"
+    prof = ncu_profile(kname)
+    sm_hz = (clocks["sm_mhz"] or 1965.0) * 1e6 if clocks else 1965.0e6
+    issue = None
+    if prof and prof["warp_instr_per_launch"]:
+        issue = {"warp_instr_per_launch": prof["warp_instr_per_launch"],
+                 "warp_instr_per_agent_step": prof["warp_instr_per_launch"] * 32 / (N_AGENTS * STEPS_PER_SLICE),
+                 "peak_warp_instr_per_s": ISSUE_SLOTS_PER_CLOCK * sm_hz,
+                 "frac": prof["warp_instr_per_launch"] / (run_avg_ms * 1e-3) / (ISSUE_SLOTS_PER_CLOCK * sm_hz),
+                 "source": prof["file"] + " (instruction count) / this run's launch time and SM clock"}
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": K, "warmup": W,
             "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic", "config": dict(config_dict(n_gpus), skin=args.skin, rebuilds_per_slice=rebuilds / K,
@@ -429,12 +474,18 @@ def run_ours(args):
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": ro.h2d, "d2h_bytes_per_step": ro.d2h,
                     "ms_per_step": e2e_ms / K},
             "gpu_launches": launches,
-            "roofline": {"bound": "hbm", "kernel": "k_bd2d_resident<true> (one cooperative launch = 100 Brownian steps of 100k agents)",
-                         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": NCU_DRAM_BYTES_PER_LAUNCH,
+            "roofline": {"bound": "hbm", "kernel": kname + "<true> (one cooperative launch = 100 Brownian steps of 100k agents)",
+                         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": prof["dram_bytes_per_launch"] if prof else None,
+                         "traffic_source": prof["file"] if prof else None,
+                         "issue": issue, "issue_frac": issue["frac"] if issue else None,
+                         "tiling": tiling,
                          "bytes_per_launch": N_AGENTS * STEPS_PER_SLICE * BYTES_PER_AGENT_STEP,
                          "launch_ms": run_avg_ms, "share_of_step": run_avg_ms * K / dev_ms,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback"},
             "clocks": clocks, "wall_s_timed": t_wall}
+    if eng is not None:
+        line["e2e_engine"] = eng
     if n_gpus == 1 and not args.no_cpu:
         cb = cpu_slice_rate(sample_steps=args.cpu_steps, observers=2000)
         line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
@@ -447,6 +498,90 @@ def run_ours(args):
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+def engine_record(args, local, K, W):
+    """`e2e_engine`: the same C4 slice through the repo's own Engine API, the call a SwarmRL user makes --
+    SwarmEngine.integrate(K, ForceFunction({'0': DeviceAgent(FusedActorCritic, GradientSensing, SubdividedVisionCones)}))
+    (espresso.py:1251-1308, actor_critic.py:159-216) -- CUDA events around the WHOLE integrate() call, so the Python
+    host loop counts; the only D2H is the K reward means.  Policy: the reference tests' network (Dense(128) + ReLU,
+    actor 4 / critic 1, test_rl_trainers.py:17-26), random-init, evaluated and sampled on the device."""
+    import tempfile
+
+    import torch
+
+    import swarmrl_b200 as sw
+    from swarmrl_b200 import decay
+    from swarmrl_b200.observables import SubdividedVisionCones
+    from swarmrl_b200.tasks import GradientSensing
+    from swarmrl_b200.units import UnitRegistry
+
+    ureg = UnitRegistry()
+    dt = ureg.Quantity(DT, "second")
+    md = sw.MDParams(ureg=ureg, fluid_dyn_viscosity=ureg.Quantity(8.9e-4, "pascal * second"),
+                     WCA_epsilon=ureg.Quantity(297.0, "kelvin") * ureg.boltzmann_constant,
+                     temperature=ureg.Quantity(300.0, "kelvin"), box_length=ureg.Quantity(3 * [BOX], "micrometer"),
+                     time_step=dt, time_slice=dt * STEPS_PER_SLICE, write_interval=dt * STEPS_PER_SLICE * 100000)
+    tmp = tempfile.mkdtemp(prefix="swarm_bench_")
+    e = sw.SwarmEngine(md_params=md, n_dims=2, seed=SEED, out_folder=tmp, skin=args.skin)
+    pos, th = initial_state(N_AGENTS, BOX, SEED)
+    dirs = np.stack([np.cos(th), np.sin(th), np.zeros_like(th)], axis=1)
+    e.add_colloids_at(ureg.Quantity(pos, "micrometer"), dirs, ureg.Quantity(1.0, "micrometer"), type_colloid=0)
+    rng = np.random.default_rng(0)
+    D, H, A = VISION["n_cones"], 128, 4
+    net = dict(w1=rng.normal(size=(D, H)) * 0.5, b1=rng.normal(size=H) * 0.1, wa=rng.normal(size=(H, A)) * 0.2,
+               ba=np.zeros(A), wv=rng.normal(size=H) * 0.2, bv=np.zeros(1))
+    gt, gr = stokes(1.0)
+    actions = {"Translate": sw.Action(force=5.0 * gt), "RotateCCW": sw.Action(torque=np.array([0.0, 0.0, gr * 10.0])),
+               "RotateCW": sw.Action(torque=np.array([0.0, 0.0, -gr * 10.0])), "Nothing": sw.Action()}
+    box = np.array([BOX] * 3)
+    src = np.array([0.5 * BOX, 0.5 * BOX, 0.0])
+    agent = sw.DeviceAgent(
+        0, sw.FusedActorCritic(net),
+        GradientSensing(source=src, decay_function=decay.Linear(1.0, -1.0), box_length=box, reward_scale_factor=10, particle_type=0),
+        SubdividedVisionCones(VISION["range"], VISION["half_angle"], VISION["n_cones"], np.ones(N_AGENTS), detected_types=[0],
+                              particle_type=0),
+        actions, train=True, keep_trajectory=False, reward_mean=True)
+    ff = sw.ForceFunction({"0": agent})
+    agent.reset_agent(e.colloids)
+    e.integrate(max(W, 2), ff)          # first call: overlap removal (1000 steepest-descent steps), the checked chunk, warm-up
+    st0 = e._backend.stats()
+    agent.reward_means.clear()
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=e._backend.dev)
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    flush.fill_(1)
+    torch.cuda.synchronize()
+    a.record()
+    e.integrate(K, ff)
+    means = torch.stack(agent.reward_means)[:, 1].cpu()
+    b.record()
+    torch.cuda.synchronize()
+    ms = a.elapsed_time(b)
+    st1 = e._backend.stats()
+    # the same, one integrate(1) call per slice with the L2 flushed between the calls (flush outside the events)
+    agent.reward_means.clear()
+    ms_f = 0.0
+    for _ in range(K):
+        flush.fill_(1)
+        a.record()
+        e.integrate(1, ff)
+        m1 = agent.reward_means[-1].cpu()
+        b.record()
+        torch.cuda.synchronize()
+        ms_f += a.elapsed_time(b)
+    rec = {"api": "SwarmEngine.integrate(K, ForceFunction({'0': DeviceAgent(FusedActorCritic(5-128-4/1), GradientSensing, "
+                  "SubdividedVisionCones)}))", "value": N_AGENTS * STEPS_PER_SLICE * K / (ms * 1e-3), "unit": UNIT,
+           "ms_per_step": ms / K, "slices": K, "d2h_bytes_per_step": 8, "h2d_bytes_per_step": 0,
+           "gpu_launches_per_slice": (st1.launches - st0.launches) / K, "reward_mean_last": float(means[-1]),
+           "l2": "one integrate(K) call: no flush between its slices (the state is L2-resident in every arm)",
+           "flushed_per_call": {"ms_per_step": ms_f / K, "note": "K calls of integrate(1), 256 MiB L2 flush between the calls, each "
+                                "call ends with the engine's one synchronising counter check"},
+           "tiling": e._backend.tiling_stats(), "reward_mean_check": float(m1[1])}
+    e.finalize()
+    del flush
+    e._backend.close()
+    torch.cuda.empty_cache()
+    return rec
 
 
 def extra_records(args, world, rank, local):
@@ -514,6 +649,7 @@ def main():
     ap.add_argument("--cpu-steps", type=int, default=100, help="BD steps of the cpu_baseline sample")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-extra", action="store_true", help="skip the c5_domain / c3_envs records")
+    ap.add_argument("--no-engine", action="store_true", help="skip the e2e_engine record (SwarmEngine.integrate with a device agent)")
     ap.add_argument("--c5-agents", type=int, default=8_000_000)
     ap.add_argument("--c5-slices", type=int, default=5)
     ap.add_argument("--c5-k", type=int, default=33, help="steps between halo exchanges (halo = k * r_cut * 1.15)")

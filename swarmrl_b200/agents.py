@@ -184,7 +184,7 @@ class DeviceAgent(Agent):
     """
 
     def __init__(self, particle_type: int, policy, task, observable, actions: dict, train: bool = True,
-                 keep_trajectory: bool = True):
+                 keep_trajectory: bool = True, reward_mean: bool = False):
         self.particle_type = particle_type
         self.policy = policy
         self.task = task
@@ -195,6 +195,10 @@ class DeviceAgent(Agent):
         self.trajectory = TrajectoryInformation(particle_type=particle_type)
         self.last_rewards = None
         self.last_observable = None
+        # reward_mean=True: (sum, mean) of every reward evaluation stays on the device (trainer.py:92-95 takes the mean
+        # on the host); `reward_means` is the list of those 2-element device tensors, one D2H for a whole rollout
+        self.reward_mean = reward_mean
+        self.reward_means = []
         self._table = None
         self._idx = None
 
@@ -255,6 +259,8 @@ class DeviceAgent(Agent):
         if external_reward:
             rewards = rewards + external_reward
         self.last_rewards = rewards
+        if self.reward_mean:
+            self.reward_means.append(view.swarm.reduce_mean(rewards))
         if self.train and self.keep_trajectory:
             self.trajectory.rewards.append(rewards)
         self.kill_switch = self.task.kill_switch

@@ -26,11 +26,14 @@
 // quotient corrected by its residual: <= 1 ulp from the IEEE divisions of the generic path and the oracle, ~20
 // instead of ~85 instructions.  It matters because a warp runs this branch whenever ANY of its lanes is in contact,
 // which in a clustering active swarm is almost always.
+// Every product and sum below is spelled out (__dmul_rn / fma): nvcc otherwise decides per call site which
+// multiply of an expression it fuses into an FMA, and the four kernels that inline these helpers (resident, tiled,
+// stream, env) must produce the same bits for the same particle.
 __device__ __forceinline__ double swm_wca_factor(double r2, double sigma, double eps) {
   const double r = swm_rcp(r2);
-  const double f2 = swm_div_r(sigma * sigma, r2, r);
-  const double f6 = f2 * f2 * f2;
-  return swm_div_r(48.0 * eps * f6 * (f6 - 0.5), r2, r);
+  const double f2 = swm_div_r(__dmul_rn(sigma, sigma), r2, r);
+  const double f6 = __dmul_rn(__dmul_rn(f2, f2), f2);
+  return swm_div_r(__dmul_rn(__dmul_rn(__dmul_rn(48.0, eps), f6), __dsub_rn(f6, 0.5)), r2, r);
 }
 
 // pair force of one Verlet entry on particle (xi, yi) of type ti
@@ -42,7 +45,7 @@ __device__ __forceinline__ void bd2d_pair(const DevParams &P, double xi, double 
   double cut = P.wca_cut[ti][tj];
   if (r2 < __dmul_rn(cut, cut) && r2 > 0.0) {
     double fac = swm_wca_factor(r2, P.wca_sigma[ti][tj], P.wca_eps[ti][tj]);
-    Fx += fac * dx; Fy += fac * dy;
+    Fx = fma(fac, dx, Fx); Fy = fma(fac, dy, Fy);
   }
 }
 
@@ -56,15 +59,41 @@ __device__ __forceinline__ Bd2dSelf bd2d_self_forces(const DevParams &P, int ti,
   if (P.walls) {
     const double cutw = P.wall_cut[ti];
     // two separate accumulations per axis, in the oracle's order (lower wall, upper wall)
-    if (xi < cutw && xi > 0.0) o.wx += sw_wca_factor(xi * xi, P.wall_sigma[ti], P.wall_eps[ti]) * xi;
+    const double ws = P.wall_sigma[ti], we = P.wall_eps[ti];
+    if (xi < cutw && xi > 0.0) o.wx = fma(swm_wca_factor(__dmul_rn(xi, xi), ws, we), xi, o.wx);
     double d2 = P.box[0] - xi;
-    if (d2 < cutw && d2 > 0.0) o.wx -= sw_wca_factor(d2 * d2, P.wall_sigma[ti], P.wall_eps[ti]) * d2;
-    if (yi < cutw && yi > 0.0) o.wy += sw_wca_factor(yi * yi, P.wall_sigma[ti], P.wall_eps[ti]) * yi;
+    if (d2 < cutw && d2 > 0.0) o.wx = fma(-swm_wca_factor(__dmul_rn(d2, d2), ws, we), d2, o.wx);
+    if (yi < cutw && yi > 0.0) o.wy = fma(swm_wca_factor(__dmul_rn(yi, yi), ws, we), yi, o.wy);
     d2 = P.box[1] - yi;
-    if (d2 < cutw && d2 > 0.0) o.wy -= sw_wca_factor(d2 * d2, P.wall_sigma[ti], P.wall_eps[ti]) * d2;
+    if (d2 < cutw && d2 > 0.0) o.wy = fma(-swm_wca_factor(__dmul_rn(d2, d2), ws, we), d2, o.wy);
   }
-  o.sx = fsw * ex; o.sy = fsw * ey;
+  o.sx = __dmul_rn(fsw, ex); o.sy = __dmul_rn(fsw, ey);
   return o;
+}
+
+// The Brownian update of one particle from its total force (phase_step<2>, oracle: orc_bd_steps): velocity F / gamma
+// (per body axis when the friction is anisotropic), Euler-Maruyama step of position and angle.
+struct Bd2dConst { double gt1, gt2, r_gt1, r_gt2, sg_par, sg_per, sg_rot; };
+template <bool NOISE>
+__device__ __forceinline__ void bd2d_update(bool iso, const Bd2dConst &c, double dt, double Fx, double Fy, double ex, double ey,
+                                            double w, double g0, double g1, double g3, double &x, double &y, double &th,
+                                            double &vx, double &vy) {
+  if (iso) {
+    vx = swm_div_r(Fx, c.gt2, c.r_gt2); vy = swm_div_r(Fy, c.gt2, c.r_gt2);
+    x = fma(vx, dt, x); y = fma(vy, dt, y);
+    if (NOISE) { x = fma(c.sg_par, g0, x); y = fma(c.sg_par, g1, y); }
+  } else {
+    const double fpar = fma(Fx, ex, __dmul_rn(Fy, ey)), fper = fma(Fy, ex, -__dmul_rn(Fx, ey));
+    const double vpar = swm_div_r(fpar, c.gt2, c.r_gt2), vper = swm_div_r(fper, c.gt1, c.r_gt1);
+    vx = fma(vpar, ex, -__dmul_rn(vper, ey)); vy = fma(vpar, ey, __dmul_rn(vper, ex));
+    x = fma(vx, dt, x); y = fma(vy, dt, y);
+    if (NOISE) {
+      const double spar = __dmul_rn(c.sg_par, g0), sper = __dmul_rn(c.sg_per, g1);
+      x += fma(spar, ex, -__dmul_rn(sper, ey)); y += fma(spar, ey, __dmul_rn(sper, ex));
+    }
+  }
+  th = fma(w, dt, th);
+  if (NOISE) th = fma(c.sg_rot, g3, th);
 }
 
 // PIPE = 1 (default): the Philox words of step s+1 are drawn between the ISSUE of step s's neighbour loads and their
@@ -72,7 +101,7 @@ __device__ __forceinline__ Bd2dSelf bd2d_self_forces(const DevParams &P, int ti,
 // of the neighbour positions and the barrier, are covered by work that depends on the particle alone.  PIPE = 0 keeps
 // the whole draw behind the barrier (round 1's order; SWARM_B200_RES_PIPE=0 selects it for A/B runs).
 template <bool NOISE, int PIPE>
-__global__ void __maxnreg__(SW_RES_MAXREG) k_bd2d_resident(const __grid_constant__ DevParams P, DevArrays A, RunArgs R) {
+__global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_resident(const __grid_constant__ DevParams P, DevArrays A, RunArgs R) {
   Ctl *ctl = A.ctl;
   if (ldcg(&ctl->halted)) return;
   unsigned int epoch = 0;
@@ -207,24 +236,9 @@ __global__ void __maxnreg__(SW_RES_MAXREG) k_bd2d_resident(const __grid_constant
       Fx += sf.sx; Fy += sf.sy;
       if (A.fex) { Fx += fxe; Fy += fye; }
       // ---- Brownian update (phase_step<2>) ------------------------------------------------------
-      double xn, yn;
-      if (iso) {
-        vx_l = swm_div_r(Fx, gt2, r_gt2); vy_l = swm_div_r(Fy, gt2, r_gt2);
-        xn = xi + vx_l * dt; yn = yi + vy_l * dt;
-        if (NOISE) { xn += sg_par * g0; yn += sg_par * g1; }
-      } else {
-        double fpar = Fx * ex + Fy * ey, fper = -Fx * ey + Fy * ex;
-        double vpar = swm_div_r(fpar, gt2, r_gt2), vper = swm_div_r(fper, gt1, r_gt1);
-        vx_l = vpar * ex - vper * ey; vy_l = vpar * ey + vper * ex;
-        xn = xi + vx_l * dt; yn = yi + vy_l * dt;
-        if (NOISE) {
-          double spar = sg_par * g0, sper = sg_per * g1;
-          xn += spar * ex - sper * ey; yn += spar * ey + sper * ex;
-        }
-      }
-      double thn = th + w * dt;
-      if (NOISE) thn += sg_rot * g3;
-      xi = xn; yi = yn; th = thn;
+      const Bd2dConst cc = {gt1, gt2, r_gt1, r_gt2, sg_par, sg_per, sg_rot};
+      bd2d_update<NOISE>(iso, cc, dt, Fx, Fy, ex, ey, w, g0, g1, g3, xi, yi, th, vx_l, vy_l);
+      const double xn = xi, yn = yi;
       A.x[nxt][i] = xn; A.y[nxt][i] = yn;
       double ddx = xn - xr, ddy = yn - yr;
       moved = (ddx * ddx + ddy * ddy) > lim2;
@@ -357,24 +371,10 @@ __device__ __forceinline__ bool bd2d_step_stream(const DevParams &P, const DevAr
   double g0 = pg0, g1 = pg1, g3 = pg3;  // drawn behind the previous step's barrier for the thread's first particle
   if (NOISE && !have_g) swm_gaussians_xyt(P.seed, pid, step, g0, g1, g3);
   const double dt = P.dt;
-  double xn, yn, vx, vy;
-  if (c.gt1 == c.gt2) {
-    vx = swm_div_r(Fx, c.gt2, c.r_gt2); vy = swm_div_r(Fy, c.gt2, c.r_gt2);
-    xn = xi + vx * dt; yn = yi + vy * dt;
-    if (NOISE) { xn += c.sg_par * g0; yn += c.sg_par * g1; }
-  } else {
-    const double fpar = Fx * ex + Fy * ey, fper = -Fx * ey + Fy * ex;
-    const double vpar = swm_div_r(fpar, c.gt2, c.r_gt2), vper = swm_div_r(fper, c.gt1, c.r_gt1);
-    vx = vpar * ex - vper * ey; vy = vpar * ey + vper * ex;
-    xn = xi + vx * dt; yn = yi + vy * dt;
-    if (NOISE) {
-      const double spar = c.sg_par * g0, sper = c.sg_per * g1;
-      xn += spar * ex - sper * ey; yn += spar * ey + sper * ex;
-    }
-  }
+  double xn = xi, yn = yi, thn = th, vx, vy;
   const double w = swm_div_r(tqz, c.gr0, c.r_gr0);
-  double thn = th + w * dt;
-  if (NOISE) thn += c.sg_rot * g3;
+  const Bd2dConst cc = {c.gt1, c.gt2, c.r_gt1, c.r_gt2, c.sg_par, c.sg_per, c.sg_rot};
+  bd2d_update<NOISE>(c.gt1 == c.gt2, cc, dt, Fx, Fy, ex, ey, w, g0, g1, g3, xn, yn, thn, vx, vy);
   A.theta[i] = thn;
   A.x[nxt][i] = xn; A.y[nxt][i] = yn;
   if (last) {
@@ -592,24 +592,8 @@ __global__ void __launch_bounds__(SW_ENV_THREADS) k_bd2d_env(const __grid_consta
     Fx += sf.wx; Fy += sf.wy;
     Fx += sf.sx; Fy += sf.sy;
     if (A.fex) { Fx += fxe; Fy += fye; }
-    double xn, yn;
-    if (iso) {
-      vx_l = swm_div_r(Fx, gt2, r_gt2); vy_l = swm_div_r(Fy, gt2, r_gt2);
-      xn = xi + vx_l * dt; yn = yi + vy_l * dt;
-      if (NOISE) { xn += sg_par * g0; yn += sg_par * g1; }
-    } else {
-      double fpar = Fx * ex + Fy * ey, fper = -Fx * ey + Fy * ex;
-      double vpar = swm_div_r(fpar, gt2, r_gt2), vper = swm_div_r(fper, gt1, r_gt1);
-      vx_l = vpar * ex - vper * ey; vy_l = vpar * ey + vper * ex;
-      xn = xi + vx_l * dt; yn = yi + vy_l * dt;
-      if (NOISE) {
-        double spar = sg_par * g0, sper = sg_per * g1;
-        xn += spar * ex - sper * ey; yn += spar * ey + sper * ex;
-      }
-    }
-    double thn = th + w * dt;
-    if (NOISE) thn += sg_rot * g3;
-    xi = xn; yi = yn; th = thn;
+    const Bd2dConst cc = {gt1, gt2, r_gt1, r_gt2, sg_par, sg_per, sg_rot};
+    bd2d_update<NOISE>(iso, cc, dt, Fx, Fy, ex, ey, w, g0, g1, g3, xi, yi, th, vx_l, vy_l);
   }
   if (act) {
     A.x[0][i] = xi; A.y[0][i] = yi; A.theta[i] = th;

@@ -217,6 +217,174 @@ __global__ void k_vis_pack(long long n, const int *items, const double *x, const
   scol[k] = (t >= 0 && t < n_type_col) ? type_col[t] : -1;
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// k_vis_build -- the whole grid construction above (bounding box, grid, cell count, cell-start scan, placement,
+// per-cell order, packed copies) in ONE cooperative launch with five grid barriers instead of ten dependent launches
+// of 3-8 us each (profiles/r01_launch_shares.txt: 45 us of a 690 us slice).  Same arithmetic, phase by phase, as the
+// k_vis_* / k_scan_* kernels, which stay as the fallback for devices without cooperative launch.
+// The memset before the launch zeroes VisBuild and count[]; the bounding box is kept as two maxima (the minimum as
+// the maximum of the complement) so that zero is the neutral start of both.
+// ---------------------------------------------------------------------------------------------
+struct VisBuild {
+  unsigned long long mnc[3], mx[3];   // max of ~enc(v), max of enc(v)
+  unsigned int bar;
+  unsigned int pad;
+};
+
+__device__ __forceinline__ void vis_grid_barrier(unsigned int *counter, unsigned int &epoch) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    epoch += gridDim.x;
+    __threadfence();
+    atomicAdd(counter, 1u);
+    while (*((volatile unsigned int *)counter) < epoch) {
+    }
+    __threadfence();
+  }
+  __syncthreads();
+}
+
+#define VISB_T 512
+__global__ void __launch_bounds__(VISB_T) k_vis_build(long long n, const double *x, const double *y, const double *z,
+                                                      const double *radii, const int *species, const __grid_constant__ DevParams P,
+                                                      const int *type_col, int n_type_col, double range, long long ncell_max,
+                                                      VisBuild *B, VisGrid *G, int *count, int *start, int *fill, int *cellid,
+                                                      int *items, double *sx, double *sy, double *sz, double *sr, int *scol,
+                                                      double *out, long long out_len) {
+  unsigned int epoch = 0;
+  const long long gtid = (long long)blockIdx.x * blockDim.x + threadIdx.x, gsz = (long long)gridDim.x * blockDim.x;
+  __shared__ unsigned long long smn[3][VISB_T / 32], smx[3][VISB_T / 32];
+  __shared__ VisGrid g;
+  // ---- phase 0: zero the output, bounding box of the unfolded positions ------------------------------------------
+  for (long long i = gtid; i < out_len; i += gsz) out[i] = 0.0;
+  {
+    unsigned long long mn[3] = {0ULL, 0ULL, 0ULL}, mx[3] = {0ULL, 0ULL, 0ULL};
+    for (long long i = gtid; i < n; i += gsz) {
+      const unsigned long long e[3] = {enc_double(x[i]), enc_double(y[i]), enc_double(z[i])};
+#pragma unroll
+      for (int a = 0; a < 3; ++a) { mn[a] = max(mn[a], ~e[a]); mx[a] = max(mx[a], e[a]); }
+    }
+#pragma unroll
+    for (int a = 0; a < 3; ++a)
+      for (int o = 16; o > 0; o >>= 1) {
+        mn[a] = max(mn[a], __shfl_xor_sync(0xffffffffu, mn[a], o));
+        mx[a] = max(mx[a], __shfl_xor_sync(0xffffffffu, mx[a], o));
+      }
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    if (l == 0)
+      for (int a = 0; a < 3; ++a) { smn[a][w] = mn[a]; smx[a][w] = mx[a]; }
+    __syncthreads();
+    if (threadIdx.x < 3) {
+      const int a = threadIdx.x;
+      unsigned long long m0 = 0ULL, m1 = 0ULL;
+      for (int k = 0; k < VISB_T / 32; ++k) { m0 = max(m0, smn[a][k]); m1 = max(m1, smx[a][k]); }
+      atomicMax(&B->mnc[a], m0);
+      atomicMax(&B->mx[a], m1);
+    }
+  }
+  vis_grid_barrier(&B->bar, epoch);
+  // ---- phase 1: the grid (every CTA computes the same one), cell of every particle, histogram -----------------------
+  if (threadIdx.x == 0) {
+    double ext[3];
+    for (int a = 0; a < 3; ++a) {
+      double lo = dec_double(~__ldcg(&B->mnc[a])), hi = dec_double(__ldcg(&B->mx[a]));
+      if (!(hi >= lo)) { lo = 0.0; hi = 0.0; }
+      g.lo[a] = lo;
+      ext[a] = hi - lo;
+    }
+    double cs = range > 0.0 ? range : 1.0;
+    for (;;) {
+      long long tot = 1;
+      for (int a = 0; a < 3; ++a) {
+        double f = floor(ext[a] / cs) + 1.0;
+        int nc = (f > 1048576.0) ? 1048576 : (int)f;
+        if (nc < 1) nc = 1;
+        g.nc[a] = nc;
+        tot *= nc;
+        if (tot > ncell_max) break;
+      }
+      if (tot <= ncell_max) { g.ncell = (int)tot; break; }
+      cs *= 1.5;
+    }
+    g.cs = cs;
+    g.inv_cs = 1.0 / cs;
+    if (blockIdx.x == 0) *G = g;   // for the cone kernel
+  }
+  __syncthreads();
+  for (long long i = gtid; i < n; i += gsz) {
+    const int cx = vis_coord(x[i], g.lo[0], g.inv_cs, g.nc[0]);
+    const int cy = vis_coord(y[i], g.lo[1], g.inv_cs, g.nc[1]);
+    const int cz = vis_coord(z[i], g.lo[2], g.inv_cs, g.nc[2]);
+    const int c = (cz * g.nc[1] + cy) * g.nc[0] + cx;
+    cellid[i] = c;
+    atomicAdd(&count[c], 1);
+  }
+  vis_grid_barrier(&B->bar, epoch);
+  // ---- phase 2: exclusive scan of the histogram = cell start (CTA 0; the grid has ~3 particles per cell) -------------
+  if (blockIdx.x == 0) {
+    __shared__ int wsum[VISB_T / 32];
+    __shared__ int carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int m = g.ncell + 1;
+    for (int b0 = 0; b0 < m; b0 += VISB_T) {
+      const int b = b0 + threadIdx.x;
+      const int v = (b < m) ? __ldcg(&count[b]) : 0;
+      int inc = v;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= d) inc += t;
+      }
+      if (lane == 31) wsum[warp] = inc;
+      __syncthreads();
+      if (warp == 0) {
+        const int wv = (lane < VISB_T / 32) ? wsum[lane] : 0;
+        int winc = wv;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+          const int t = __shfl_up_sync(0xffffffffu, winc, d);
+          if (lane >= d) winc += t;
+        }
+        if (lane < VISB_T / 32) wsum[lane] = winc - wv;
+      }
+      __syncthreads();
+      const int excl = carry + wsum[warp] + inc - v;
+      if (b < m) { start[b] = excl; fill[b] = excl; }
+      __syncthreads();
+      if (threadIdx.x == VISB_T - 1) carry = excl + v;
+      __syncthreads();
+    }
+  }
+  vis_grid_barrier(&B->bar, epoch);
+  // ---- phase 3: placement -----------------------------------------------------------------------------------------
+  for (long long i = gtid; i < n; i += gsz) {
+    const int p = atomicAdd(&fill[cellid[i]], 1);
+    items[p] = (int)i;
+  }
+  vis_grid_barrier(&B->bar, epoch);
+  // ---- phase 4: ids of a cell in ascending order (deterministic; == a stable radix sort) -----------------------------
+  for (long long c = gtid; c < g.ncell; c += gsz) {
+    const int b = __ldcg(&start[c]), e = __ldcg(&start[c + 1]);
+    for (int k = b + 1; k < e; ++k) {
+      const int v = __ldcg(&items[k]);
+      int j = k;
+      while (j > b && __ldcg(&items[j - 1]) > v) { items[j] = __ldcg(&items[j - 1]); --j; }
+      items[j] = v;
+    }
+  }
+  vis_grid_barrier(&B->bar, epoch);
+  // ---- phase 5: packed, cell-ordered copies ---------------------------------------------------------------------------
+  for (long long k = gtid; k < n; k += gsz) {
+    const int i = __ldcg(&items[k]);
+    sx[k] = x[i]; sy[k] = y[i]; sz[k] = z[i]; sr[k] = radii[i];
+    const int t = P.sp_type[species[i]];
+    scol[k] = (t >= 0 && t < n_type_col) ? type_col[t] : -1;
+  }
+}
+
 #define VIS_MAX_ACC 64
 
 // one thread per cell-ordered slot; observers (row_of >= 0) accumulate their cones
@@ -489,6 +657,38 @@ __global__ void __launch_bounds__(PF_TILE) k_pair_field(long long n, const doubl
 
 // ---- deterministic two-stage sum -------------------------------------------------------------
 #define RED_BLOCKS 296
+// One launch: every CTA writes its slice's sum, takes a ticket, and the CTA that draws the last ticket adds the
+// partials in a fixed order (what k_reduce_final did in a second launch) and re-arms the ticket.
+__global__ void k_reduce_mean(long long n, const double *in, double *partial, unsigned int *ticket, double *out2) {
+  __shared__ double ws[8];
+  __shared__ bool last;
+  long long per = (n + RED_BLOCKS - 1) / RED_BLOCKS;
+  long long lo = (long long)blockIdx.x * per, hi = min(n, lo + per);
+  double s = 0.0;
+  for (long long i = lo + threadIdx.x; i < hi; i += blockDim.x) s += in[i];
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    for (int k = 0; k < (int)(blockDim.x >> 5); ++k) t += ws[k];
+    partial[blockIdx.x] = t;
+    __threadfence();
+    last = (atomicAdd(ticket, 1u) == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!last || threadIdx.x >= 32) return;
+  __threadfence();
+  double t = 0.0;
+  for (int k = threadIdx.x; k < RED_BLOCKS; k += 32) t += __ldcg(&partial[k]);
+  for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+  if (threadIdx.x == 0) {
+    out2[0] = t;
+    out2[1] = (n > 0) ? t / (double)n : 0.0;
+    *ticket = 0u;
+  }
+}
+
 __global__ void k_reduce_partial(long long n, const double *in, double *partial) {
   __shared__ double ws[8];
   // fixed, grid-independent assignment: block b owns a contiguous slice
@@ -573,11 +773,19 @@ extern "C" int swarm_obs_position(swarm_t *s, const int32_t *row_of, const doubl
 extern "C" int swarm_reduce_mean(swarm_t *s, const double *in, int64_t n, double *out2, void *stream) {
   if (!s || n < 0 || !out2 || (n > 0 && !in)) { sw_set_error("bad arguments"); return SWARM_ERR_INVALID; }
   SW_CUDA(cudaSetDevice(s->cfg.device));
-  if (!s->red_scratch) SW_CUDA(cudaMalloc((void **)&s->red_scratch, sizeof(double) * RED_BLOCKS));
+  if (!s->red_scratch) {
+    SW_CUDA(cudaMalloc((void **)&s->red_scratch, sizeof(double) * (RED_BLOCKS + 1)));
+    SW_CUDA(cudaMemset(s->red_scratch, 0, sizeof(double) * (RED_BLOCKS + 1)));   // [RED_BLOCKS]: the ticket
+  }
   cudaStream_t st = (cudaStream_t)stream;
-  k_reduce_partial<<<RED_BLOCKS, 256, 0, st>>>(n, in, s->red_scratch);
-  k_reduce_final<<<1, 32, 0, st>>>(n, s->red_scratch, out2);
-  s->launches += 2;
+  if (getenv("SWARM_B200_REDUCE_TWO_PASS")) {
+    k_reduce_partial<<<RED_BLOCKS, 256, 0, st>>>(n, in, s->red_scratch);
+    k_reduce_final<<<1, 32, 0, st>>>(n, s->red_scratch, out2);
+    s->launches += 2;
+  } else {
+    k_reduce_mean<<<RED_BLOCKS, 256, 0, st>>>(n, in, s->red_scratch, (unsigned int *)(s->red_scratch + RED_BLOCKS), out2);
+    s->launches += 1;
+  }
   SW_CUDA(cudaGetLastError());
   return SWARM_OK;
 }
@@ -594,7 +802,6 @@ extern "C" int swarm_obs_vision(swarm_t *s, const int32_t *row_of, int64_t rows,
   const DevArrays &A = s->A;
   const long long n = A.n;
   cudaStream_t st = (cudaStream_t)stream;
-  if (rows > 0) SW_CUDA(cudaMemsetAsync(out, 0, sizeof(double) * (size_t)rows * (size_t)n_cones * (size_t)n_cols, st));
   if (n == 0 || rows == 0) return SWARM_OK;
   long long ncell_max = 4 * n;
   if (ncell_max < 4096) ncell_max = 4096;
@@ -605,6 +812,7 @@ extern "C" int swarm_obs_vision(swarm_t *s, const int32_t *row_of, int64_t rows,
   size_t off = 0;
   auto carve = [&](size_t bytes) { size_t o = off; off += align256(bytes); return o; };
   size_t o_grid = carve(sizeof(VisGrid));
+  size_t o_build = carve(sizeof(VisBuild));   // directly in front of count[]: one memset zeroes both
   size_t o_count = carve(sizeof(int) * (size_t)m), o_start = carve(sizeof(int) * (size_t)m), o_fill = carve(sizeof(int) * (size_t)m);
   size_t o_tiles = carve(sizeof(int) * (size_t)ntiles);
   size_t o_cell = carve(sizeof(int) * (size_t)n), o_items = carve(sizeof(int) * (size_t)n), o_col = carve(sizeof(int) * (size_t)n);
@@ -624,6 +832,32 @@ extern "C" int swarm_obs_vision(swarm_t *s, const int32_t *row_of, int64_t rows,
   double *sx = (double *)(base + o_sx), *sy = (double *)(base + o_sy), *sz = (double *)(base + o_sz), *sr = (double *)(base + o_sr);
   const int T = 256, B = sw_blocks(n, T);
   const int gb = B < 4 * s->num_sms ? B : 4 * s->num_sms;
+  const long long out_len = (long long)rows * n_cones * n_cols;
+  bool fused = s->persistent && !getenv("SWARM_B200_VIS_UNFUSED");
+  int bpsm = 0;
+  if (fused) {
+    SW_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bpsm, k_vis_build, VISB_T, 0));
+    fused = bpsm >= 1;
+  }
+  if (fused) {
+    VisBuild *VB = (VisBuild *)(base + o_build);
+    SW_CUDA(cudaMemsetAsync(VB, 0, (size_t)((char *)(count + m) - (char *)VB), st));
+    long long want = (n + VISB_T - 1) / VISB_T;
+    if (bpsm > 2) bpsm = 2;
+    const long long maxb = (long long)s->num_sms * bpsm;
+    int grid = (int)(want < maxb ? (want > 0 ? want : 1) : maxb);
+    DevParams P = s->P;
+    long long nn = n, ncm = ncell_max, ol = out_len;
+    const double *px = A.x[0], *py = A.y[0], *pz = A.z[0];
+    const int *spc = A.species;
+    double rng_ = vision_range;
+    int ntc = n_type_col;
+    void *args[] = {&nn, &px, &py, &pz, &radii, &spc, &P, &type_col, &ntc, &rng_, &ncm, &VB, &G, &count, &start, &fill,
+                    &cellid, &items, &sx, &sy, &sz, &sr, &scol, &out, &ol};
+    SW_CUDA(cudaLaunchCooperativeKernel((void *)k_vis_build, dim3(grid), dim3(VISB_T), args, 0, st));
+    s->launches += 1;
+  } else {
+  if (rows > 0) SW_CUDA(cudaMemsetAsync(out, 0, sizeof(double) * (size_t)rows * (size_t)n_cones * (size_t)n_cols, st));
   k_vis_init<<<gb > 0 ? gb : 1, T, 0, st>>>(G, count, ncell_max);
   k_vis_bbox<<<gb > 0 ? gb : 1, T, 0, st>>>(n, A.x[0], A.y[0], A.z[0], G);
   k_vis_grid<<<1, 32, 0, st>>>(G, vision_range, ncell_max);
@@ -634,6 +868,8 @@ extern "C" int swarm_obs_vision(swarm_t *s, const int32_t *row_of, int64_t rows,
   k_vis_fill<<<B, T, 0, st>>>(n, cellid, fill, items);
   k_vis_sortcell<<<sw_blocks(ncell_max, T), T, 0, st>>>(G, start, items);
   k_vis_pack<<<B, T, 0, st>>>(n, items, A.x[0], A.y[0], A.z[0], radii, A.species, s->P, type_col, n_type_col, sx, sy, sz, sr, scol);
+  s->launches += 10;
+  }
   if (n_cones * n_cols <= VISW_MAX_ACC && !getenv("SWARM_B200_VIS_SERIAL")) {
     const size_t smem = sizeof(double) * (size_t)(n_cones * n_cols) * VISW_THREADS;
     const char *eg = getenv("SWARM_B200_VIS_GROUP");
@@ -652,7 +888,7 @@ extern "C" int swarm_obs_vision(swarm_t *s, const int32_t *row_of, int64_t rows,
     k_vis_cones<<<sw_blocks(n, 128), 128, 0, st>>>(n, items, row_of, G, start, sx, sy, sz, sr, scol, s->P.n_dims, A.theta, A.q0,
                                                    A.q1, A.q2, A.q3, dirs, vision_range, half_angle, n_cones, n_cols, out);
   }
-  s->launches += 11;
+  s->launches += 1;
   SW_CUDA(cudaGetLastError());
   return SWARM_OK;
 }

@@ -53,7 +53,7 @@ __device__ __forceinline__ void tile_st_release(unsigned int *p, unsigned int v)
 }
 
 template <bool NOISE>
-__global__ void __maxnreg__(SW_RES_MAXREG) k_bd2d_tiled(const __grid_constant__ DevParams P, DevArrays A, DevArrays T, TileArgs G,
+__global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_tiled(const __grid_constant__ DevParams P, DevArrays A, DevArrays T, TileArgs G,
                                                         RunArgs R) {
   Ctl *ctl = A.ctl;
   if (ldcg(&ctl->halted)) return;
@@ -215,6 +215,11 @@ __global__ void __maxnreg__(SW_RES_MAXREG) k_bd2d_tiled(const __grid_constant__ 
   bool viol = false;        // a position of this thread used for forces since the last rebuild was beyond skin / 2
   double dmax2 = 0.0;       // its largest displacement^2 in the period
 
+#ifdef SW_TIMING
+  // clock64 per phase of CTA 0: slots 0..5 from the first particle thread, 6..7 from the flag thread (swarm_debug_timing)
+  long long tp[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tc = clock64();
+  const bool prof = (blockIdx.x == 0) && (threadIdx.x == 32 || threadIdx.x == 0);
+#endif
   long long s = 0;          // steps completed in this launch
   long long s_ck = 0;       // step index of the checkpoint
   bool ck_start = true;     // checkpoint = launch start (state still in the caller's arrays)
@@ -310,6 +315,7 @@ __global__ void __maxnreg__(SW_RES_MAXREG) k_bd2d_tiled(const __grid_constant__ 
         have_partners = true;
       }
     }
+    SW_TICK(0);   // synchronisation points (validation, rebuild)
     // ================= one Brownian step: read buffer cur, write buffer nxt ==========================================
     const int cur = (int)(e & 1u), nxt = cur ^ 1;
     const bool last = (s == R.n_steps - 1);
@@ -354,34 +360,20 @@ __global__ void __maxnreg__(SW_RES_MAXREG) k_bd2d_tiled(const __grid_constant__ 
       Fx += __dmul_rn(fsw, ex); Fy += __dmul_rn(fsw, ey);   // product rounded on its own, as in the other kernels
       if (A.fex) { Fx += sfx[ptid]; Fy += sfy[ptid]; }
       const Bd2dSpecies &c = S[sp];
-      double xn, yn;
-      if (iso) {
-        const double gt2 = c.gt2, r_gt2 = c.r_gt2;
-        vx_l = swm_div_r(Fx, gt2, r_gt2); vy_l = swm_div_r(Fy, gt2, r_gt2);
-        xn = xi + vx_l * dt; yn = yi + vy_l * dt;
-        if (NOISE) { const double sg = c.sg_par; xn += sg * g0; yn += sg * g1; }
-      } else {
-        double fpar = Fx * ex + Fy * ey, fper = -Fx * ey + Fy * ex;
-        double vpar = swm_div_r(fpar, c.gt2, c.r_gt2), vper = swm_div_r(fper, c.gt1, c.r_gt1);
-        vx_l = vpar * ex - vper * ey; vy_l = vpar * ey + vper * ex;
-        xn = xi + vx_l * dt; yn = yi + vy_l * dt;
-        if (NOISE) {
-          double spar = c.sg_par * g0, sper = c.sg_per * g1;
-          xn += spar * ex - sper * ey; yn += spar * ey + sper * ex;
-        }
-      }
-      double thn = th + w * dt;
-      if (NOISE) thn += c.sg_rot * g3;
-      xi = xn; yi = yn; th = thn;
-      sx[nxt][ptid] = xn; sy[nxt][ptid] = yn;
-      if (exported) { T.x[nxt][slot] = xn; T.y[nxt][slot] = yn; }
+      const Bd2dConst cc = {c.gt1, c.gt2, c.r_gt1, c.r_gt2, c.sg_par, c.sg_per, c.sg_rot};
+      bd2d_update<NOISE>(iso, cc, dt, Fx, Fy, ex, ey, w, g0, g1, g3, xi, yi, th, vx_l, vy_l);
+      sx[nxt][ptid] = xi; sy[nxt][ptid] = yi;
+      if (exported) { T.x[nxt][slot] = xi; T.y[nxt][slot] = yi; }
     }
+    SW_TICK(1);   // pair forces + update
     // the next iteration is a grid-wide synchronisation point: its barrier replaces the neighbourhood barrier
     const bool next_sync = (since + 1 >= K) || last;
     if (threadIdx.x < 32) {
       // ---- flag warp: all rim stores of the CTA done -> publish the epoch -> wait for the partners' -----------------
       asm volatile("barrier.cta.sync 1, %0;" ::"r"((int)blockDim.x) : "memory");
+      SW_TICK(2);   // flag warp: until every particle warp has stored
       if (threadIdx.x == 0) tile_st_release(&G.flags[me * 32], e + 1u);
+      SW_TICK(6);   // flag thread: fence + release
       if (!next_sync) {
         const int np = s_np;
         for (int p = (int)threadIdx.x; p < np; p += 32) {
@@ -391,13 +383,23 @@ __global__ void __maxnreg__(SW_RES_MAXREG) k_bd2d_tiled(const __grid_constant__ 
         }
       }
       __syncwarp();
+      SW_TICK(7);   // flag thread: partners' flags
     } else {
       asm volatile("barrier.cta.arrive 1, %0;" ::"r"((int)blockDim.x) : "memory");
+      SW_TICK(2);
       if (act && !last) local_inputs(R.step0 + (u64)(s + 1));   // step s+1's particle-local work hides the flag wait
     }
+    SW_TICK(4);   // particle-local work of the next step
     __syncthreads();
+    SW_TICK(5);   // wait for the flag warp (partners)
     ++s; ++since; ++e;
   }
+#ifdef SW_TIMING
+  if (prof) {
+    if (threadIdx.x == 0) { ctl->tprof[6] += tp[6]; ctl->tprof[7] += tp[7]; }
+    else for (int k = 0; k < 6; ++k) ctl->tprof[k] += tp[k];
+  }
+#endif
 
   // ---- results back to the caller's arrays (indexed by id) --------------------------------------------------------
   if (act) {

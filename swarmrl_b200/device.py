@@ -87,6 +87,7 @@ class DeviceSwarm:
             self._set_walls(walls)
         self.n = 0
         self._hold = []
+        self._row_maps, self._sensed = {}, {}
 
     # ------------------------------------------------------------------ tables
     def _set_species(self, species):
@@ -135,6 +136,7 @@ class DeviceSwarm:
         pos = np.asarray(pos, dtype=np.float64).reshape(-1, 3)
         n = pos.shape[0]
         self.n = n
+        self._row_maps, self._sensed = {}, {}
         f64 = dict(dtype=torch.float64, device=self.dev)
         m = max(n, 1)
         # one allocation per field group; rows are the SoA components
@@ -319,19 +321,26 @@ class DeviceSwarm:
 
     # ------------------------------------------------------------- observables
     def row_map(self, particle_type):
-        """int32 device tensor: output row of every particle of `particle_type`, else -1."""
-        rows = -np.ones(max(self.n, 1), dtype=np.int32)
-        sel = np.nonzero(self.ptype_host == int(particle_type))[0]
-        rows[sel] = np.arange(len(sel), dtype=np.int32)
-        return self.torch.from_numpy(rows).to(self.dev), len(sel)
+        """int32 device tensor: output row of every particle of `particle_type`, else -1.  Cached per type until the
+        next set_state (the types of the bound particles do not change): no host work or copy on the slice path."""
+        key = int(particle_type)
+        hit = self._row_maps.get(key)
+        if hit is None:
+            rows = -np.ones(max(self.n, 1), dtype=np.int32)
+            sel = np.nonzero(self.ptype_host == key)[0]
+            rows[sel] = np.arange(len(sel), dtype=np.int32)
+            hit = (self.torch.from_numpy(rows).to(self.dev), len(sel))
+            self._row_maps[key] = hit
+        return hit
 
     def obs_field(self, row_of, n_rows, src, box_length, hist, decay=_lib.DECAY_NONE, c0=0.0, c1=0.0,
                   scale=1.0, clip=False, want_dist=True):
         torch = self.torch
         f64 = dict(dtype=torch.float64, device=self.dev)
-        out = torch.zeros(max(n_rows, 1), **f64) if decay != _lib.DECAY_NONE else None
-        dn = torch.zeros(max(n_rows, 1), **f64) if want_dist else None
-        dp = torch.zeros(max(n_rows, 1), **f64) if want_dist else None
+        # every row belongs to one particle and the kernel writes it: no fill needed
+        out = torch.empty(max(n_rows, 1), **f64) if decay != _lib.DECAY_NONE else None
+        dn = torch.empty(max(n_rows, 1), **f64) if want_dist else None
+        dp = torch.empty(max(n_rows, 1), **f64) if want_dist else None
         s3 = (C.c_double * 3)(*[float(v) for v in src])
         b3 = (C.c_double * 3)(*[float(v) for v in box_length])
         _lib.check(self.lib.swarm_obs_field(
@@ -344,7 +353,7 @@ class DeviceSwarm:
 
     def obs_vision(self, row_of, n_rows, vision_range, half_angle, n_cones, radii, type_col, n_cols, dirs=None):
         torch = self.torch
-        out = torch.zeros((max(n_rows, 1), n_cones, n_cols), dtype=torch.float64, device=self.dev)
+        out = torch.empty((max(n_rows, 1), n_cones, n_cols), dtype=torch.float64, device=self.dev)  # zeroed by the call
         _lib.check(self.lib.swarm_obs_vision(
             self.h, row_of.data_ptr(), int(n_rows), float(vision_range), float(half_angle), int(n_cones),
             radii.data_ptr(), type_col.data_ptr(), int(type_col.numel()), int(n_cols),
@@ -352,9 +361,14 @@ class DeviceSwarm:
         return out[:n_rows]
 
     def sensed_index(self, sensing_type):
-        """int32 device tensor of the particles of `sensing_type`, ascending (the reference's `test_points`)."""
-        sel = np.nonzero(self.ptype_host == int(sensing_type))[0].astype(np.int32)
-        return self.torch.from_numpy(sel).to(self.dev), len(sel)
+        """int32 device tensor of the particles of `sensing_type`, ascending (the reference's `test_points`); cached."""
+        key = int(sensing_type)
+        hit = self._sensed.get(key)
+        if hit is None:
+            sel = np.nonzero(self.ptype_host == key)[0].astype(np.int32)
+            hit = (self.torch.from_numpy(sel).to(self.dev), len(sel))
+            self._sensed[key] = hit
+        return hit
 
     def obs_pair_field(self, row_of, n_rows, sensed, n_sensed, box_length, hist_rows, decay, c0, c1, scale=1.0, clip_mode=0,
                        init_only=False):
@@ -398,7 +412,7 @@ class DeviceSwarm:
 
     def reduce_mean(self, values):
         """(sum, mean) of a 1-D fp64 device tensor, deterministic order."""
-        out = self.torch.zeros(2, dtype=self.torch.float64, device=self.dev)
+        out = self.torch.empty(2, dtype=self.torch.float64, device=self.dev)
         v = values.contiguous()
         _lib.check(self.lib.swarm_reduce_mean(self.h, v.data_ptr(), int(v.numel()), out.data_ptr(), self._stream()))
         return out

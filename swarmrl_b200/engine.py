@@ -249,9 +249,11 @@ class SwarmEngine(Engine):
         self._pos, self._dir, self._types_l, self._props = [], [], [], []
         self._ext_force = {}
         self._walls = None
-        self._types = np.zeros(0, dtype=np.int64)
+        self._types_cache = np.zeros(0, dtype=np.int64)
         self._backend = None
         self._state_version = 0
+        self._capacity_proven = False   # first device-path chunk has run with a check (see _run_chunk)
+        self._unchecked_steps = 0
 
     # ------------------------------------------------------------------ setup
     def _init_unit_system(self):
@@ -298,6 +300,13 @@ class SwarmEngine(Engine):
     def _check_already_initialised(self):
         if self.integration_initialised:
             raise RuntimeError("You cannot change the system configuration after the first call to integrate()")
+
+    @property
+    def _types(self):
+        """Types of the staged particles as an array (rebuilt only when particles were added since the last look)."""
+        if len(self._types_cache) != len(self._types_l):
+            self._types_cache = np.array(self._types_l, dtype=np.int64)
+        return self._types_cache
 
     @property
     def n_colloids(self):
@@ -361,7 +370,6 @@ class SwarmEngine(Engine):
         self._dir.append(init_direction)
         self._types_l.append(int(type_colloid))
         self._props.append(prop)
-        self._types = np.array(self._types_l, dtype=np.int64)
         self.colloid_radius_register.update({type_colloid: {"radius": radius_simunits, "aspect_ratio": aspect_ratio}})
         self._state_version += 1
         return self.colloids[len(self._pos) - 1]
@@ -392,6 +400,38 @@ class SwarmEngine(Engine):
                 radius_colloid=radius_colloid, init_position=self.ureg.Quantity(start_pos, "sim_length"),
                 init_direction=init_direction, type_colloid=type_colloid, gamma_translation=gamma_translation,
                 gamma_rotation=gamma_rotation, aspect_ratio=aspect_ratio, mass=mass, rinertia=rinertia)
+
+    def add_colloids_at(self, positions, directions, radius_colloid=None, type_colloid: int = 0, gamma_translation=None,
+                        gamma_rotation=None, mass=None, rinertia=None):
+        """Bulk form of `add_colloid_on_point` (espresso.py:307-457) for large swarms -- not in the reference, whose
+        per-particle `system.part.add` is fine for its tens of colloids: `positions` is a pint quantity of shape
+        (n, 3), `directions` an (n, 3) array; every particle gets the same radius / type / friction, computed and
+        checked exactly as for a single particle (the first one goes through `add_colloid_on_point` itself)."""
+        positions_sim = np.array(positions.m_as("sim_length"), dtype=float).reshape(-1, 3)
+        directions = np.array(directions, dtype=float).reshape(-1, 3)
+        if len(positions_sim) != len(directions):
+            raise ValueError("positions and directions must have the same length")
+        if len(positions_sim) == 0:
+            return
+        self.add_colloid_on_point(radius_colloid=radius_colloid, init_position=self.ureg.Quantity(positions_sim[0], "sim_length"),
+                                  init_direction=directions[0], type_colloid=type_colloid, gamma_translation=gamma_translation,
+                                  gamma_rotation=gamma_rotation, mass=mass, rinertia=rinertia)
+        prop = self._props[-1]
+        rest_p, rest_d = positions_sim[1:].copy(), directions[1:].copy()
+        rest_d /= np.linalg.norm(rest_d, axis=1, keepdims=True)
+        if self.n_dims == 2:
+            if np.any(np.abs(np.arccos(np.clip(rest_d[:, 2], -1, 1)) - np.pi / 2) > 10e-6):
+                raise ValueError(
+                    "It seems like you want to have a 2D simulation with colloids that point some amount in"
+                    " Z-direction. Change something in your colloid setup.")
+            rest_p[:, 2] = 0.0
+            rest_d[:, 2] = 0.0
+            rest_d /= np.linalg.norm(rest_d, axis=1, keepdims=True)
+        self._pos.extend(rest_p)
+        self._dir.extend(rest_d)
+        self._types_l.extend([int(type_colloid)] * len(rest_p))
+        self._props.extend([prop] * len(rest_p))
+        self._state_version += 1
 
     def add_confining_walls(self, wall_type: int):
         """WCA walls on the box faces (espresso.py:667-711)."""
@@ -626,7 +666,7 @@ class SwarmEngine(Engine):
             steps_to_next_slice = self.params.steps_per_slice * self.slice_idx - self.step_idx
             steps_to_next = min(steps_to_next_write, steps_to_next_slice)
 
-            self._run_chunk(steps_to_next)
+            self._run_chunk(steps_to_next, deferred_check=device_path)
             # the reference calls this unguarded (espresso.py:1307): force_model=None raises there too
             if device_path:
                 from .device_view import SwarmDeviceView
@@ -635,12 +675,39 @@ class SwarmEngine(Engine):
             else:
                 force_model.calc_reward(self.colloids)
             self.step_idx += steps_to_next
+        self._check_deferred_runs()
 
-    def _run_chunk(self, n_steps):
-        """system.integrator.run(n_steps) (espresso.py:1304-1306)."""
-        self._backend.run_checked(int(n_steps), int(self.step_idx))
+    def _run_chunk(self, n_steps, deferred_check=False):
+        """system.integrator.run(n_steps) (espresso.py:1304-1306).
+
+        On the device path (nothing of a slice visits the host) only the FIRST chunk of this engine is run with a
+        synchronising check -- it grows the Verlet capacity to twice what the swarm needs -- and the later chunks are
+        only enqueued; `integrate` reads the counters once, after its loop.  A list overflow in an unchecked chunk
+        halts the integrator on the device (later launches are no-ops) and is raised there as OverflowError."""
+        be = self._backend
+        if deferred_check and self._capacity_proven and hasattr(be, "run") and hasattr(be, "stats"):
+            be.run(int(n_steps), int(self.step_idx))
+            self._unchecked_steps += int(n_steps)
+        else:
+            st = be.run_checked(int(n_steps), int(self.step_idx))
+            if deferred_check and hasattr(be, "set_max_neighbors") and st is not None:
+                if 2 * int(st.max_neighbors_seen) > int(st.capacity):
+                    be.set_max_neighbors(min(128, max(2 * int(st.max_neighbors_seen), int(st.capacity))))
+                self._capacity_proven = True
         self._time += n_steps * self._time_step
         self._state_version += 1
+
+    def _check_deferred_runs(self):
+        if not self._unchecked_steps:
+            return
+        self._unchecked_steps = 0
+        st = self._backend.stats()
+        if st.overflow:
+            self._capacity_proven = False
+            raise OverflowError(
+                f"a Verlet list overflowed in a chunk that was enqueued without a check (capacity {st.capacity}, "
+                f"needed >= {st.max_neighbors_seen}); the integrator halted on the device. Re-create the engine with a "
+                "larger max_neighbors, or drive it through the object path, which grows the lists chunk by chunk")
 
     def finalize(self):
         """espresso.py:1310-1318: flush, no snapshot."""

@@ -223,11 +223,15 @@ class SubdividedVisionCones(Observable):
         if self.detected_types is None:
             self._detect_all_things_to_see(swarm.ptype_host)
         det = [int(t) for t in self.detected_types]
-        tmax = max([int(swarm.ptype_host.max(initial=0))] + det) + 1
-        type_col = -np.ones(tmax, dtype=np.int32)
-        for c, t in enumerate(det):
-            type_col[t] = c
-        type_col_d = torch.from_numpy(type_col).to(swarm.dev)
+        ckey = (id(swarm), swarm.n, tuple(det))
+        if getattr(self, "_type_col_key", None) != ckey:
+            tmax = max([int(swarm.ptype_host.max(initial=0))] + det) + 1
+            type_col = -np.ones(tmax, dtype=np.int32)
+            for c, t in enumerate(det):
+                type_col[t] = c
+            self._type_col_d = torch.from_numpy(type_col).to(swarm.dev)
+            self._type_col_key = ckey
+        type_col_d = self._type_col_d
         if self._radii_dev is None or self._radii_dev.numel() != max(swarm.n, 1) or self._radii_dev.device != swarm.dev:
             r = np.zeros(max(swarm.n, 1))
             r[: swarm.n] = np.asarray(self.radii, dtype=float)[: swarm.n]

@@ -114,7 +114,7 @@ def test_tiled_positions_edited_between_launches_and_overflow_growth():
     capacity that is too small halts the launch and run_checked grows it, as on the other kernels."""
     res = []
     for mode in (0, 2):
-        _, d = _pair(20000, 800.0, KT_300, skin=2.0, max_neighbors=4)
+        _, d = _pair(20000, 450.0, KT_300, skin=2.0, max_neighbors=4)
         d.set_tiling(mode)
         st = d.run_checked(50, 0)
         assert st.capacity > 4

@@ -9,6 +9,7 @@ keys = ['gpu__time_duration.sum', 'launch__grid_size', 'launch__block_size', 'la
         'sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active', 'sm__inst_executed_pipe_fmaheavy.avg.pct_of_peak_sustained_active',
         'dram__bytes_read.sum', 'dram__bytes_write.sum', 'lts__t_bytes.sum', 'l1tex__t_sector_hit_rate.pct', 'sm__cycles_elapsed.max',
         'smsp__inst_executed_op_local_ld.sum', 'smsp__inst_executed_op_local_st.sum', 'sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active']
+print(f"{'profiled_launch_steps':70s} {steps:g} step")   # integrator steps of the profiled launch (bench.py scales per-launch figures by it)
 for h, u, v in zip(hdr, units, vals):
     if h in keys: print(f"{h:70s} {v} {u}")
 src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "sass"], capture_output=True, text=True).stdout

@@ -24,8 +24,12 @@ for kT in (0.0, bench.KT):
     d = DeviceSwarm(2, (200.0,) * 3, True, 1e-3, kT, 1, bench.species_table(), bench.wca_table(), skin=5.0)
     d.set_state(pos, np.zeros(1000, dtype=np.int32), theta=th)
     prof(d, 2000, f"n=1000 kT={kT:.2f}")
-for kT in (0.0, bench.KT):
-    pos, th = bench.initial_state(bench.N_AGENTS, bench.BOX, 42)
-    d = DeviceSwarm(2, (bench.BOX,) * 3, True, 1e-3, kT, 42, bench.species_table(), bench.wca_table(), skin=2.0)
-    d.set_state(pos, np.zeros(bench.N_AGENTS, dtype=np.int32), theta=th)
-    prof(d, 500, f"n=100k kT={kT:.2f}")
+for mode in (0, 1):
+    for kT in (0.0, bench.KT):
+        pos, th = bench.initial_state(bench.N_AGENTS, bench.BOX, 42)
+        d = DeviceSwarm(2, (bench.BOX,) * 3, True, 1e-3, kT, 42, bench.species_table(), bench.wca_table(), skin=2.0)
+        d.set_state(pos, np.zeros(bench.N_AGENTS, dtype=np.int32), theta=th)
+        d.set_tiling(mode)
+        prof(d, 500, f"n=100k kT={kT:.2f} {'tiled' if mode else 'resident'}")
+        if mode:
+            print(json.dumps(d.tiling_stats()))
