@@ -165,7 +165,7 @@ int swarm_debug_timing(swarm_t *s, int64_t out8[8]);
 int swarm_set_tiling(swarm_t *s, int32_t mode, int32_t resort_interval);
 /* out8: [0] 1 if the Verlet list currently lives in the tiled kernel's slot space (the last Brownian run was tiled),
  * [1] rebuild cadence K, [2] steps integrated on the current list, [3] periods rolled back so far, [4] sum of
- * partner CTAs over all rebuilds, [5] spatial sorts so far, [6] CTAs, [7] slots per CTA.  Synchronises the device. */
+ * rim particles (particles whose list points into another CTA's tile) over all rebuilds, [5] spatial sorts so far, [6] CTAs, [7] slots per CTA.  Synchronises the device. */
 int swarm_tiling_stats(swarm_t *s, int64_t out8[8]);
 /* The tiled kernel's OWN Verlet list as it stands (built at the last in-kernel rebuild, slots mapped back to particle
  * ids), every ordered pair sorted by (i,j) -- for the bit-exact list check of that path.  SWARM_ERR_STATE unless the
@@ -320,6 +320,10 @@ int swarm_policy_forward(swarm_t *s, const swarm_policy_t *net, const double *ob
 /* ---- host-buffer entry points (what a cgo/ctypes binding of the reference would call) --- */
 /* manage_forces: write f_swim and ext torque of every particle (espresso.py:1227-1235) */
 int swarm_set_actions_host(swarm_t *s, const double *f_swim_host, const double *torque3n_host, void *stream);
+/* One trajectory frame (espresso.py:1110-1130: Unwrapped_Positions, Velocities, Directors) into three [n][3]
+ * row-major DEVICE buffers, one kernel on `stream`, no host synchronisation: the snapshot ring of the asynchronous
+ * trajectory writer (espresso.py:1278-1285 takes the snapshot before the chunk is integrated). */
+int swarm_snapshot_dev(swarm_t *s, double *pos_n3_dev, double *vel_n3_dev, double *dir_n3_dev, void *stream);
 /* get_particle_data (espresso.py:1320-1336): [n][3] row-major outputs; synchronises */
 int swarm_get_particle_data_host(swarm_t *s, double *pos_n3, double *vel_n3, double *dir_n3, void *stream);
 

@@ -341,6 +341,83 @@ def pair_field(pos, ptype, particle_type, sensing_type, box_length, kind, c0, c1
     return np.array(out)
 
 
+# ------------------------------------------------------------------------------------------------
+# float32 evaluation mode: the reference evaluates its observables and tasks with
+# JAX in its default float32 -- positions are normalised / packed in float64 numpy and rounded to float32 where they
+# enter a jnp call.  The kernels (and the restatements above) compute in fp64; these functions repeat the reference's
+# arithmetic with the reference's rounding points, so that tests can STATE how far an fp64 result may lie from what
+# real JAX would return (tests/test_oracle_fp32.py on the CPU, tests/test_gpu_obs.py against the kernels).
+# ------------------------------------------------------------------------------------------------
+_F = np.float32
+
+
+def decay_eval_f32(kind, c0, c1, d):
+    d = np.asarray(d, dtype=_F)
+    c0, c1 = _F(c0), _F(c1)
+    return {1: lambda: c0 + c1 * d, 2: lambda: c0 * np.exp(-c1 * d), 3: lambda: c0 / (d + c1)}[int(kind)]().astype(_F)
+
+
+def field_delta_f32(p_now, p_prev, src, kind, c0, c1, scale, clip):
+    """ConcentrationField.compute_single_observable / GradientSensing.compute_colloid_reward
+    (concentration_field.py:84-110, gradient_sensing.py:92-126) with JAX's float32: `source - position` is float64
+    numpy, jnp.linalg.norm rounds it to float32 and everything after that is float32.
+    p_now, p_prev: (n, 3) NORMALISED positions (fp64); src: normalised source.  Returns float32 (n,)."""
+    dn = np.sqrt(((np.asarray(src, dtype=np.float64) - np.asarray(p_now, dtype=np.float64)).astype(_F) ** 2).sum(axis=1, dtype=_F))
+    dp = np.sqrt(((np.asarray(src, dtype=np.float64) - np.asarray(p_prev, dtype=np.float64)).astype(_F) ** 2).sum(axis=1, dtype=_F))
+    v = _F(scale) * (decay_eval_f32(kind, c0, c1, dn) - decay_eval_f32(kind, c0, c1, dp))
+    return np.clip(v, _F(0), None) if clip else v
+
+
+def vision_cones_f32(pos, dirs, ptype, want_type, vision_range, half_angle, n_cones, radii, detected_types):
+    """SubdividedVisionCones (subdivided_vision_cones.py:83-258, utils.py:297-332) in float32: positions, directors and
+    radii are rounded to float32 when they enter the jitted function; every later operation is float32.  The observer
+    itself is visited (distance 0: 0/0 = NaN angle, no cone), as in the reference.  O(observers x particles) numpy."""
+    pos = np.asarray(pos, dtype=np.float64).astype(_F)
+    dirs = np.asarray(dirs, dtype=np.float64).astype(_F)
+    rad = np.asarray(radii, dtype=np.float64).astype(_F)
+    ptype = np.asarray(ptype)
+    det = [int(t) for t in detected_types]
+    rims = (_F(-half_angle) + np.arange(n_cones + 1, dtype=_F) * _F(half_angle) * _F(2) / _F(n_cones)).astype(_F)
+    obs = np.nonzero(ptype == int(want_type))[0]
+    out = np.zeros((len(obs), n_cones, len(det)), dtype=_F)
+    with np.errstate(invalid="ignore", divide="ignore"):
+        for r, i in enumerate(obs):
+            dist = pos - pos[i]
+            dn = np.sqrt((dist * dist).sum(axis=1, dtype=_F))
+            w = np.minimum(_F(1), _F(2) * rad / dn).astype(_F) * (dn < _F(vision_range))
+            e = dirs[i] / np.sqrt((dirs[i] * dirs[i]).sum(dtype=_F))
+            o = dist / dn[:, None]
+            o = o / np.sqrt((o * o).sum(axis=1, dtype=_F))[:, None]
+            ang = np.arccos(np.clip((o * e).sum(axis=1, dtype=_F), _F(-1), _F(1))).astype(_F)
+            orth = (o * np.array([-e[1], e[0], e[2]], dtype=_F)).sum(axis=1, dtype=_F)
+            ang = ang * np.where(orth >= 0, _F(1), _F(-1))
+            for k in range(n_cones):
+                inc = (rims[k] < ang) & (rims[k + 1] > ang)       # NaN (the observer itself) is in no cone
+                for c, t in enumerate(det):
+                    sel = inc & (ptype == t)
+                    out[r, k, c] = w[sel].sum(dtype=_F)
+    return out
+
+
+def pair_field_f32(pos, ptype, particle_type, sensing_type, box_length, kind, c0, c1):
+    """pair_field() with the reference's float32 rounding points (particle_sensing.py:95-131): positions enter the
+    jitted function as float32; division by the box, norm, decay and the sum are float32."""
+    pos = np.asarray(pos, dtype=np.float64).reshape(-1, 3).astype(_F)
+    box = np.asarray(box_length, dtype=np.float64).astype(_F)
+    ptype = np.asarray(ptype)
+    sensed = pos[ptype == sensing_type]
+    M = len(sensed)
+    out = []
+    for i in np.nonzero(ptype == particle_type)[0]:
+        dd = (sensed - pos[i]) / box
+        d = np.sqrt((dd * dd).sum(axis=1, dtype=_F))
+        nz = np.nonzero(d)[0][: max(M - 1, 0)]
+        idx = np.zeros(max(M - 1, 0), dtype=np.int64)
+        idx[: len(nz)] = nz
+        out.append(decay_eval_f32(kind, c0, c1, d[idx]).sum(dtype=_F) if M > 1 else _F(0))
+    return np.array(out, dtype=_F)
+
+
 PHILOX_DOMAIN_POLICY = 0x706F6C696379  # counter word c2 of the policy's Gumbel noise (swarm_common.cuh)
 
 

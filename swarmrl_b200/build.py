@@ -16,7 +16,7 @@ PKG = pathlib.Path(__file__).resolve().parent
 CSRC = PKG / "csrc"
 LIB = PKG / "libswarm_b200.so"
 SOURCES = ["swarm_engine.cu", "swarm_obs.cu", "swarm_dd.cu", "swarm_policy.cu"]
-HEADERS = [CSRC / "swarm_common.cuh", CSRC / "swarm_math.cuh", CSRC / "swarm_bd2d.cuh", PKG.parent / "include" / "swarm_b200.h"]
+HEADERS = sorted(CSRC.glob("*.cuh")) + [PKG.parent / "include" / "swarm_b200.h"]   # every header: a stale library is worse than a slow build
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

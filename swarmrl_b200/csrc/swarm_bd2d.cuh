@@ -158,7 +158,7 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_resident(const __grid_c
   if (act) {
     swm_sincos(th, ey, ex);
     sf = bd2d_self_forces(P, ti, xi, yi, ex, ey, fsw);
-    if (NOISE) swm_gaussians_xyt(P.seed, pid, R.step0, g0, g1, g3);
+    if (NOISE) swm_gaussians_xyt(P.rk, pid, R.step0, g0, g1, g3);
   }
   u64 rw[4] = {0, 0, 0, 0};   // PIPE: Philox words of the next step, carried from the load shadow to the barrier shadow
   int cnt = 0, nb[SW_RES_NBR];
@@ -209,7 +209,7 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_resident(const __grid_c
         xj[k] = ldcg(&A.x[cur][j]); yj[k] = ldcg(&A.y[cur][j]);
       }
       // ---- shadow of those loads: the next step's Philox block (integer pipe, depends on (seed, id, step) only) ----
-      if (NOISE && PIPE && !last) swm_philox_xyt(P.seed, pid, R.step0 + (u64)(s + 1), rw);
+      if (NOISE && PIPE && !last) swm_philox_xyt(P.rk, pid, R.step0 + (u64)(s + 1), rw);
       double Fx = 0.0, Fy = 0.0;
 #pragma unroll
       for (int k = 0; k < SW_RES_NBR; ++k)
@@ -270,7 +270,7 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_resident(const __grid_c
         sf = bd2d_self_forces(P, ti, xi, yi, ex, ey, fsw);
         if (NOISE) {
           if (PIPE) swm_boxmuller_xyt(rw, g0, g1, g3);
-          else swm_gaussians_xyt(P.seed, pid, R.step0 + (u64)(s + 1), g0, g1, g3);
+          else swm_gaussians_xyt(P.rk, pid, R.step0 + (u64)(s + 1), g0, g1, g3);
         }
       }
     }
@@ -369,7 +369,7 @@ __device__ __forceinline__ bool bd2d_step_stream(const DevParams &P, const DevAr
   Fx += sf.sx; Fy += sf.sy;
   if (A.fex) { Fx += fxe; Fy += fye; }
   double g0 = pg0, g1 = pg1, g3 = pg3;  // drawn behind the previous step's barrier for the thread's first particle
-  if (NOISE && !have_g) swm_gaussians_xyt(P.seed, pid, step, g0, g1, g3);
+  if (NOISE && !have_g) swm_gaussians_xyt(P.rk, pid, step, g0, g1, g3);
   const double dt = P.dt;
   double xn = xi, yn = yi, thn = th, vx, vy;
   const double w = swm_div_r(tqz, c.gr0, c.r_gr0);
@@ -442,7 +442,7 @@ __global__ void __launch_bounds__(SW_STREAM_THREADS, SW_STREAM_MINB) k_bd2d_stre
         const long long i = i0 + k * gstride;
         if (i >= hi) break;
         double a, b, c;
-        swm_gaussians_xyt(P.seed, sw_pid(A, i), next_step, a, b, c);
+        swm_gaussians_xyt(P.rk, sw_pid(A, i), next_step, a, b, c);
         s_g[k][0][threadIdx.x] = a; s_g[k][1][threadIdx.x] = b; s_g[k][2][threadIdx.x] = c;
       }
       have_g = true;
@@ -546,7 +546,7 @@ __global__ void __launch_bounds__(SW_ENV_THREADS) k_bd2d_env(const __grid_consta
     double ex, ey, g0 = 0.0, g1 = 0.0, g3 = 0.0;
     swm_sincos(th, ey, ex);
     const Bd2dSelf sf = bd2d_self_forces(P, ti, xi, yi, ex, ey, fsw);
-    if (NOISE) swm_gaussians_xyt(P.seed, pid, R.step0 + (u64)s, g0, g1, g3);
+    if (NOISE) swm_gaussians_xyt(P.rk, pid, R.step0 + (u64)s, g0, g1, g3);
     double Fx = 0.0, Fy = 0.0;
     if (prefilter) {
       // A Verlet list in one register: bit j of `mask` = agent j was within cut-off + skin of this agent when the

@@ -4,6 +4,7 @@
 #include <stdint.h>
 
 #include <string>
+#include <type_traits>
 #include <vector>
 
 #include "../../include/swarm_b200.h"
@@ -22,6 +23,7 @@ struct DevParams {
   double box[3], inv_box[3];
   double dt, kT;
   u64 seed;
+  unsigned int rk[20];  // Philox4x32-10 round keys of the seed (sw_key_schedule): the kernels read them as constant-bank operands
   int n_species, n_types;
   int sp_type[SW_S];
   double sp_gt[SW_S][3], sp_gr[SW_S][3], sp_mass[SW_S], sp_rin[SW_S][3];
@@ -56,7 +58,7 @@ struct Ctl {
   int tile_K;                    // steps between Verlet rebuilds chosen by the last launch (0: not chosen yet)
   int tile_since;                // steps integrated on the current list
   long long tile_rollbacks;      // periods replayed because a particle left skin/2 before the scheduled rebuild
-  long long tile_partners;       // sum over CTAs of neighbour-flag partners at the last rebuild
+  long long tile_partners;       // sum over rebuilds of the number of rim particles (lists pointing into another CTA's tile)
 };
 
 struct DevArrays {
@@ -99,7 +101,11 @@ struct TileHost {
   int *perm = nullptr, *key = nullptr, *hist = nullptr, *start = nullptr, *cursor = nullptr, *species_s = nullptr;
   long long *gid_s = nullptr;
   double *xs[2] = {nullptr, nullptr}, *ys[2] = {nullptr, nullptr};
-  unsigned int *flags = nullptr, *pbits = nullptr;
+  void *crec = nullptr;                    // CellRec[n_pad]: the rebuild's per-particle search records
+  unsigned long long *head64 = nullptr;   // tagged cell heads of the tiled rebuild
+  long long head64_cells = 0;
+  unsigned long long tag_next = 1;         // first unused rebuild tag
+  void *rim[2] = {nullptr, nullptr};   // RimRec[n_pad] per epoch parity (swarm_tiled.cuh)
   int nbins_alloc = 0;
   int mode = 1;                // swarm_set_tiling: 0 off, 1 automatic
   int resort_interval = 16;    // launches between two spatial sorts
@@ -196,6 +202,36 @@ __host__ __device__ __forceinline__ void sw_philox4x32_10(unsigned int c0, unsig
     k0 += W0; k1 += W1;
   }
   out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+
+// Round keys of Philox4x32-10 for key = (seed lo, seed hi): rk[2r], rk[2r+1] = the key of round r.
+__host__ __device__ __forceinline__ void sw_key_schedule(u64 seed, unsigned int rk[20]) {
+  unsigned int k0 = (unsigned int)seed, k1 = (unsigned int)(seed >> 32);
+  for (int r = 0; r < 10; ++r) { rk[2 * r] = k0; rk[2 * r + 1] = k1; k0 += 0x9E3779B9u; k1 += 0xBB67AE85u; }
+}
+
+// sw_philox4x32_10 with the key schedule precomputed (DevParams.rk): a round is two IMAD.WIDE and two LOP3 with a
+// constant-bank operand -- 81 instructions for the two blocks of a draw; the in-line key bumps, done by the uniform
+// datapath, and the register moves around them cost another 60 (cuobjdump, sm_100a).
+__device__ __forceinline__ void sw_philox4x32_10_rk(unsigned int c0, unsigned int c1, unsigned int c2, unsigned int c3,
+                                                    const unsigned int *rk, unsigned int out[4]) {
+  const unsigned int M0 = 0xD2511F53u, M1 = 0xCD9E8D57u;
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const unsigned int h0 = __umulhi(M0, c0), l0 = M0 * c0, h1 = __umulhi(M1, c2), l1 = M1 * c2;
+    const unsigned int n0 = h1 ^ c1 ^ rk[2 * r], n2 = h0 ^ c3 ^ rk[2 * r + 1];
+    c0 = n0; c1 = l1; c2 = n2; c3 = l0;
+  }
+  out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+__device__ __forceinline__ void sw_noise_words_rk(const unsigned int *rk, u64 id, u64 step, u64 stream, u64 r[4]) {
+  const unsigned int c0 = (unsigned int)step, c1 = (unsigned int)(step >> 32), c2 = (unsigned int)id;
+  const unsigned int c3 = ((unsigned int)((id >> 32) & 0xFFFFFFULL) << 8) | ((unsigned int)(stream & 0x7FULL) << 1);
+  unsigned int a[4], b[4];
+  sw_philox4x32_10_rk(c0, c1, c2, c3, rk, a);
+  sw_philox4x32_10_rk(c0, c1, c2, c3 | 1u, rk, b);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) r[k] = ((u64)a[k] << 32) | (u64)b[k];
 }
 
 // The thermostat's four 64-bit noise words of (seed, particle id, step, stream) -- oracle: orc_noise_words.  Two

@@ -45,6 +45,7 @@ struct RunArgs {
   // MODE_LV (velocity Verlet): iteration 0 of the launch is the force recalculation at the start of a chunk
   // (no closing half kick); the last iteration only closes the final step (no drift)
   int lv_first, lv_close;
+  int prof_cta, prof_warp;   // SW_TIMING builds: whose clock64 sums go to Ctl.tprof (SWARM_B200_PROF_CTA / _WARP)
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -826,6 +827,7 @@ extern "C" int swarm_create(const swarm_config_t *cfg, swarm_t **out) {
     P.inv_box[a] = 1.0 / cfg->box[a];
   }
   P.dt = cfg->dt; P.kT = cfg->kT; P.seed = cfg->seed; P.skin = cfg->skin;
+  sw_key_schedule(P.seed, P.rk);
   P.n_envs = cfg->n_envs;
   s->A.cap = cfg->max_neighbors > 0 ? cfg->max_neighbors : (cfg->n_dims == 2 ? 16 : 64);
   if (s->A.cap > SW_MAXCAP) s->A.cap = SW_MAXCAP;
@@ -913,6 +915,7 @@ extern "C" int swarm_set_walls(swarm_t *s, int32_t enabled, const double *sigma,
 extern "C" int swarm_set_thermostat(swarm_t *s, double kT, uint64_t seed) {
   if (!s || kT < 0.0) { sw_set_error("kT must be >= 0"); return SWARM_ERR_INVALID; }
   s->P.kT = kT; s->P.seed = seed;
+  sw_key_schedule(seed, s->P.rk);
   return SWARM_OK;
 }
 
@@ -1147,14 +1150,14 @@ static bool sw_wca_symmetric(const swarm *s) {
   return true;
 }
 
-// CTAs and slots per CTA of the tiled (and resident) layout
+// CTAs and slots per CTA of the tiled layout: one particle per thread, the particles spread evenly over the SMs
 static void sw_tile_shape(const swarm *s, long long *ctas_out, int *ppc_out, int *threads_out) {
   long long ctas = s->num_sms;
-  if (s->A.n < ctas * 128) ctas = (s->A.n + 127) / 128;   // small swarms: at least 4 particle warps per CTA
+  if (s->A.n < ctas * 128) ctas = (s->A.n + 127) / 128;   // small swarms: at least 4 warps per CTA
   if (ctas < 1) ctas = 1;
   const int ppc = (int)((s->A.n + ctas - 1) / ctas);
   *ppc_out = ppc;
-  *threads_out = 32 + ((ppc + 31) / 32) * 32;
+  *threads_out = ((ppc + 31) / 32) * 32 + 32;   // + the halo warp
   *ctas_out = (s->A.n + ppc - 1) / ppc;
 }
 
@@ -1188,8 +1191,9 @@ static int sw_tile_prepare(swarm *s, cudaStream_t st, bool *resorted) {
       if ((rc = sw_alloc(s, (void **)&t.xs[b], sizeof(double) * np))) return rc;
       if ((rc = sw_alloc(s, (void **)&t.ys[b], sizeof(double) * np))) return rc;
     }
-    if ((rc = sw_alloc(s, (void **)&t.flags, sizeof(unsigned int) * 32 * SW_TILE_MAXCTA))) return rc;
-    if ((rc = sw_alloc(s, (void **)&t.pbits, sizeof(unsigned int) * (SW_TILE_MAXCTA / 32) * SW_TILE_MAXCTA))) return rc;
+    if ((rc = sw_alloc(s, &t.rim[0], sizeof(RimRec) * 2 * np))) return rc;
+    if ((rc = sw_alloc(s, &t.crec, sizeof(CellRec) * np))) return rc;
+    t.rim[1] = (RimRec *)t.rim[0] + np;
     t.n = A.n_pad;
     t.sorted = false;
     t.nbins_alloc = 0;
@@ -1229,6 +1233,12 @@ static int sw_tile_prepare(swarm *s, cudaStream_t st, bool *resorted) {
   k_sort_scan<<<1, 1024, 0, st>>>(nbins, t.hist, t.start, t.cursor);
   k_sort_place<<<B, 256, 0, st>>>(n, t.key, t.cursor, t.perm);
   k_sort_fix<<<sw_blocks(nbins, 128), 128, 0, st>>>(nbins, t.start, t.perm);
+  if (!getenv("SWARM_B200_TILE_NO_RIMFIRST")) {
+    const double rc = s->P.max_cut + s->P.skin;
+    const int rows_margin = (int)ceil(rc * G.inv_h) + 1;
+    k_sort_rimfirst<<<(unsigned)ctas, 1024, 0, st>>>(s->P, G, n, ppc, rc, rows_margin, A.x[0], t.key, t.perm);
+    s->launches += 1;
+  }
   k_sort_gather<<<B, 256, 0, st>>>(n, t.perm, A.species, A.gid, t.species_s, t.gid_s);
   s->launches += 5;
   SW_CUDA(cudaGetLastError());
@@ -1245,7 +1255,7 @@ static int sw_launch_tiled(swarm *s, const RunArgs &R, cudaStream_t st, bool *fi
   long long ctas; int ppc, threads;
   sw_tile_shape(s, &ctas, &ppc, &threads);
   int bpsm = 0;
-  const size_t dsm = sizeof(double) * SW_TILE_COLS * SW_TILE_MAXP;
+  const size_t dsm = sizeof(double) * SW_TILE_DSM_DOUBLES;
   SW_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dsm));
   SW_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bpsm, kern, threads, dsm));
   *fits = bpsm >= 1 && ctas <= (long long)s->num_sms * bpsm;
@@ -1256,11 +1266,8 @@ static int sw_launch_tiled(swarm *s, const RunArgs &R, cudaStream_t st, bool *fi
   TileHost &t = s->tile;
   RunArgs Rr = R;
   Rr.particles_per_cta = ppc;
-  if (resorted) {
-    // new slot order (or other particles): restart the flag epochs, so no CTA index carries a stale flag
-    SW_CUDA(cudaMemsetAsync(t.flags, 0, sizeof(unsigned int) * 32 * SW_TILE_MAXCTA, st));
-    t.launches_total = 0;
-  }
+  Rr.prof_cta = getenv("SWARM_B200_PROF_CTA") ? atoi(getenv("SWARM_B200_PROF_CTA")) : 0;
+  Rr.prof_warp = getenv("SWARM_B200_PROF_WARP") ? atoi(getenv("SWARM_B200_PROF_WARP")) : 0;
   if (resorted || s->list_space != 1) Rr.force_rebuild = 1;   // the list in A.nbr is in another index space
   s->list_space = 1;
   s->coop_blocks_per_sm = bpsm;
@@ -1272,9 +1279,20 @@ static int sw_launch_tiled(swarm *s, const RunArgs &R, cudaStream_t st, bool *fi
   T.species = t.species_s;
   T.gid = t.gid_s;
   T.okey = t.gid_s;
+  const long long ncell = (long long)s->P.ncell_env;
+  if (ncell > t.head64_cells) {
+    int rc2;
+    if ((rc2 = sw_alloc(s, (void **)&t.head64, sizeof(unsigned long long) * (size_t)ncell))) return rc2;   // zero: tag 0 is never used
+    t.head64_cells = ncell;
+  }
   TileArgs G;
-  G.perm = t.perm; G.flags = t.flags; G.pbits = t.pbits; G.ppc = ppc; G.k_init = 8;
-  G.epoch0 = (unsigned int)((t.launches_total + 1) & 0xFFF) << 20;
+  G.head64 = t.head64;
+  G.crec = (CellRec *)t.crec;
+  G.tag0 = t.tag_next;
+  t.tag_next += 4ULL * (unsigned long long)R.n_steps + 16ULL;   // more than the rebuilds (and rolled-back ones) of this launch
+  G.perm = t.perm; G.rim = (RimRec *)t.rim[0]; G.rim_stride = s->A.n_pad; G.ppc = ppc; G.k_init = 8; G.k_cap = SW_TILE_KMAX;
+  if (const char *e = getenv("SWARM_B200_TILE_KCAP")) { const int k = atoi(e); if (k >= 1 && k <= SW_TILE_KMAX) G.k_cap = k; }
+  G.flag0 = (unsigned int)((t.launches_total + 1) << 15);
   if (const char *e = getenv("SWARM_B200_TILE_KINIT")) { const int k = atoi(e); if (k >= 1 && k <= SW_TILE_KMAX) G.k_init = k; }
   void *args[] = {(void *)&P, (void *)&A, (void *)&T, (void *)&G, (void *)&Rr};
   SW_CUDA(cudaLaunchCooperativeKernel((void *)kern, dim3((unsigned)ctas), dim3(threads), args, dsm, st));
@@ -1688,6 +1706,40 @@ extern "C" int swarm_set_actions_host(swarm_t *s, const double *f_swim_host, con
     s->launches += 1;
     SW_CUDA(cudaGetLastError());
   }
+  return SWARM_OK;
+}
+
+// One frame of the trajectory (espresso.py:1110-1130: Unwrapped_Positions, Velocities, Directors, each (N, 3)) written
+// into DEVICE memory by one kernel on the caller's stream: the snapshot ring of the asynchronous trajectory writer
+// (swarmrl_b200/trajectory.py) is filled without touching the host; the D2H copy runs on the writer's own stream.
+__global__ void k_snapshot(int n_dims, long long n, const double *x, const double *y, const double *z, const double *vx, const double *vy,
+                           const double *vz, const double *theta, const double *q0, const double *q1, const double *q2,
+                           const double *q3, double *pos, double *vel, double *dir) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  pos[3 * i] = x[i]; pos[3 * i + 1] = y[i]; pos[3 * i + 2] = z[i];
+  vel[3 * i] = vx[i]; vel[3 * i + 1] = vy[i]; vel[3 * i + 2] = vz[i];
+  double ex, ey, ez;
+  if (n_dims == 2) {
+    double s, c;
+    sincos(theta[i], &s, &c);
+    ex = c; ey = s; ez = 0.0;
+  } else {
+    const double a = q0[i], b = q1[i], c = q2[i], d = q3[i];
+    ex = 2 * (b * d + a * c); ey = 2 * (c * d - a * b); ez = a * a - b * b - c * c + d * d;
+  }
+  dir[3 * i] = ex; dir[3 * i + 1] = ey; dir[3 * i + 2] = ez;
+}
+
+extern "C" int swarm_snapshot_dev(swarm_t *s, double *pos_n3_dev, double *vel_n3_dev, double *dir_n3_dev, void *stream) {
+  if (!s || !s->state_bound || !pos_n3_dev || !vel_n3_dev || !dir_n3_dev) { sw_set_error("bad arguments"); return SWARM_ERR_INVALID; }
+  SW_CUDA(cudaSetDevice(s->cfg.device));
+  const DevArrays &A = s->A;
+  if (A.n == 0) return SWARM_OK;
+  k_snapshot<<<sw_blocks(A.n, 256), 256, 0, (cudaStream_t)stream>>>(s->P.n_dims, A.n, A.x[0], A.y[0], A.z[0], A.vx, A.vy, A.vz, A.theta,
+                                                                    A.q0, A.q1, A.q2, A.q3, pos_n3_dev, vel_n3_dev, dir_n3_dev);
+  s->launches += 1;
+  SW_CUDA(cudaGetLastError());
   return SWARM_OK;
 }
 

@@ -176,6 +176,113 @@ __device__ __forceinline__ void swm_uniforms(u64 seed, u64 id, u64 step, u64 str
   for (int k = 0; k < 4; ++k) u[k] = swm_u01(r[k]) - 0.5;
 }
 
+// the same draws with the key schedule of the seed precomputed (DevParams.rk, a constant-bank operand): the hot kernels
+__device__ __forceinline__ void swm_philox_xyt(const unsigned int *rk, u64 id, u64 step, u64 r[4]) {
+  sw_noise_words_rk(rk, id, step, 0ULL, r);
+}
+__device__ __forceinline__ void swm_gaussians_xyt(const unsigned int *rk, u64 id, u64 step, double &g0, double &g1, double &g3) {
+  u64 r[4];
+  sw_noise_words_rk(rk, id, step, 0ULL, r);
+  swm_boxmuller_xyt(r, g0, g1, g3);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Everything a 2-D Brownian step needs that depends on the particle alone, in ONE pass: the three normals of
+// (key schedule, id, step) and the director (sin, cos)(theta).  Same operations, value by value, as
+// swm_gaussians_xyt + swm_sincos (every product / fma is explicit, so the bits are the same) -- but the two logarithms
+// and the three sine / cosine polynomials are evaluated side by side: a coefficient is fetched from the constant bank
+// once for all chains instead of once per chain (70 constant loads per warp-step in the separate version, ncu
+// profiles/r02_ncu_k_bd2d_tiled_flag_version_summary.txt: LDC + LDCU), and the independent chains interleave.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void swm_quadrant(unsigned q, double ps, double pc, double &sn, double &cs) {
+  const bool swap = q & 1u;
+  double s0 = swap ? pc : ps, c0 = swap ? ps : pc;
+  if ((q + 1u) & 2u) c0 = -c0;
+  if (q & 2u) s0 = -s0;
+  sn = s0; cs = c0;
+}
+
+__device__ __forceinline__ void swm_step_inputs(const unsigned int *rk, u64 id, u64 step, double th, double &g0, double &g1,
+                                                double &g3, double &sn, double &cs) {
+  u64 r[4];
+  sw_noise_words_rk(rk, id, step, 0ULL, r);
+  // ---- arguments of the three (sin, cos) pairs: t in [-1/8, 1/8] turns, quadrant q --------------------------------
+  double t[3];
+  unsigned q[3];
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const u64 k = r[2 * i + 1] >> 12;
+    q[i] = (unsigned)((k + (1ULL << 49)) >> 50);
+    t[i] = fma((double)q[i], -0.25, swm_u01(r[2 * i + 1]));
+  }
+  const bool big = !(fabs(th) < 1073741824.0);   // beyond 2^30 rad the library routine takes over (swm_sincos)
+  {
+    const double c_hi = 0.15915494309189535, c_lo = -9.839338337591243e-18;
+    const double turns = th * c_hi;
+    const double rem = fma(th, c_hi, -turns) + th * c_lo;
+    const double bigc = 6755399441055744.0;
+    const double qs = fma(4.0, turns, bigc);
+    const double qd = qs - bigc;
+    q[2] = (unsigned)__double2loint(qs);
+    t[2] = big ? 0.0 : fma(qd, -0.25, turns) + rem;
+  }
+  // ---- polynomials, coefficient by coefficient ---------------------------------------------------------------------
+  double z[3], ps[3], pc[3];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) { z[i] = t[i] * t[i]; ps[i] = SWM_SIN[8]; pc[i] = SWM_COS[9]; }
+#pragma unroll
+  for (int k = 7; k >= 0; --k) {
+    const double c = SWM_SIN[k];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) ps[i] = fma(ps[i], z[i], c);
+  }
+#pragma unroll
+  for (int i = 0; i < 3; ++i) ps[i] *= t[i];
+#pragma unroll
+  for (int k = 8; k >= 0; --k) {
+    const double c = SWM_COS[k];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) pc[i] = fma(pc[i], z[i], c);
+  }
+  // ---- the two logarithms (swm_log01), side by side ----------------------------------------------------------------
+  double lg[2];
+  {
+    double s2[2], zz[2], p[2], ed[2];
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      const double u = swm_u01(r[2 * i]);
+      int hi = __double2hiint(u), lo = __double2loint(u);
+      int e = (hi >> 20) - 1023;
+      hi = (hi & 0x000FFFFF) | 0x3FF00000;
+      if (hi >= 0x3FF6A09F) { hi -= 0x00100000; e += 1; }
+      const double f = __hiloint2double(hi, lo) - 1.0;
+      s2[i] = swm_div(f, 2.0 + f);
+      zz[i] = s2[i] * s2[i];
+      p[i] = SWM_LOG[10];
+      ed[i] = (double)e;
+    }
+#pragma unroll
+    for (int k = 9; k >= 0; --k) {
+      const double c = SWM_LOG[k];
+#pragma unroll
+      for (int i = 0; i < 2; ++i) p[i] = fma(p[i], zz[i], c);
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      const double rr = fma(s2[i] * zz[i], p[i], ed[i] * SWM_K[2]);
+      lg[i] = fma(ed[i], SWM_K[1], fma(2.0, s2[i], rr));
+    }
+  }
+  const double m0 = swm_sqrt(-2.0 * lg[0]), m1 = swm_sqrt(-2.0 * lg[1]);
+  double s0, c0, s1, c1;
+  swm_quadrant(q[0], ps[0], pc[0], s0, c0);
+  swm_quadrant(q[1], ps[1], pc[1], s1, c1);
+  g0 = m0 * c0; g1 = m0 * s0; g3 = m1 * s1;
+  (void)c1;
+  if (big) sincos(th, &sn, &cs);
+  else swm_quadrant(q[2], ps[2], pc[2], sn, cs);
+}
+
 // all four normals with the fast kernels (parity hook / 3-D)
 __device__ __forceinline__ void swm_gaussians(u64 seed, u64 id, u64 step, u64 stream, double g[4]) {
   u64 r[4];

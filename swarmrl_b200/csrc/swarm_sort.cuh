@@ -106,6 +106,57 @@ __global__ void k_sort_fix(int nbins, const int *start, int *perm) {
   }
 }
 
+// K4b: within every tile (the `ppc` consecutive slots of one CTA) the particles that can have a neighbour in another tile
+// come FIRST: those within `rc` = cut-off + skin of a strip edge, and those in the first / last rows of the tile.  The
+// rim of a tile then occupies its first few warps and the remaining warps never execute (or wait for) a remote read.
+// Stable partition, one CTA per tile.
+__global__ void __launch_bounds__(1024) k_sort_rimfirst(const __grid_constant__ DevParams P, SortGeom G, long long n, int ppc, double rc,
+                                                        int rows_margin, const double *x, const int *key, int *perm) {
+  __shared__ int s_id[1024];
+  __shared__ int wsum[32];
+  __shared__ int s_total;
+  const long long base = (long long)blockIdx.x * ppc;
+  const int cnt = (int)((n - base < ppc) ? (n - base) : ppc);
+  const int t = threadIdx.x;
+  int id = -1, flag = 0;
+  if (t < cnt) {
+    id = perm[base + t];
+    const int kf = key[perm[base]], kl = key[perm[base + cnt - 1]], k = key[id];
+    double ux = x[id] * P.inv_box[0];
+    ux -= floor(ux);
+    if (!P.periodic[0]) ux = fmin(fmax(x[id] * P.inv_box[0], 0.0), 1.0);
+    const double xs = ux * P.box[0] * G.inv_w;          // in strip widths
+    const double fr = xs - floor(xs);
+    const double w = 1.0 / G.inv_w;
+    const bool edge = fr * w < rc || (1.0 - fr) * w < rc;
+    flag = (edge || k - kf <= rows_margin || kl - k <= rows_margin) ? 1 : 0;
+  }
+  // exclusive scan of the flags over the CTA
+  const int lane = t & 31, warp = t >> 5;
+  const unsigned int b = __ballot_sync(0xffffffffu, flag);
+  if (lane == 0) wsum[warp] = __popc(b);
+  __syncthreads();
+  if (warp == 0) {
+    const int v = wsum[lane];
+    int inc = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int u = __shfl_up_sync(0xffffffffu, inc, d);
+      if (lane >= d) inc += u;
+    }
+    wsum[lane] = inc - v;
+    if (lane == 31) s_total = inc;
+  }
+  __syncthreads();
+  const int before = wsum[warp] + __popc(b & ((1u << lane) - 1u));   // flagged particles in front of this one
+  if (t < cnt) {
+    const int dst = flag ? before : s_total + (t - before);
+    s_id[dst] = id;
+  }
+  __syncthreads();
+  if (t < cnt) perm[base + t] = s_id[t];
+}
+
 // K5: the per-slot constants the rebuild phases gather by slot (species, ordering key = Philox id)
 __global__ void k_sort_gather(long long n, const int *perm, const int *species, const long long *gid, int *species_s,
                               long long *gid_s) {

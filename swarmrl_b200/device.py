@@ -240,7 +240,7 @@ class DeviceSwarm:
         """dict of the tiled kernel's counters (swarm_tiling_stats); synchronises."""
         out = (C.c_int64 * 8)()
         _lib.check(self.lib.swarm_tiling_stats(self.h, out))
-        keys = ("tiled", "cadence", "steps_on_list", "rollbacks", "partner_sum", "sorts", "ctas", "slots_per_cta")
+        keys = ("tiled", "cadence", "steps_on_list", "rollbacks", "rim_sum", "sorts", "ctas", "slots_per_cta")
         return dict(zip(keys, [int(v) for v in out]))
 
     def tiled_neighbors(self):

@@ -224,7 +224,7 @@ class SwarmEngine(Engine):
     backend_factory = staticmethod(_default_backend)
 
     def __init__(self, md_params, n_dims=3, seed=42, out_folder=".", write_chunk_size=100, system=None,
-                 h5_group_tag=None, skin=None, persistent=True):
+                 h5_group_tag=None, skin=None, persistent=True, async_writer=True):
         self.params = md_params
         self.out_folder = pathlib.Path(out_folder).resolve()
         self.seed = seed
@@ -237,6 +237,8 @@ class SwarmEngine(Engine):
         self.h5_group_tag = "colloids" if h5_group_tag is None else h5_group_tag
         self._skin = skin
         self._persistent = persistent
+        self._async_writer = async_writer   # False: the synchronous snapshot / chunk writer (what the oracle backend uses)
+        self._writer = None
         self._time = 0.0
         self._init_system()
         self.system = _SystemView(self)
@@ -537,6 +539,18 @@ class SwarmEngine(Engine):
                             ("Times", "Ids", "Types", "Unwrapped_Positions", "Velocities", "Directors")}
         self.write_idx = 0
         self.h5_time_steps_written = 0
+        self._writer = None
+        be = self._backend
+        if self._async_writer and be is not None and hasattr(be, "lib") and hasattr(be, "h") and self.n_colloids > 0:
+            # CUDA backend: device snapshot ring -> pinned host -> writer thread (swarmrl_b200/trajectory.py); the hot
+            # loop only enqueues.  `traj_holder` is the writer's pending chunk (filled by its thread).
+            from .trajectory import AsyncTrajectoryWriter
+
+            self._writer = AsyncTrajectoryWriter(be, self._types, self.out_folder, self.h5_group_tag, self.write_chunk_size,
+                                                 h5_filename=self.h5_filename)
+            self.traj_holder = self._writer.pending
+            self._h5py = self._writer._h5py
+            return
         try:
             import h5py
         except ModuleNotFoundError:
@@ -559,6 +573,9 @@ class SwarmEngine(Engine):
         """Snapshot taken BEFORE the chunk is integrated (espresso.py:1110-1130, 1278-1280)."""
         if self.n_colloids == 0:
             logger.warning("No colloids in the system. Not writing to hdf5")
+            return
+        if self._writer is not None:
+            self._writer.snapshot(self._time)
             return
         pos, vel, dr = self.colloids._snapshot()
         self.traj_holder["Times"].append(np.array([self._time])[:, np.newaxis])
@@ -649,7 +666,7 @@ class SwarmEngine(Engine):
             if self.step_idx == self.params.steps_per_write_interval * self.write_idx:
                 self._update_traj_holder()
                 self.write_idx += 1
-                if len(self.traj_holder["Times"]) >= self.write_chunk_size:
+                if self._writer is None and len(self.traj_holder["Times"]) >= self.write_chunk_size:
                     self._write_traj_chunk_to_file()
                     for val in self.traj_holder.values():
                         val.clear()
@@ -712,6 +729,10 @@ class SwarmEngine(Engine):
     def finalize(self):
         """espresso.py:1310-1318: flush, no snapshot."""
         if self.traj_holder is None:
+            return
+        if self._writer is not None:
+            self._writer.flush()
+            self.h5_time_steps_written = self._writer.frames_written
             return
         self._write_traj_chunk_to_file()
         for val in self.traj_holder.values():
