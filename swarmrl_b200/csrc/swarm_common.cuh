@@ -145,6 +145,8 @@ struct swarm {
   double *red_scratch = nullptr;
   void *vis_buf = nullptr;   // vision-cone cell structure + packed copies
   size_t vis_bytes = 0;
+  long long vis_prev_n = -1;   // the bounding box of the previous vision call is usable for this n / range
+  double vis_prev_range = 0.0;
   Ctl *ctl_host = nullptr;  // pinned
 };
 

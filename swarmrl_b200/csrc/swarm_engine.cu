@@ -949,6 +949,7 @@ extern "C" int swarm_bind_state(swarm_t *s, int64_t n, const swarm_state_dev_t *
     s->tile.mode = tmode; s->tile.resort_interval = tint;
   }
   s->tile.sorted = false;   // other particles: the slot order has to be computed again
+  s->vis_prev_n = -1;
   A.n = n;
   s->st = *st;
   A.x[0] = st->x; A.y[0] = st->y; A.z[0] = st->z;

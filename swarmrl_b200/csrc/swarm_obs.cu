@@ -231,6 +231,10 @@ struct VisBuild {
   unsigned int bar;
   unsigned int pad;
 };
+// Bounding box of the previous call (outside the memset).  A grid laid over ANY box is correct -- coordinates are clamped
+// into the edge cells, which keeps cell indices of two particles within `range` of each other at most one apart -- so the
+// box of the previous slice, widened by one range, saves the barrier between "bounding box" and "cell of every particle".
+struct VisPrev { unsigned long long mnc[3], mx[3]; };
 
 __device__ __forceinline__ void vis_grid_barrier(unsigned int *counter, unsigned int &epoch) {
   __syncthreads();
@@ -249,7 +253,7 @@ __device__ __forceinline__ void vis_grid_barrier(unsigned int *counter, unsigned
 __global__ void __launch_bounds__(VISB_T) k_vis_build(long long n, const double *x, const double *y, const double *z,
                                                       const double *radii, const int *species, const __grid_constant__ DevParams P,
                                                       const int *type_col, int n_type_col, double range, long long ncell_max,
-                                                      VisBuild *B, VisGrid *G, int *count, int *start, int *fill, int *cellid,
+                                                      VisBuild *B, VisPrev *prev, int use_prev, VisGrid *G, int *count, int *start, int *fill, int *cellid,
                                                       int *items, double *sx, double *sy, double *sz, double *sr, int *scol,
                                                       double *out, long long out_len) {
   unsigned int epoch = 0;
@@ -283,12 +287,18 @@ __global__ void __launch_bounds__(VISB_T) k_vis_build(long long n, const double 
       atomicMax(&B->mx[a], m1);
     }
   }
-  vis_grid_barrier(&B->bar, epoch);
+  if (!use_prev) vis_grid_barrier(&B->bar, epoch);
   // ---- phase 1: the grid (every CTA computes the same one), cell of every particle, histogram -----------------------
   if (threadIdx.x == 0) {
     double ext[3];
     for (int a = 0; a < 3; ++a) {
-      double lo = dec_double(~__ldcg(&B->mnc[a])), hi = dec_double(__ldcg(&B->mx[a]));
+      double lo, hi;
+      if (use_prev) {
+        lo = dec_double(~prev->mnc[a]); hi = dec_double(prev->mx[a]);
+        if (hi > lo || a < 2) { lo -= range; hi += range; }   // a flat axis (2-D: z) stays flat
+      } else {
+        lo = dec_double(~__ldcg(&B->mnc[a])); hi = dec_double(__ldcg(&B->mx[a]));
+      }
       if (!(hi >= lo)) { lo = 0.0; hi = 0.0; }
       g.lo[a] = lo;
       ext[a] = hi - lo;
@@ -329,10 +339,13 @@ __global__ void __launch_bounds__(VISB_T) k_vis_build(long long n, const double 
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int m = g.ncell + 1;
-    for (int b0 = 0; b0 < m; b0 += VISB_T) {
-      const int b = b0 + threadIdx.x;
-      const int v = (b < m) ? __ldcg(&count[b]) : 0;
-      int inc = v;
+    for (int b0 = 0; b0 < m; b0 += VISB_T * 8) {
+      // eight consecutive cells per thread: 4096 per round
+      const int b = b0 + threadIdx.x * 8;
+      int v[8], tsum = 0;
+#pragma unroll
+      for (int q = 0; q < 8; ++q) { v[q] = (b + q < m) ? __ldcg(&count[b + q]) : 0; tsum += v[q]; }
+      int inc = tsum;
 #pragma unroll
       for (int d = 1; d < 32; d <<= 1) {
         const int t = __shfl_up_sync(0xffffffffu, inc, d);
@@ -351,10 +364,14 @@ __global__ void __launch_bounds__(VISB_T) k_vis_build(long long n, const double 
         if (lane < VISB_T / 32) wsum[lane] = winc - wv;
       }
       __syncthreads();
-      const int excl = carry + wsum[warp] + inc - v;
-      if (b < m) { start[b] = excl; fill[b] = excl; }
+      int excl = carry + wsum[warp] + inc - tsum;
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        if (b + q < m) { start[b + q] = excl; fill[b + q] = excl; }
+        excl += v[q];
+      }
       __syncthreads();
-      if (threadIdx.x == VISB_T - 1) carry = excl + v;
+      if (threadIdx.x == VISB_T - 1) carry = excl;
       __syncthreads();
     }
   }
@@ -383,6 +400,7 @@ __global__ void __launch_bounds__(VISB_T) k_vis_build(long long n, const double 
     const int t = P.sp_type[species[i]];
     scol[k] = (t >= 0 && t < n_type_col) ? type_col[t] : -1;
   }
+  if (gtid < 3) { prev->mnc[gtid] = __ldcg(&B->mnc[gtid]); prev->mx[gtid] = __ldcg(&B->mx[gtid]); }   // complete since the first barrier passed
 }
 
 #define VIS_MAX_ACC 64
@@ -812,6 +830,7 @@ extern "C" int swarm_obs_vision(swarm_t *s, const int32_t *row_of, int64_t rows,
   size_t off = 0;
   auto carve = [&](size_t bytes) { size_t o = off; off += align256(bytes); return o; };
   size_t o_grid = carve(sizeof(VisGrid));
+  size_t o_prev = carve(sizeof(VisPrev));
   size_t o_build = carve(sizeof(VisBuild));   // directly in front of count[]: one memset zeroes both
   size_t o_count = carve(sizeof(int) * (size_t)m), o_start = carve(sizeof(int) * (size_t)m), o_fill = carve(sizeof(int) * (size_t)m);
   size_t o_tiles = carve(sizeof(int) * (size_t)ntiles);
@@ -823,6 +842,7 @@ extern "C" int swarm_obs_vision(swarm_t *s, const int32_t *row_of, int64_t rows,
     s->vis_buf = nullptr; s->vis_bytes = 0;
     SW_CUDA(cudaMalloc(&s->vis_buf, off));
     s->vis_bytes = off;
+    s->vis_prev_n = -1;
   }
   char *base = (char *)s->vis_buf;
   VisGrid *G = (VisGrid *)(base + o_grid);
@@ -841,6 +861,9 @@ extern "C" int swarm_obs_vision(swarm_t *s, const int32_t *row_of, int64_t rows,
   }
   if (fused) {
     VisBuild *VB = (VisBuild *)(base + o_build);
+    VisPrev *VP = (VisPrev *)(base + o_prev);
+    int use_prev = (s->vis_prev_n == n && s->vis_prev_range == vision_range && !getenv("SWARM_B200_VIS_NO_PREV")) ? 1 : 0;
+    s->vis_prev_n = n; s->vis_prev_range = vision_range;
     SW_CUDA(cudaMemsetAsync(VB, 0, (size_t)((char *)(count + m) - (char *)VB), st));
     long long want = (n + VISB_T - 1) / VISB_T;
     if (bpsm > 2) bpsm = 2;
@@ -852,7 +875,7 @@ extern "C" int swarm_obs_vision(swarm_t *s, const int32_t *row_of, int64_t rows,
     const int *spc = A.species;
     double rng_ = vision_range;
     int ntc = n_type_col;
-    void *args[] = {&nn, &px, &py, &pz, &radii, &spc, &P, &type_col, &ntc, &rng_, &ncm, &VB, &G, &count, &start, &fill,
+    void *args[] = {&nn, &px, &py, &pz, &radii, &spc, &P, &type_col, &ntc, &rng_, &ncm, &VB, &VP, &use_prev, &G, &count, &start, &fill,
                     &cellid, &items, &sx, &sy, &sz, &sr, &scol, &out, &ol};
     SW_CUDA(cudaLaunchCooperativeKernel((void *)k_vis_build, dim3(grid), dim3(VISB_T), args, 0, st));
     s->launches += 1;

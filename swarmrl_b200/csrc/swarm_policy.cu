@@ -28,6 +28,10 @@ struct PolNet {
   const float *w1, *b1, *wa, *ba, *wv, *bv;
 };
 
+// DMAX / AMAX bound the unrolled loops: the network of the reference's tests (obs_dim <= 8, 4 actions) runs the <8, 4>
+// instance -- 13 multiply-adds per hidden unit instead of the 48 predicated ones of the widest instance (128 us -> the
+// kernel was a fifth of the C4 slice on the Engine path, profiles/r02_launches_engine.csv).
+template <int DMAX, int AMAX>
 __global__ void __launch_bounds__(POL_THREADS) k_policy_forward(long long n, PolNet N, const double *obs, const int *row_of,
                                                                 const long long *gid, u64 seed, u64 call, int sample,
                                                                 const double *act_force, const double *act_torque,
@@ -45,30 +49,30 @@ __global__ void __launch_bounds__(POL_THREADS) k_policy_forward(long long n, Pol
   if (i >= n) return;
   const int row = row_of ? row_of[i] : (int)i;
   if (row < 0) return;
-  float x[POL_MAX_OBS], lg[POL_MAX_ACT];
+  float x[DMAX], lg[AMAX];
 #pragma unroll
-  for (int d = 0; d < POL_MAX_OBS; ++d) x[d] = (d < D) ? (float)obs[(long long)row * D + d] : 0.0f;
+  for (int d = 0; d < DMAX; ++d) x[d] = (d < D) ? (float)obs[(long long)row * D + d] : 0.0f;
 #pragma unroll
-  for (int a = 0; a < POL_MAX_ACT; ++a) lg[a] = (a < A) ? ba[a] : -INFINITY;
+  for (int a = 0; a < AMAX; ++a) lg[a] = (a < A) ? ba[a] : -INFINITY;
   float val = N.bv[0];
   for (int j = 0; j < H; ++j) {
     float h = b1[j];
 #pragma unroll
-    for (int d = 0; d < POL_MAX_OBS; ++d)
+    for (int d = 0; d < DMAX; ++d)
       if (d < D) h = fmaf(x[d], w1[d * H + j], h);
     h = fmaxf(h, 0.0f);
 #pragma unroll
-    for (int a = 0; a < POL_MAX_ACT; ++a)
+    for (int a = 0; a < AMAX; ++a)
       if (a < A) lg[a] = fmaf(h, wa[j * A + a], lg[a]);
     val = fmaf(h, wv[j], val);
   }
   // log(softmax + 1e-8), max-shifted as jax.nn.softmax does
   float mx = -INFINITY;
 #pragma unroll
-  for (int a = 0; a < POL_MAX_ACT; ++a) if (a < A) mx = fmaxf(mx, lg[a]);
+  for (int a = 0; a < AMAX; ++a) if (a < A) mx = fmaxf(mx, lg[a]);
   float den = 0.0f;
 #pragma unroll
-  for (int a = 0; a < POL_MAX_ACT; ++a) if (a < A) den += expf(lg[a] - mx);
+  for (int a = 0; a < AMAX; ++a) if (a < A) den += expf(lg[a] - mx);
   int best = 0;
   if (sample) {
     const u64 pid = gid ? (u64)gid[i] : (u64)i;
@@ -83,7 +87,7 @@ __global__ void __launch_bounds__(POL_THREADS) k_policy_forward(long long n, Pol
         const double uu = ((double)(r[u] >> 11) + 0.5) * (1.0 / 9007199254740992.0);
         float v = -INFINITY;
 #pragma unroll
-        for (int q = 0; q < POL_MAX_ACT; ++q) if (q == a) v = lg[q];
+        for (int q = 0; q < AMAX; ++q) if (q == a) v = lg[q];
         v -= (float)log(-log(uu));
         if (v > bv) { bv = v; best = a; }
       }
@@ -91,11 +95,11 @@ __global__ void __launch_bounds__(POL_THREADS) k_policy_forward(long long n, Pol
   } else {
     float bv = -INFINITY;
 #pragma unroll
-    for (int a = 0; a < POL_MAX_ACT; ++a) if (a < A && lg[a] > bv) { bv = lg[a]; best = a; }
+    for (int a = 0; a < AMAX; ++a) if (a < A && lg[a] > bv) { bv = lg[a]; best = a; }
   }
   float lb = 0.0f;
 #pragma unroll
-  for (int a = 0; a < POL_MAX_ACT; ++a) if (a == best) lb = lg[a];
+  for (int a = 0; a < AMAX; ++a) if (a == best) lb = lg[a];
   if (idx_out) idx_out[row] = best;
   if (logp_out) logp_out[row] = logf(expf(lb - mx) / den + 1e-8f);
   if (value_out) value_out[row] = val;
@@ -103,7 +107,7 @@ __global__ void __launch_bounds__(POL_THREADS) k_policy_forward(long long n, Pol
     for (int a = 0; a < A; ++a) {
       float v = 0.0f;
 #pragma unroll
-      for (int q = 0; q < POL_MAX_ACT; ++q) if (q == a) v = lg[q];
+      for (int q = 0; q < AMAX; ++q) if (q == a) v = lg[q];
       logits_out[(long long)row * A + a] = v;
     }
   if (act_force && f_swim) {   // manage_forces: the chosen action straight into the engine's arrays
@@ -128,11 +132,18 @@ extern "C" int swarm_policy_forward(swarm_t *s, const swarm_policy_t *net, const
   SW_CUDA(cudaSetDevice(s->cfg.device));
   const DevArrays &A = s->A;
   if (A.n == 0) return SWARM_OK;
-  if (smem > 48 * 1024) SW_CUDA(cudaFuncSetAttribute(k_policy_forward, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   PolNet N{net->obs_dim, net->hidden, net->n_actions, net->w1, net->b1, net->wa, net->ba, net->wv, net->bv};
-  k_policy_forward<<<sw_blocks(A.n, POL_THREADS), POL_THREADS, smem, (cudaStream_t)stream>>>(
-      A.n, N, obs_dev, row_of_dev, A.gid, s->P.seed, call, sample, act_force_dev, act_torque_dev, A.f_swim, A.tqx, A.tqy, A.tqz,
-      idx_out_dev, logp_out_dev, value_out_dev, logits_out_dev);
+#define POL_LAUNCH(DM, AM)                                                                                                        \
+  do {                                                                                                                            \
+    if (smem > 48 * 1024) SW_CUDA(cudaFuncSetAttribute(k_policy_forward<DM, AM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    k_policy_forward<DM, AM><<<sw_blocks(A.n, POL_THREADS), POL_THREADS, smem, (cudaStream_t)stream>>>(                           \
+        A.n, N, obs_dev, row_of_dev, A.gid, s->P.seed, call, sample, act_force_dev, act_torque_dev, A.f_swim, A.tqx, A.tqy,      \
+        A.tqz, idx_out_dev, logp_out_dev, value_out_dev, logits_out_dev);                                                          \
+  } while (0)
+  if (net->obs_dim <= 8 && net->n_actions <= 4) POL_LAUNCH(8, 4);
+  else if (net->obs_dim <= 16 && net->n_actions <= 8) POL_LAUNCH(16, 8);
+  else POL_LAUNCH(POL_MAX_OBS, POL_MAX_ACT);
+#undef POL_LAUNCH
   s->launches += 1;
   SW_CUDA(cudaGetLastError());
   return SWARM_OK;

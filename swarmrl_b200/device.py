@@ -390,9 +390,9 @@ class DeviceSwarm:
         A = net["wa"].shape[1]
         p = _lib.Policy(int(D), int(H), int(A), *[net[k].data_ptr() for k in ("w1", "b1", "wa", "ba", "wv", "bv")])
         m = max(n_rows, 1)
-        idx = torch.zeros(m, dtype=torch.int32, device=self.dev)
-        logp = torch.zeros(m, dtype=torch.float32, device=self.dev)
-        val = torch.zeros(m, dtype=torch.float32, device=self.dev)
+        idx = torch.empty(m, dtype=torch.int32, device=self.dev)     # every row belongs to one particle: the kernel writes it
+        logp = torch.empty(m, dtype=torch.float32, device=self.dev)
+        val = torch.empty(m, dtype=torch.float32, device=self.dev)
         lg = torch.zeros((m, A), dtype=torch.float32, device=self.dev) if want_logits else None
         obs = obs.contiguous()
         _lib.check(self.lib.swarm_policy_forward(

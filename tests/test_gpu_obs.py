@@ -248,3 +248,38 @@ def test_pair_field_matches_oracle_at_scale_and_multi_classes():
         assert np.allclose(obs[:, k], f1[k] - f0[k], rtol=1e-9, atol=1e-9)
     want = 3.0 * np.clip(g1[0] - g0[0], 0, None) + 2.0 * np.clip(g1[1] - g0[1], None, 0)
     assert np.allclose(rew, want, rtol=1e-9, atol=1e-9)
+
+
+def test_fp32_reference_bounds(golden):
+    """The reference evaluates these observables in JAX float32; the kernels compute in fp64.
+    Kernel output against the oracle's float32 evaluation mode (oracle.{vision_cones_f32, field_delta_f32}), with the
+    per-observable bounds stated in tests/test_oracle_fp32.py: vision cones 1e-5 per cone sum except entries where a
+    particle sits within float32 rounding of a rim / of the range (< 0.5 % of the entries, off by <= one weight);
+    field observables 8 eps32 * scale * (|c0| + |c1| d_max)."""
+    import torch
+
+    from oracle import oracle
+
+    (o, d), rng = _pair(n=2500, L=260.0)
+    n = o.n
+    radii = rng.uniform(0.5, 1.5, n)
+    row_of, rows = d.row_map(0)
+    tc = torch.from_numpy(np.array([0, 1], dtype=np.int32)).to(d.dev)
+    out = d.obs_vision(row_of, rows, 12.0, np.pi / 2, 5, torch.from_numpy(radii).to(d.dev), tc, 2).cpu().numpy()
+    ref32 = oracle.vision_cones_f32(o.pos, o.directors, o.ptype, 0, 12.0, np.pi / 2, 5, radii, [0, 1]).astype(np.float64)
+    diff = np.abs(out - ref32)
+    flipped = diff > 1e-5
+    assert out.shape == ref32.shape and flipped.mean() < 0.005 and np.all(diff[flipped] <= 1.0 + 1e-5)
+    assert diff[~flipped].max() > 0.0          # the two precisions differ: the bound is not vacuous
+    # field observable, scale 1e4 as in the reference's RL tests
+    L, scale = 260.0, 10000.0
+    src = np.array([0.5, 0.5, 0.0])
+    prev = o.pos / L
+    hist = torch.from_numpy(np.ascontiguousarray(prev.T)).to(d.dev)
+    d.pos[:2, :n] += torch.from_numpy(rng.normal(size=(2, n)) * 0.5).to(d.dev)
+    now = d.pos[:, :n].cpu().numpy().T / L
+    got, _, _ = d.obs_field(row_of, rows, src, (L, L, L), hist, decay=1, c0=1.0, c1=-1.0, scale=scale, clip=False, want_dist=False)
+    sel = o.ptype == 0
+    ref = oracle.field_delta_f32(now[sel], prev[sel], src, 1, 1.0, -1.0, scale, False).astype(np.float64)
+    tol = 8 * 2.0 ** -24 * scale * (1.0 + 1.0 * 3.0)
+    assert np.max(np.abs(got.cpu().numpy() - ref)) <= tol
