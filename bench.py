@@ -548,6 +548,7 @@ def engine_record(args, local, K, W):
     # one untimed call of the timed shape: the host runs ahead of the device inside integrate(K), so the caching allocator
     # grows its pool (cudaMalloc, a device synchronisation each) the first time K slices are in flight
     e.integrate(K, ff)
+    torch.stack(agent.reward_means)[:, 1].cpu()   # and of the read-out: torch loads the kernels of stack / index lazily (tens of ms, once per process)
     st0 = e._backend.stats()
     agent.reward_means.clear()
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=e._backend.dev)

@@ -320,6 +320,10 @@ int swarm_policy_forward(swarm_t *s, const swarm_policy_t *net, const double *ob
 /* ---- host-buffer entry points (what a cgo/ctypes binding of the reference would call) --- */
 /* manage_forces: write f_swim and ext torque of every particle (espresso.py:1227-1235) */
 int swarm_set_actions_host(swarm_t *s, const double *f_swim_host, const double *torque3n_host, void *stream);
+/* Measurement hook (no reference counterpart): DFMA throughput of the device with `ilp` (1, 4 or 8) independent chains per
+ * thread -- the fp64 peak the roofline notes of DESIGN.md / BASELINE.md divide by.  out4: DFMA/s, ms, SM count, ilp used. */
+int swarm_microbench_dfma(int32_t device, int32_t ilp, int32_t iters, double out4[4]);
+
 /* One trajectory frame (espresso.py:1110-1130: Unwrapped_Positions, Velocities, Directors) into three [n][3]
  * row-major DEVICE buffers, one kernel on `stream`, no host synchronisation: the snapshot ring of the asynchronous
  * trajectory writer (espresso.py:1278-1285 takes the snapshot before the chunk is integrated). */

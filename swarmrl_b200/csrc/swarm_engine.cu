@@ -1670,6 +1670,52 @@ extern "C" int swarm_philox_host(const uint64_t ctr[4], const uint64_t key[2], u
   return SWARM_OK;
 }
 
+// fp64 peak as these kernels can see it: `ilp` independent DFMA chains per thread, `iters` x 64 DFMAs per chain, every
+// SM full (the denominator of the issue / fp64-pipe fractions in DESIGN.md)
+template <int ILP>
+__global__ void __launch_bounds__(256) k_microbench_dfma(int iters, double a, double b, double *sink) {
+  double v[ILP];
+#pragma unroll
+  for (int k = 0; k < ILP; ++k) v[k] = (double)(threadIdx.x + k);
+  for (int it = 0; it < iters; ++it) {
+#pragma unroll
+    for (int r = 0; r < 64; ++r)
+#pragma unroll
+      for (int k = 0; k < ILP; ++k) v[k] = fma(v[k], a, b);
+  }
+  double s = 0.0;
+#pragma unroll
+  for (int k = 0; k < ILP; ++k) s += v[k];
+  if (s == 123.456) sink[0] = s;   // never true: keeps the chains alive
+}
+
+extern "C" int swarm_microbench_dfma(int32_t device, int32_t ilp, int32_t iters, double out4[4]) {
+  if (!out4 || iters < 1) return SWARM_ERR_INVALID;
+  SW_CUDA(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  SW_CUDA(cudaGetDeviceProperties(&prop, device));
+  double *sink = nullptr;
+  SW_CUDA(cudaMalloc((void **)&sink, 8));
+  const int blocks = prop.multiProcessorCount * 8, threads = 256;
+  cudaEvent_t e0, e1;
+  SW_CUDA(cudaEventCreate(&e0)); SW_CUDA(cudaEventCreate(&e1));
+  const int I = (ilp >= 8) ? 8 : (ilp >= 4 ? 4 : 1);
+  for (int rep = 0; rep < 2; ++rep) {   // the first repetition warms up
+    SW_CUDA(cudaEventRecord(e0));
+    if (I == 8) k_microbench_dfma<8><<<blocks, threads>>>(iters, 0.999999, 1e-9, sink);
+    else if (I == 4) k_microbench_dfma<4><<<blocks, threads>>>(iters, 0.999999, 1e-9, sink);
+    else k_microbench_dfma<1><<<blocks, threads>>>(iters, 0.999999, 1e-9, sink);
+    SW_CUDA(cudaEventRecord(e1));
+    SW_CUDA(cudaEventSynchronize(e1));
+  }
+  float ms = 0.0f;
+  SW_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(sink);
+  const double n = (double)blocks * threads * (double)iters * 64.0 * I;
+  out4[0] = n / (ms * 1e-3); out4[1] = ms; out4[2] = prop.multiProcessorCount; out4[3] = I;
+  return SWARM_OK;
+}
+
 extern "C" int swarm_noise_words_host(uint64_t seed, uint64_t id, uint64_t step, uint64_t stream_id, uint64_t out[4]) {
   if (!out) return SWARM_ERR_INVALID;
   u64 o[4];

@@ -9,12 +9,15 @@ waits for any of that:
 
     run stream    : swarm_snapshot_dev -> one kernel writes the frame into a slot of a DEVICE ring, event
     copy stream   : waits for that event, cudaMemcpyAsync device slot -> PINNED host slot, event
-    writer thread : waits for the copy event, moves the frame into the pending chunk, frees the slot, and writes a
-                    chunk file whenever `write_chunk_size` frames are pending (HDF5 in the reference's layout when
-                    h5py is importable, numbered `.npz` chunks with the same arrays otherwise)
+    writer thread : waits for the copy event, books the frame into the pending chunk -- the pending arrays are VIEWS of
+                    the pinned slots, a frame is not copied again on the host -- and writes a chunk file whenever
+                    `write_chunk_size` frames are pending or every slot is taken (HDF5 in the reference's layout when
+                    h5py is importable, numbered `.npz` chunks with the same arrays otherwise); writing frees the slots
 
-`snapshot()` blocks only when all ring slots are still in flight (the writer cannot keep up); `flush()` drains the
-ring and writes the partial chunk without taking a snapshot (espresso.py:1310-1318, `finalize`).
+The ring holds `write_chunk_size` frames when that fits the pinned-memory budget (1 GiB), else as many as fit (chunks
+are then shorter).  `snapshot()` blocks only when every slot is taken and its chunk is still being written -- at that
+point the rollout produces frames faster than the file system takes them (C4 with a frame per slice is 10 GB/s).
+`flush()` drains the ring and writes the partial chunk without taking a snapshot (espresso.py:1310-1318, `finalize`).
 """
 from __future__ import annotations
 
@@ -40,14 +43,16 @@ class AsyncTrajectoryWriter:
         self.h5_filename = h5_filename
         frame_bytes = 72 * max(self.n, 1)
         if ring is None:
-            ring = max(2, min(self.chunk_size, (256 << 20) // frame_bytes, 64))
+            ring = max(2, min(self.chunk_size, (1 << 30) // frame_bytes))
         self.ring = int(ring)
         m = max(self.n, 1)
-        self.dev = torch.empty((self.ring, 3, m, 3), dtype=torch.float64, device=swarm.dev)     # [slot][pos|vel|dir][n][3]
+        self.dev_ring = min(self.ring, 4)           # a device slot is free again as soon as its frame has been copied out
+        self.dev = torch.empty((self.dev_ring, 3, m, 3), dtype=torch.float64, device=swarm.dev)  # [slot][pos|vel|dir][n][3]
+        self.dev_copied = [None] * self.dev_ring
         self.pin = torch.empty((self.ring, 3, m, 3), dtype=torch.float64).pin_memory()
         self.copy_stream = torch.cuda.Stream(device=swarm.dev)
         self.copied = [None] * self.ring            # event: the D2H copy of the slot has finished
-        self.free = threading.Semaphore(self.ring)  # slots the writer thread has consumed
+        self.free = threading.Semaphore(self.ring)  # slots whose frame has been written to a file
         self.q = queue.Queue()
         self.pending = {k: [] for k in KEYS}        # the reference's traj_holder
         self.frames_taken = 0
@@ -73,9 +78,10 @@ class AsyncTrajectoryWriter:
         slot = self.frames_taken % self.ring
         torch, sw = self.torch, self.swarm
         run = torch.cuda.current_stream(sw.dev)
-        if self.copied[slot] is not None:
-            run.wait_event(self.copied[slot])        # the slot's previous frame has left the device
-        d = self.dev[slot]
+        dslot = self.frames_taken % self.dev_ring
+        if self.dev_copied[dslot] is not None:
+            run.wait_event(self.dev_copied[dslot])   # the device slot's previous frame has left the device
+        d = self.dev[dslot]
         _lib.check(sw.lib.swarm_snapshot_dev(sw.h, d[0].data_ptr(), d[1].data_ptr(), d[2].data_ptr(), C.c_void_p(run.cuda_stream)))
         taken = torch.cuda.Event()
         taken.record(run)
@@ -85,6 +91,7 @@ class AsyncTrajectoryWriter:
             done = torch.cuda.Event()
             done.record(self.copy_stream)
         self.copied[slot] = done
+        self.dev_copied[dslot] = done
         self.frames_taken += 1
         self.q.put((slot, float(time), done))
 
@@ -104,15 +111,15 @@ class AsyncTrajectoryWriter:
                 self.pending["Times"].append(np.array([[time]]))
                 self.pending["Ids"].append(self.ids[:, None])
                 self.pending["Types"].append(self.types[:, None])
-                self.pending["Unwrapped_Positions"].append(f[0, : self.n].copy())
-                self.pending["Velocities"].append(f[1, : self.n].copy())
-                self.pending["Directors"].append(f[2, : self.n].copy())
-                self.free.release()
-                if len(self.pending["Times"]) >= self.chunk_size:
+                self.pending["Unwrapped_Positions"].append(f[0, : self.n])   # views of the pinned slot
+                self.pending["Velocities"].append(f[1, : self.n])
+                self.pending["Directors"].append(f[2, : self.n])
+                if len(self.pending["Times"]) >= min(self.chunk_size, self.ring):
                     self._write_chunk()
             except Exception as exc:  # surfaced by the next snapshot() / flush()
                 self.error = exc
-                self.free.release()
+                for _ in range(self.ring):
+                    self.free.release()
             finally:
                 self.q.task_done()
 
@@ -147,6 +154,8 @@ class AsyncTrajectoryWriter:
         self.frames_written += n_new
         for v in self.pending.values():
             v.clear()
+        for _ in range(n_new):      # the slots of the written frames may be overwritten now
+            self.free.release()
 
     # ------------------------------------------------------------------ control
     def drain(self):

@@ -428,3 +428,65 @@ def test_antiparallel_new_direction_turns_by_pi_without_nan():
     d.apply_new_direction()
     e1 = d.directors().cpu().numpy().T
     assert np.all(np.isfinite(e1)) and np.allclose(e1, -e0, atol=1e-12)
+
+
+def test_config2_noise_statistics_over_32_replicas():
+    """BASELINE config 2 with noise ON (north_star's third check): 32 replicas of the 1,000-colloid
+    WCA swarm in ONE batched launch (n_envs = 32; every replica draws its own noise because the Philox id is the global
+    particle index).  (a) <e(0).e(t)> of every replica against exp(-D_r t) -- exact for the Euler-Maruyama angle update,
+    whatever the forces do; (b) MSD(t) against the CPU oracle run on INDEPENDENT noise (other seeds), Welch's test on
+    the replica means.  Bars: at least three quarters of the eight checks within 2 sigma of the standard error and all
+    within 3 (the four time points of one quantity come from the same trajectories, so they are not independent draws:
+    two of them beyond 2 sigma together is one fluctuation, not two)."""
+    import torch
+
+    from oracle.oracle import OracleSwarm
+    from swarmrl_b200.device import DeviceSwarm
+
+    E, m, L, dt = 32, 1000, 125.0, 1e-3
+    rng = np.random.default_rng(1234)
+    sp, wca = species_for([1.0]), wca_for([1.0])
+    pos1 = jittered_lattice(m, L, 2, rng)
+    th1 = rng.uniform(0, 2 * np.pi, m)
+    pos, th = np.tile(pos1, (E, 1)), np.tile(th1, E)
+    d = DeviceSwarm(2, (L,) * 3, True, dt, KT_300, 42, sp, wca, n_envs=E, skin=1.0)
+    d.set_state(pos, np.zeros(E * m, dtype=np.int32), theta=th)
+    gt, gr = sp[0]["gamma_t"][0], sp[0]["gamma_r"][0]
+    Dr = KT_300 / gr
+    times = [50, 100, 200, 300]
+    msd_g, cor_g = [], []
+    done = 0
+    for t in times:
+        st = d.run_checked(t - done, done)
+        assert not st.overflow
+        done = t
+        p = d.pos[:2, : E * m].cpu().numpy().T
+        a = d.theta[: E * m].cpu().numpy()
+        msd_g.append(((p - pos[:, :2]) ** 2).sum(axis=1).reshape(E, m).mean(axis=1))
+        cor_g.append(np.cos(a - th).reshape(E, m).mean(axis=1))
+    msd_g, cor_g = np.array(msd_g), np.array(cor_g)          # (times, replicas)
+    # (a) orientation autocorrelation against the analytic decay
+    z = []
+    for k, t in enumerate(times):
+        se = cor_g[k].std(ddof=1) / np.sqrt(E)
+        z.append(abs(cor_g[k].mean() - np.exp(-Dr * t * dt)) / se)
+    # (b) MSD against oracle replicas on independent noise
+    R = 8
+    msd_o = np.zeros((len(times), R))
+    for r in range(R):
+        o = OracleSwarm(2, (L,) * 3, True, dt, KT_300, 1000 + r, sp, wca)
+        o.set_state(pos1, np.zeros(m, dtype=np.int32), theta=th1)
+        done = 0
+        for k, t in enumerate(times):
+            o.bd_steps(done, t - done, mode=2)
+            done = t
+            msd_o[k, r] = ((o.pos[:, :2] - pos1[:, :2]) ** 2).sum(axis=1).mean()
+    for k in range(len(times)):
+        se = np.sqrt(msd_g[k].var(ddof=1) / E + msd_o[k].var(ddof=1) / R)
+        z.append(abs(msd_g[k].mean() - msd_o[k].mean()) / se)
+    z = np.array(z)
+    assert np.mean(z < 2.0) >= 0.75, z
+    assert np.all(z < 3.0), z
+    # free-diffusion scale (collisions slow the swarm down, the first contacts of the jittered lattice push it apart)
+    D = KT_300 / gt
+    assert 0.5 * 4 * D * times[-1] * dt < msd_g[-1].mean() < 1.5 * 4 * D * times[-1] * dt
