@@ -475,6 +475,58 @@ __global__ void __launch_bounds__(128) k_vis_cones(long long n, const int *items
 // by a fixed shuffle tree: deterministic, though no longer in ascending particle order.
 #define VISW_THREADS 128
 #define VISW_MAX_ACC 32
+// One candidate (position, radius, output column) seen by the observer at (xi, yi, zi) with unit director e: its weight goes
+// into the lane's private cone sums.  Shared by the two cone kernels below (cell-start layout and fixed-capacity layout).
+__device__ __forceinline__ void visw_candidate(double xm, double ym, double zm, double rm, int col, double xi, double yi, double zi,
+                                               double ex, double ey, double ez, double range, double half_angle, double cone_w,
+                                               int n_cones, int n_cols, const double *rim, const double *crim, double *sacc) {
+        if (col < 0) return;
+        double dx = xm - xi, dy = ym - yi, dz = zm - zi;
+        double d = sqrt(dx * dx + dy * dy + dz * dz);
+        if (!(d < range) || d == 0.0) return;
+        double w = 2.0 * rm / d;
+        if (w > 1.0) w = 1.0;
+        {
+          // fast cone decision: compare cos(angle) with the cosines of the rims instead of taking acos and
+          // normalising the separation twice.  Whenever the cosine lies within 1e-9 of a rim's (or the side
+          // test within 1e-9 of zero) the exact sequence below decides, so the chosen cone is always the one the
+          // serial kernel / the oracle choose; everywhere else the margin exceeds the rounding by six decades.
+          const double inv_d = 1.0 / d;
+          const double cf = (dx * ex + dy * ey + dz * ez) * inv_d;
+          const double of = (dx * (-ey) + dy * ex + dz * ez) * inv_d;
+          bool near = fabs(of) < 1e-9;
+          int tf = -1;
+          for (int t = 0; t < n_cones; ++t) {
+            const double r0 = rim[t], r1 = rim[t + 1], c0 = crim[t], c1 = crim[t + 1];
+            near = near || fabs(cf - c0) < 1e-9 || fabs(cf - c1) < 1e-9;
+            bool in;
+            if (of >= 0.0) in = (r0 < 0.0 || cf < c0) && (r1 > 0.0 && cf > c1);      // r0 < acos(c) < r1
+            else in = (r0 < 0.0 && cf > c0) && (r1 > 0.0 || cf < c1);               // r0 < -acos(c) < r1
+            if (in) tf = t;
+          }
+          if (!near) {
+            if (tf >= 0) sacc[(tf * n_cols + col) * VISW_THREADS + threadIdx.x] += w;
+            return;
+          }
+        }
+        double s0 = dx / d, s1 = dy / d, s2 = dz / d;
+        double sn = sqrt(s0 * s0 + s1 * s1 + s2 * s2);
+        s0 /= sn; s1 /= sn; s2 /= sn;
+        double c = s0 * ex + s1 * ey + s2 * ez;
+        c = fmin(1.0, fmax(-1.0, c));
+        double ang = acos(c);
+        double od = s0 * (-ey) + s1 * ex + s2 * ez;
+        if (!(od >= 0.0)) ang = -ang;
+        // the rims are evaluated exactly as in the serial kernel; only the candidate cone is guessed
+        int kc = (int)floor((ang + half_angle) / cone_w);
+        for (int t = kc - 1; t <= kc + 1; ++t) {
+          if (t < 0 || t >= n_cones) continue;
+          double lo = -half_angle + (double)t * half_angle * 2.0 / (double)n_cones;
+          double hi = -half_angle + (double)(t + 1) * half_angle * 2.0 / (double)n_cones;
+          if (lo < ang && hi > ang) sacc[(t * n_cols + col) * VISW_THREADS + threadIdx.x] += w;
+        }
+}
+
 template <int GS>
 __global__ void __launch_bounds__(VISW_THREADS) k_vis_cones_warp(long long n, const int *items, const int *row_of, const VisGrid *G,
                                                                   const int *start, const double *sx, const double *sy,
@@ -521,54 +573,223 @@ __global__ void __launch_bounds__(VISW_THREADS) k_vis_cones_warp(long long n, co
       const long long rowbase = ((long long)zz * G->nc[1] + yy) * G->nc[0];
       const int b = start[rowbase + x0], e = (row >= 0) ? start[rowbase + x1 + 1] : b;
       for (int m = b + lane; m < e; m += GS) {
-        const int col = __ldg(&scol[m]);
-        if (col < 0) continue;
-        double dx = __ldg(&sx[m]) - xi, dy = __ldg(&sy[m]) - yi, dz = __ldg(&sz[m]) - zi;
-        double d = sqrt(dx * dx + dy * dy + dz * dz);
-        if (!(d < range) || d == 0.0) continue;
-        double w = 2.0 * __ldg(&sr[m]) / d;
-        if (w > 1.0) w = 1.0;
-        {
-          // fast cone decision: compare cos(angle) with the cosines of the rims instead of taking acos and
-          // normalising the separation twice.  Whenever the cosine lies within 1e-9 of a rim's (or the side
-          // test within 1e-9 of zero) the exact sequence below decides, so the chosen cone is always the one the
-          // serial kernel / the oracle choose; everywhere else the margin exceeds the rounding by six decades.
-          const double inv_d = 1.0 / d;
-          const double cf = (dx * ex + dy * ey + dz * ez) * inv_d;
-          const double of = (dx * (-ey) + dy * ex + dz * ez) * inv_d;
-          bool near = fabs(of) < 1e-9;
-          int tf = -1;
-          for (int t = 0; t < n_cones; ++t) {
-            const double r0 = rim[t], r1 = rim[t + 1], c0 = crim[t], c1 = crim[t + 1];
-            near = near || fabs(cf - c0) < 1e-9 || fabs(cf - c1) < 1e-9;
-            bool in;
-            if (of >= 0.0) in = (r0 < 0.0 || cf < c0) && (r1 > 0.0 && cf > c1);      // r0 < acos(c) < r1
-            else in = (r0 < 0.0 && cf > c0) && (r1 > 0.0 || cf < c1);               // r0 < -acos(c) < r1
-            if (in) tf = t;
-          }
-          if (!near) {
-            if (tf >= 0) sacc[(tf * n_cols + col) * VISW_THREADS + threadIdx.x] += w;
-            continue;
-          }
-        }
-        double s0 = dx / d, s1 = dy / d, s2 = dz / d;
-        double sn = sqrt(s0 * s0 + s1 * s1 + s2 * s2);
-        s0 /= sn; s1 /= sn; s2 /= sn;
-        double c = s0 * ex + s1 * ey + s2 * ez;
-        c = fmin(1.0, fmax(-1.0, c));
-        double ang = acos(c);
-        double od = s0 * (-ey) + s1 * ex + s2 * ez;
-        if (!(od >= 0.0)) ang = -ang;
-        // the rims are evaluated exactly as in the serial kernel; only the candidate cone is guessed
-        int kc = (int)floor((ang + half_angle) / cone_w);
-        for (int t = kc - 1; t <= kc + 1; ++t) {
-          if (t < 0 || t >= n_cones) continue;
-          double lo = -half_angle + (double)t * half_angle * 2.0 / (double)n_cones;
-          double hi = -half_angle + (double)(t + 1) * half_angle * 2.0 / (double)n_cones;
-          if (lo < ang && hi > ang) sacc[(t * n_cols + col) * VISW_THREADS + threadIdx.x] += w;
-        }
+        visw_candidate(__ldg(&sx[m]), __ldg(&sy[m]), __ldg(&sz[m]), __ldg(&sr[m]), __ldg(&scol[m]), xi, yi, zi, ex, ey, ez, range, half_angle,
+                       cone_w, n_cones, n_cols, rim, crim, sacc);
       }
     }
+  __syncwarp();
+  for (int a = 0; a < nacc; ++a) {
+    double v = sacc[a * VISW_THREADS + threadIdx.x];
+#pragma unroll
+    for (int off = GS / 2; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+    if (lane == 0 && row >= 0) out[(long long)row * nacc + a] = v;
+  }
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// Vision-cone grid, second layout: FIXED CAPACITY per cell -- no histogram, no scan, no scatter.
+//   k_vis2_fill : cell of every particle on the grid of the PREVIOUS call's bounding box (widened by one range; any
+//                 box is correct, see VisPrev); slot = atomicAdd(count[cell]); the first VIS2_CAP ids of a cell go into
+//                 its slot row, the rest into one overflow list; the bounding box of THIS call is reduced on the side.
+//   k_vis2_pack : one warp per cell ranks the ids of its row (ascending id: a deterministic candidate order) and writes
+//                 the packed records {x, y, z, radius} + column in rank order.
+//   k_vis2_cones: as k_vis_cones_warp, walking the (up to) 27 slot rows, then the overflow list when it is not empty.
+// Three dependent launches instead of a cooperative kernel with five grid barriers (k_vis_build: 66 us at C4 against
+// ~20 us for these three; profiles/r02_launches_engine.csv).  The very first call has no previous box: it takes the
+// cell-start path once, which also leaves the box behind.
+// ---------------------------------------------------------------------------------------------
+#define VIS2_CAP 32
+struct Vis2Ovf { int n; int pad; };
+
+__global__ void k_vis2_grid(const VisPrev *prev, double range, long long ncell_max, VisGrid *G, VisBuild *B, Vis2Ovf *ovf) {
+  if (blockIdx.x != 0 || threadIdx.x != 0) return;
+  double ext[3];
+  for (int a = 0; a < 3; ++a) {
+    double lo = dec_double(~prev->mnc[a]), hi = dec_double(prev->mx[a]);
+    if (hi > lo || a < 2) { lo -= range; hi += range; }
+    if (!(hi >= lo)) { lo = 0.0; hi = 0.0; }
+    G->lo[a] = lo;
+    ext[a] = hi - lo;
+    B->mnc[a] = 0ULL; B->mx[a] = 0ULL;
+  }
+  double cs = range > 0.0 ? range : 1.0;
+  for (;;) {
+    long long tot = 1;
+    for (int a = 0; a < 3; ++a) {
+      double f = floor(ext[a] / cs) + 1.0;
+      int nc = (f > 1048576.0) ? 1048576 : (int)f;
+      if (nc < 1) nc = 1;
+      G->nc[a] = nc;
+      tot *= nc;
+      if (tot > ncell_max) break;
+    }
+    if (tot <= ncell_max) { G->ncell = (int)tot; break; }
+    cs *= 1.5;
+  }
+  G->cs = cs;
+  G->inv_cs = 1.0 / cs;
+  ovf->n = 0;
+}
+
+__global__ void __launch_bounds__(256) k_vis2_fill(long long n, const double *x, const double *y, const double *z, const VisGrid *G,
+                                                   int *count, int *ids, Vis2Ovf *ovf, int2 *ovf_items, VisBuild *B, double *out,
+                                                   long long out_len) {
+  __shared__ unsigned long long smn[3][8], smx[3][8];
+  const long long gtid = (long long)blockIdx.x * blockDim.x + threadIdx.x, gsz = (long long)gridDim.x * blockDim.x;
+  for (long long i = gtid; i < out_len; i += gsz) out[i] = 0.0;
+  unsigned long long mn[3] = {0ULL, 0ULL, 0ULL}, mx[3] = {0ULL, 0ULL, 0ULL};
+  for (long long i = gtid; i < n; i += gsz) {
+    const double xi = x[i], yi = y[i], zi = z[i];
+    const unsigned long long e[3] = {enc_double(xi), enc_double(yi), enc_double(zi)};
+#pragma unroll
+    for (int a = 0; a < 3; ++a) { mn[a] = max(mn[a], ~e[a]); mx[a] = max(mx[a], e[a]); }
+    const int cx = vis_coord(xi, G->lo[0], G->inv_cs, G->nc[0]);
+    const int cy = vis_coord(yi, G->lo[1], G->inv_cs, G->nc[1]);
+    const int cz = vis_coord(zi, G->lo[2], G->inv_cs, G->nc[2]);
+    const int c = (cz * G->nc[1] + cy) * G->nc[0] + cx;
+    const int p = atomicAdd(&count[c], 1);
+    if (p < VIS2_CAP) ids[(long long)c * VIS2_CAP + p] = (int)i;
+    else { const int q = atomicAdd(&ovf->n, 1); ovf_items[q] = make_int2(c, (int)i); }
+  }
+#pragma unroll
+  for (int a = 0; a < 3; ++a)
+    for (int o = 16; o > 0; o >>= 1) {
+      mn[a] = max(mn[a], __shfl_xor_sync(0xffffffffu, mn[a], o));
+      mx[a] = max(mx[a], __shfl_xor_sync(0xffffffffu, mx[a], o));
+    }
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  if (l == 0)
+    for (int a = 0; a < 3; ++a) { smn[a][w] = mn[a]; smx[a][w] = mx[a]; }
+  __syncthreads();
+  if (threadIdx.x < 3) {
+    const int a = threadIdx.x;
+    unsigned long long m0 = 0ULL, m1 = 0ULL;
+    for (int k = 0; k < 8; ++k) { m0 = max(m0, smn[a][k]); m1 = max(m1, smx[a][k]); }
+    atomicMax(&B->mnc[a], m0);
+    atomicMax(&B->mx[a], m1);
+  }
+}
+
+// first call of a swarm: no previous box yet -- the box of the current positions
+__global__ void __launch_bounds__(256) k_vis2_bbox(long long n, const double *x, const double *y, const double *z, VisPrev *prev) {
+  __shared__ unsigned long long smn[3][8], smx[3][8];
+  const long long gtid = (long long)blockIdx.x * blockDim.x + threadIdx.x, gsz = (long long)gridDim.x * blockDim.x;
+  unsigned long long mn[3] = {0ULL, 0ULL, 0ULL}, mx[3] = {0ULL, 0ULL, 0ULL};
+  for (long long i = gtid; i < n; i += gsz) {
+    const unsigned long long e[3] = {enc_double(x[i]), enc_double(y[i]), enc_double(z[i])};
+#pragma unroll
+    for (int a = 0; a < 3; ++a) { mn[a] = max(mn[a], ~e[a]); mx[a] = max(mx[a], e[a]); }
+  }
+#pragma unroll
+  for (int a = 0; a < 3; ++a)
+    for (int o = 16; o > 0; o >>= 1) {
+      mn[a] = max(mn[a], __shfl_xor_sync(0xffffffffu, mn[a], o));
+      mx[a] = max(mx[a], __shfl_xor_sync(0xffffffffu, mx[a], o));
+    }
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  if (l == 0)
+    for (int a = 0; a < 3; ++a) { smn[a][w] = mn[a]; smx[a][w] = mx[a]; }
+  __syncthreads();
+  if (threadIdx.x < 3) {
+    const int a = threadIdx.x;
+    unsigned long long m0 = 0ULL, m1 = 0ULL;
+    for (int k = 0; k < 8; ++k) { m0 = max(m0, smn[a][k]); m1 = max(m1, smx[a][k]); }
+    atomicMax(&prev->mnc[a], m0);
+    atomicMax(&prev->mx[a], m1);
+  }
+}
+
+// one warp per cell
+__global__ void __launch_bounds__(256) k_vis2_pack(const VisGrid *G, const int *count, const int *ids, const double *x, const double *y,
+                                                   const double *z, const double *radii, const int *species, const __grid_constant__ DevParams P,
+                                                   const int *type_col, int n_type_col, double4 *rec, int *rcol, const VisBuild *B,
+                                                   VisPrev *prev) {
+  const long long gw = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (gw == 0 && lane < 3) { prev->mnc[lane] = B->mnc[lane]; prev->mx[lane] = B->mx[lane]; }   // the box for the next call
+  if (gw >= G->ncell) return;
+  int m = count[gw];
+  if (m == 0) return;
+  if (m > VIS2_CAP) m = VIS2_CAP;
+  const int id = (lane < m) ? ids[gw * VIS2_CAP + lane] : 0x7fffffff;
+  int rank = 0;
+#pragma unroll
+  for (int q = 0; q < 32; ++q) rank += (__shfl_sync(0xffffffffu, id, q) < id) ? 1 : 0;
+  if (lane < m) {
+    const long long o = gw * VIS2_CAP + rank;
+    rec[o] = make_double4(x[id], y[id], z[id], radii[id]);
+    const int t = P.sp_type[species[id]];
+    rcol[o] = (t >= 0 && t < n_type_col) ? type_col[t] : -1;
+  }
+}
+
+template <int GS>
+__global__ void __launch_bounds__(VISW_THREADS) k_vis2_cones(long long n, const int *row_of, const VisGrid *G, const int *count,
+                                                             const double4 *rec, const int *rcol, const Vis2Ovf *ovf, const int2 *ovf_items,
+                                                             const double *x, const double *y, const double *z, const double *radii,
+                                                             const int *species, const __grid_constant__ DevParams P, const int *type_col,
+                                                             int n_type_col, int n_dims, const double *theta, const double *q0,
+                                                             const double *q1, const double *q2, const double *q3, const double *dirs,
+                                                             double range, double half_angle, int n_cones, int n_cols, double *out) {
+  extern __shared__ double sacc[];   // [nacc][VISW_THREADS]
+  const int lane = threadIdx.x & (GS - 1);
+  long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) / GS;
+  const bool in_range = i < n;
+  if (!in_range) i = n - 1;
+  const int row = in_range ? row_of[i] : -1;
+  const int nacc = n_cones * n_cols;
+  for (int a = 0; a < nacc; ++a) sacc[a * VISW_THREADS + threadIdx.x] = 0.0;
+  const double xi = x[i], yi = y[i], zi = z[i];
+  double ex, ey, ez;
+  if (dirs) { ex = dirs[i]; ey = dirs[n + i]; ez = dirs[2 * n + i]; }
+  else if (n_dims == 2) { sincos(theta[i], &ey, &ex); ez = 0.0; }
+  else {
+    double a = q0[i], b = q1[i], c = q2[i], d = q3[i];
+    ex = 2 * (b * d + a * c); ey = 2 * (c * d - a * b); ez = a * a - b * b - c * c + d * d;
+  }
+  {
+    double en = sqrt(ex * ex + ey * ey + ez * ez);
+    ex /= en; ey /= en; ez /= en;
+  }
+  const double cone_w = half_angle * 2.0 / (double)n_cones;
+  __shared__ double rim[VIS_MAX_ACC + 1], crim[VIS_MAX_ACC + 1];
+  for (int t = threadIdx.x; t <= n_cones; t += blockDim.x) {
+    rim[t] = -half_angle + (double)t * half_angle * 2.0 / (double)n_cones;
+    crim[t] = cos(rim[t]);
+  }
+  __syncthreads();
+  const int cx = vis_coord(xi, G->lo[0], G->inv_cs, G->nc[0]);
+  const int cy = vis_coord(yi, G->lo[1], G->inv_cs, G->nc[1]);
+  const int cz = vis_coord(zi, G->lo[2], G->inv_cs, G->nc[2]);
+  if (row >= 0) {
+    for (int zz = max(cz - 1, 0); zz <= min(cz + 1, G->nc[2] - 1); ++zz)
+      for (int yy = max(cy - 1, 0); yy <= min(cy + 1, G->nc[1] - 1); ++yy)
+        for (int xx = max(cx - 1, 0); xx <= min(cx + 1, G->nc[0] - 1); ++xx) {
+          const long long c = ((long long)zz * G->nc[1] + yy) * G->nc[0] + xx;
+          int m = __ldg(&count[c]);
+          if (m > VIS2_CAP) m = VIS2_CAP;
+          for (int k = lane; k < m; k += GS) {
+            const long long o = c * VIS2_CAP + k;
+            const double2 r01 = __ldg(reinterpret_cast<const double2 *>(&rec[o]));
+            const double2 r23 = __ldg(reinterpret_cast<const double2 *>(&rec[o]) + 1);
+            visw_candidate(r01.x, r01.y, r23.x, r23.y, __ldg(&rcol[o]), xi, yi, zi, ex, ey, ez, range, half_angle, cone_w, n_cones, n_cols,
+                           rim, crim, sacc);
+          }
+        }
+    // particles beyond the capacity of their cell (dense clusters): one list, scanned by every observer that has such a
+    // cell in its neighbourhood -- empty in all but pathological packings
+    const int no = ovf->n;
+    for (int k = lane; k < no; k += GS) {
+      const int2 it = ovf_items[k];
+      const int ox = it.x % G->nc[0], oy = (it.x / G->nc[0]) % G->nc[1], oz = it.x / (G->nc[0] * G->nc[1]);
+      if (abs(ox - cx) > 1 || abs(oy - cy) > 1 || abs(oz - cz) > 1) continue;
+      const int j = it.y;
+      const int t = P.sp_type[species[j]];
+      const int col = (t >= 0 && t < n_type_col) ? type_col[t] : -1;
+      visw_candidate(x[j], y[j], z[j], radii[j], col, xi, yi, zi, ex, ey, ez, range, half_angle, cone_w, n_cones, n_cols, rim, crim, sacc);
+    }
+  }
   __syncwarp();
   for (int a = 0; a < nacc; ++a) {
     double v = sacc[a * VISW_THREADS + threadIdx.x];
@@ -837,6 +1058,12 @@ extern "C" int swarm_obs_vision(swarm_t *s, const int32_t *row_of, int64_t rows,
   size_t o_cell = carve(sizeof(int) * (size_t)n), o_items = carve(sizeof(int) * (size_t)n), o_col = carve(sizeof(int) * (size_t)n);
   size_t o_sx = carve(sizeof(double) * (size_t)n), o_sy = carve(sizeof(double) * (size_t)n);
   size_t o_sz = carve(sizeof(double) * (size_t)n), o_sr = carve(sizeof(double) * (size_t)n);
+  // fixed-capacity layout (k_vis2_*): at most n / 2 cells of VIS2_CAP slots
+  long long ncell2 = n / 2;
+  if (ncell2 < 4096) ncell2 = 4096;
+  if (ncell2 > (1LL << 20)) ncell2 = (1LL << 20);
+  size_t o_ids2 = carve(sizeof(int) * (size_t)ncell2 * VIS2_CAP), o_rcol2 = carve(sizeof(int) * (size_t)ncell2 * VIS2_CAP);
+  size_t o_rec2 = carve(sizeof(double4) * (size_t)ncell2 * VIS2_CAP), o_ovf = carve(sizeof(Vis2Ovf)), o_ovfi = carve(sizeof(int2) * (size_t)n);
   if (s->vis_bytes < off) {
     if (s->vis_buf) cudaFree(s->vis_buf);
     s->vis_buf = nullptr; s->vis_bytes = 0;
@@ -853,6 +1080,33 @@ extern "C" int swarm_obs_vision(swarm_t *s, const int32_t *row_of, int64_t rows,
   const int T = 256, B = sw_blocks(n, T);
   const int gb = B < 4 * s->num_sms ? B : 4 * s->num_sms;
   const long long out_len = (long long)rows * n_cones * n_cols;
+  if (n_cones * n_cols <= VISW_MAX_ACC && !getenv("SWARM_B200_VIS_V1") && !getenv("SWARM_B200_VIS_SERIAL")) {
+    // ---- fixed-capacity layout on the previous call's bounding box: memset, grid, fill, pack, cones -------------------
+    VisBuild *VB = (VisBuild *)(base + o_build);
+    VisPrev *VP = (VisPrev *)(base + o_prev);
+    if (!(s->vis_prev_n == n && s->vis_prev_range == vision_range)) {
+      SW_CUDA(cudaMemsetAsync(VP, 0, sizeof(VisPrev), st));
+      k_vis2_bbox<<<gb > 0 ? gb : 1, T, 0, st>>>(n, A.x[0], A.y[0], A.z[0], VP);
+      s->launches += 1;
+      s->vis_prev_n = n; s->vis_prev_range = vision_range;
+    }
+    int *ids2 = (int *)(base + o_ids2), *rcol2 = (int *)(base + o_rcol2);
+    double4 *rec2 = (double4 *)(base + o_rec2);
+    Vis2Ovf *ovf = (Vis2Ovf *)(base + o_ovf);
+    int2 *ovfi = (int2 *)(base + o_ovfi);
+    SW_CUDA(cudaMemsetAsync(count, 0, sizeof(int) * (size_t)(ncell2 + 1), st));
+    k_vis2_grid<<<1, 32, 0, st>>>(VP, vision_range, ncell2, G, VB, ovf);
+    k_vis2_fill<<<gb > 0 ? gb : 1, T, 0, st>>>(n, A.x[0], A.y[0], A.z[0], G, count, ids2, ovf, ovfi, VB, out, out_len);
+    k_vis2_pack<<<sw_blocks(ncell2 * 32, T), T, 0, st>>>(G, count, ids2, A.x[0], A.y[0], A.z[0], radii, A.species, s->P, type_col, n_type_col,
+                                                        rec2, rcol2, VB, VP);
+    const size_t smem = sizeof(double) * (size_t)(n_cones * n_cols) * VISW_THREADS;
+    k_vis2_cones<4><<<sw_blocks(n * 4, VISW_THREADS), VISW_THREADS, smem, st>>>(
+        n, row_of, G, count, rec2, rcol2, ovf, ovfi, A.x[0], A.y[0], A.z[0], radii, A.species, s->P, type_col, n_type_col, s->P.n_dims,
+        A.theta, A.q0, A.q1, A.q2, A.q3, dirs, vision_range, half_angle, n_cones, n_cols, out);
+    s->launches += 4;
+    SW_CUDA(cudaGetLastError());
+    return SWARM_OK;
+  }
   bool fused = s->persistent && !getenv("SWARM_B200_VIS_UNFUSED");
   int bpsm = 0;
   if (fused) {

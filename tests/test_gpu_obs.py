@@ -283,3 +283,38 @@ def test_fp32_reference_bounds(golden):
     ref = oracle.field_delta_f32(now[sel], prev[sel], src, 1, 1.0, -1.0, scale, False).astype(np.float64)
     tol = 8 * 2.0 ** -24 * scale * (1.0 + 1.0 * 3.0)
     assert np.max(np.abs(got.cpu().numpy() - ref)) <= tol
+
+
+def test_vision_fixed_capacity_layout_second_call_moved_particles_and_overflow():
+    """The vision grid (k_vis2_*: fixed capacity per cell) is laid over the bounding box of the PREVIOUS call -- the first
+    call of a swarm measures its own.  Same answers as the oracle, call after call (bit-identical while nothing moves),
+    also after particles have left the previous box by more than a range (they are clamped into edge cells) and with
+    more particles in one cell than its capacity (overflow list)."""
+    import torch
+
+    (o, d), rng = _pair(n=3000, L=300.0)
+    n = o.n
+    radii = np.ones(n)
+    rd = torch.from_numpy(radii).to(d.dev)
+    tc = torch.from_numpy(np.array([0, 1], dtype=np.int32)).to(d.dev)
+    row_of, rows = d.row_map(0)
+
+    def both():
+        got = d.obs_vision(row_of, rows, 12.0, np.pi / 2, 5, rd, tc, 2).cpu().numpy()
+        ref = o.vision_cones(0, 12.0, np.pi / 2, 5, radii, [0, 1])
+        assert np.max(np.abs(got - ref)) < 1e-11
+        return got
+
+    first = both()                    # box of the current positions
+    second = both()                   # box of the previous call
+    assert np.array_equal(first, second)
+    assert d.stats().launches > 0
+    # move: a block of particles far outside the previous box, a dense clump of 120 inside one cell
+    shift = np.zeros((n, 3)); shift[:40, 0] = 80.0; shift[40:80, 1] = -95.0
+    clump = np.arange(200, 320)
+    newpos = o.pos + shift
+    newpos[clump, :2] = np.array([150.0, 150.0]) + rng.uniform(-3.0, 3.0, (len(clump), 2))
+    o.x[:], o.y[:] = newpos[:, 0], newpos[:, 1]
+    d.pos[:2, :n] = torch.from_numpy(np.ascontiguousarray(newpos[:, :2].T)).to(d.dev)
+    both()
+    both()                            # and once more on the box of the moved swarm
