@@ -152,6 +152,7 @@ class DomainSwarm:
         self.n_owned = 0
         self.since_exchange = 0
         self.exchanges = 0
+        self._deferred_sums = []   # per-slice reward sums of this rank awaiting reward_means()
         self.cur = 0
         # profile = True brackets every phase with CUDA events (asynchronous, no host sync): `timeline()` then tells
         # how a slice splits into integration, exchange (pack + transport + merge, i.e. including the wait for the
@@ -351,9 +352,14 @@ class DomainSwarm:
         o = np.argsort(gid, kind="stable")
         return gid[o], xg[o], y[o], th[o]
 
-    def field_reward(self, src, box_length, decay=_lib.DECAY_LINEAR, c0=1.0, c1=-1.0, scale=1.0, clip=True, init_only=False):
+    def field_reward(self, src, box_length, decay=_lib.DECAY_LINEAR, c0=1.0, c1=-1.0, scale=1.0, clip=True, init_only=False,
+                     defer=False):
         """GradientSensing reward (tasks/searching/gradient_sensing.py:92-150) of the owned particles and
-        its global mean (trainers/trainer.py:92-95): returns (per-slot rewards, device tensor [sum, mean])."""
+        its global mean (trainers/trainer.py:92-95): returns (per-slot rewards, device tensor [sum, mean]).
+
+        defer=True keeps this rank's sum on the device and returns (per-slot rewards, None): the reference takes the
+        mean of an EPISODE's rewards after the episode (trainer.py:92-95), so the ranks need not meet in an all-reduce
+        after every slice -- `reward_means()` reduces all deferred sums in one collective."""
         torch = self.torch
         if self.n_aux < 2:
             raise ValueError("the field history needs n_aux >= 2")
@@ -366,8 +372,23 @@ class DomainSwarm:
                                                    int(bool(init_only)), self.out.data_ptr(), self._stream()))
             red = self.sw.reduce_mean(self.out)      # slots past the live count were written as 0
             tot = red[:1].clone()
+            if defer:
+                self._deferred_sums.append(tot)
+                return self.out, None
             self.transport.all_reduce_sum(tot)
         return self.out, torch.cat([tot, tot / float(self.n_global)])
+
+    def reward_means(self):
+        """Global reward mean of every slice evaluated with defer=True since the last call: ONE all-reduce of the vector
+        of per-slice sums.  Returns a device tensor (n_slices,)."""
+        torch = self.torch
+        if not self._deferred_sums:
+            return torch.zeros(0, dtype=torch.float64, device=self.dev)
+        v = torch.cat(self._deferred_sums)
+        self._deferred_sums = []
+        with self._timed("obs"):
+            self.transport.all_reduce_sum(v)
+        return v / float(self.n_global)
 
     def close(self):
         self.sw.close()

@@ -76,8 +76,7 @@ def _make(world, rank, local, group, swarm, k, skin, margin, capf, kT, profile=F
 def _slice(d, f_glob, t_glob, L, steps, step0):
     d.set_actions_global(f_glob, t_glob)
     d.run(steps, step0)
-    _, red = d.field_reward(SRC, (L, L), scale=10.0)
-    return red
+    d.field_reward(SRC, (L, L), scale=10.0, defer=True)   # the reward MEAN is taken once per measurement (one all-reduce)
 
 
 def measure(world, rank, local, swarm, *, steps=100, slices=5, warmup=2, k=33, skin=2.0, margin=0.15, capf=1.3,
@@ -106,9 +105,12 @@ def measure(world, rank, local, swarm, *, steps=100, slices=5, warmup=2, k=33, s
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     ev0.record()
+    d.reward_means()
     for _ in range(slices):
-        red = _slice(d, f_glob, t_glob, L, steps, step)
+        _slice(d, f_glob, t_glob, L, steps, step)
         step += steps
+    means = d.reward_means()    # inside the timed region: the collective of the measurement
+    red = torch.stack([means[-1] * float(d.n_global), means[-1]])
     ev1.record()
     barrier()
     st = d.stats()   # raises on a Verlet or exchange-buffer overflow
@@ -194,9 +196,9 @@ def parity_selfcheck(world, rank, local, *, n=20000, steps=61, slices=2, k=4, sk
     step = 0
     means = []
     for _ in range(slices):
-        red = _slice(d, f_glob, t_glob, L, steps, step)
-        means.append(float(red[1]))
+        _slice(d, f_glob, t_glob, L, steps, step)
         step += steps
+    means = [float(v) for v in d.reward_means().cpu()]
     d.stats()
     full, owned_total = gather_owned(d, world, rank, group)
     ex = d.exchanges
