@@ -295,6 +295,13 @@ int swarm_obs_position(swarm_t *s, const int32_t *row_of_dev, const double box_l
  * Deterministic two-stage reduction. */
 int swarm_reduce_mean(swarm_t *s, const double *in_dev, int64_t n, double *out2_dev, void *stream);
 
+/* swarm_obs_field (closed-form decay, rewards into out_dev) and swarm_reduce_mean over its n_rows rewards in ONE launch:
+ * GradientSensing.__call__ (tasks/searching/gradient_sensing.py:140-183) followed by the trainer's np.mean
+ * (trainers/trainer.py:92-95).  out2_dev[0] = sum, out2_dev[1] = sum / n_rows; fixed summation order. */
+int swarm_obs_field_mean(swarm_t *s, const int32_t *row_of_dev, int64_t n_rows, const double src[3],
+                         const double box_length[3], double *hist_dev, int32_t decay, double c0, double c1, double scale,
+                         int32_t clip, double *out_dev, double *out2_dev, void *stream);
+
 /* ---- fused policy forward ----------------------------------------------------
  * ActorCriticAgent.calc_action (agents/actor_critic.py:159-184) -> FlaxModel.compute_action
  * (networks/flax_network.py:153-195) -> GumbelDistribution (sampling_strategies/gumbel_distribution.py:

@@ -255,12 +255,14 @@ class DeviceAgent(Agent):
             self.trajectory.killed = self.task.kill_switch
 
     def calc_reward_device(self, view, particle_type=None, external_reward: float = 0.0):
-        rewards = self.task.call_device(view)
+        fused = self.reward_mean and not external_reward and getattr(self.task, "fused_mean", False)
+        rewards = self.task.call_device(view, want_mean=True) if fused else self.task.call_device(view)
         if external_reward:
             rewards = rewards + external_reward
         self.last_rewards = rewards
         if self.reward_mean:
-            self.reward_means.append(view.swarm.reduce_mean(rewards))
+            red = self.task.last_mean if fused else None
+            self.reward_means.append(red if red is not None else view.swarm.reduce_mean(rewards))
         if self.train and self.keep_trajectory:
             self.trajectory.rewards.append(rewards)
         self.kill_switch = self.task.kill_switch

@@ -143,6 +143,8 @@ struct swarm {
   void *obs_scratch = nullptr;
   size_t obs_scratch_bytes = 0;
   double *red_scratch = nullptr;
+  double *field_scratch = nullptr;   // per-CTA reward sums + ticket of swarm_obs_field_mean
+  int field_scratch_blocks = 0;
   void *vis_buf = nullptr;   // vision-cone cell structure + packed copies
   size_t vis_bytes = 0;
   long long vis_prev_n = -1;   // the bounding box of the previous vision call is usable for this n / range

@@ -854,6 +854,7 @@ extern "C" int swarm_destroy(swarm_t *s) {
   if (s->ctl_host) cudaFreeHost(s->ctl_host);
   if (s->obs_scratch) cudaFree(s->obs_scratch);
   if (s->red_scratch) cudaFree(s->red_scratch);
+  if (s->field_scratch) cudaFree(s->field_scratch);
   if (s->vis_buf) cudaFree(s->vis_buf);
   delete s;
   return SWARM_OK;

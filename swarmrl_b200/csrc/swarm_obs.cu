@@ -602,8 +602,9 @@ __global__ void __launch_bounds__(VISW_THREADS) k_vis_cones_warp(long long n, co
 #define VIS2_CAP 32
 struct Vis2Ovf { int n; int pad; };
 
-__global__ void k_vis2_grid(const VisPrev *prev, double range, long long ncell_max, VisGrid *G, VisBuild *B, Vis2Ovf *ovf) {
-  if (blockIdx.x != 0 || threadIdx.x != 0) return;
+// Grid over the previous call's box: a few dozen flops, so every CTA of k_vis2_fill derives it for itself (thread 0,
+// shared memory) and CTA 0 leaves the copy k_vis2_pack / k_vis2_cones read -- no launch of its own.
+__device__ void vis2_make_grid(const VisPrev *prev, double range, long long ncell_max, VisGrid *G) {
   double ext[3];
   for (int a = 0; a < 3; ++a) {
     double lo = dec_double(~prev->mnc[a]), hi = dec_double(prev->mx[a]);
@@ -611,7 +612,7 @@ __global__ void k_vis2_grid(const VisPrev *prev, double range, long long ncell_m
     if (!(hi >= lo)) { lo = 0.0; hi = 0.0; }
     G->lo[a] = lo;
     ext[a] = hi - lo;
-    B->mnc[a] = 0ULL; B->mx[a] = 0ULL;
+    G->mn[a] = 0ULL; G->mx[a] = 0ULL;
   }
   double cs = range > 0.0 ? range : 1.0;
   for (;;) {
@@ -629,13 +630,20 @@ __global__ void k_vis2_grid(const VisPrev *prev, double range, long long ncell_m
   }
   G->cs = cs;
   G->inv_cs = 1.0 / cs;
-  ovf->n = 0;
 }
 
-__global__ void __launch_bounds__(256) k_vis2_fill(long long n, const double *x, const double *y, const double *z, const VisGrid *G,
+__global__ void __launch_bounds__(256) k_vis2_fill(long long n, const double *x, const double *y, const double *z,
+                                                   const VisPrev *prev, double range, long long ncell_max, VisGrid *Gout,
                                                    int *count, int *ids, Vis2Ovf *ovf, int2 *ovf_items, VisBuild *B, double *out,
                                                    long long out_len) {
   __shared__ unsigned long long smn[3][8], smx[3][8];
+  __shared__ VisGrid sG;
+  if (threadIdx.x == 0) {
+    vis2_make_grid(prev, range, ncell_max, &sG);
+    if (blockIdx.x == 0) *Gout = sG;
+  }
+  __syncthreads();
+  const VisGrid *G = &sG;
   const long long gtid = (long long)blockIdx.x * blockDim.x + threadIdx.x, gsz = (long long)gridDim.x * blockDim.x;
   for (long long i = gtid; i < out_len; i += gsz) out[i] = 0.0;
   unsigned long long mn[3] = {0ULL, 0ULL, 0ULL}, mx[3] = {0ULL, 0ULL, 0ULL};
@@ -809,24 +817,60 @@ __device__ __forceinline__ double decay_eval(int kind, double c0, double c1, dou
   }
 }
 
-__global__ void k_obs_field(long long n, const double *x, const double *y, const double *z, const int *row_of,
-                            double s0, double s1, double s2, double b0, double b1, double b2, double *hist, int decay,
-                            double c0, double c1, double scale, int clip, double *out, double *d_now, double *d_prev) {
-  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  int row = row_of ? row_of[i] : (int)i;
-  if (row < 0) return;
-  double p0 = x[i] / b0, p1 = y[i] / b1, p2 = z[i] / b2;
-  double h0 = hist[i], h1 = hist[n + i], h2 = hist[2 * n + i];
-  double dn = sqrt((s0 - p0) * (s0 - p0) + (s1 - p1) * (s1 - p1) + (s2 - p2) * (s2 - p2));
-  double dp = sqrt((s0 - h0) * (s0 - h0) + (s1 - h1) * (s1 - h1) + (s2 - h2) * (s2 - h2));
-  hist[i] = p0; hist[n + i] = p1; hist[2 * n + i] = p2;
-  if (d_now) d_now[row] = dn;
-  if (d_prev) d_prev[row] = dp;
-  if (out && decay != SWARM_DECAY_NONE) {
-    double v = scale * (decay_eval(decay, c0, c1, dn) - decay_eval(decay, c0, c1, dp));
-    if (clip && !(v > 0.0)) v = 0.0;
-    out[row] = v;
+// `partial` != nullptr: the launch also leaves (sum, mean over n_rows) of the written rewards in out2 -- every CTA adds
+// its 256 values in a fixed tree, the CTA that draws the last ticket adds the per-CTA sums in a fixed order (the
+// reference takes the mean on the host, trainers/trainer.py:92-95; here reward and mean are one launch).
+__global__ void __launch_bounds__(256) k_obs_field(long long n, const double *x, const double *y, const double *z, const int *row_of,
+                                                   double s0, double s1, double s2, double b0, double b1, double b2, double *hist,
+                                                   int decay, double c0, double c1, double scale, int clip, double *out,
+                                                   double *d_now, double *d_prev, double *partial, unsigned int *ticket,
+                                                   double *out2, long long n_rows) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int row = (i < n) ? (row_of ? row_of[i] : (int)i) : -1;
+  double v = 0.0;
+  if (row >= 0) {
+    double p0 = x[i] / b0, p1 = y[i] / b1, p2 = z[i] / b2;
+    double h0 = hist[i], h1 = hist[n + i], h2 = hist[2 * n + i];
+    double dn = sqrt((s0 - p0) * (s0 - p0) + (s1 - p1) * (s1 - p1) + (s2 - p2) * (s2 - p2));
+    double dp = sqrt((s0 - h0) * (s0 - h0) + (s1 - h1) * (s1 - h1) + (s2 - h2) * (s2 - h2));
+    hist[i] = p0; hist[n + i] = p1; hist[2 * n + i] = p2;
+    if (d_now) d_now[row] = dn;
+    if (d_prev) d_prev[row] = dp;
+    if (out && decay != SWARM_DECAY_NONE) {
+      v = scale * (decay_eval(decay, c0, c1, dn) - decay_eval(decay, c0, c1, dp));
+      if (clip && !(v > 0.0)) v = 0.0;
+      out[row] = v;
+    }
+  }
+  if (!partial) return;
+  __shared__ double ws[8];
+  __shared__ bool last;
+  double sum = v;
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = sum;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    for (int k = 0; k < 8; ++k) t += ws[k];
+    partial[blockIdx.x] = t;
+    __threadfence();
+    last = (atomicAdd(ticket, 1u) == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!last) return;
+  __threadfence();
+  double t = 0.0;
+  for (long long k = threadIdx.x; k < (long long)gridDim.x; k += 256) t += __ldcg(&partial[k]);
+  for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = t;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double tot = 0.0;
+    for (int k = 0; k < 8; ++k) tot += ws[k];
+    out2[0] = tot;
+    out2[1] = (n_rows > 0) ? tot / (double)n_rows : 0.0;
+    *ticket = 0u;
   }
 }
 
@@ -962,20 +1006,48 @@ __global__ void k_reduce_final(long long n, const double *partial, double *out2)
 // ---------------------------------------------------------------------------------------------
 static inline size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
 
-extern "C" int swarm_obs_field(swarm_t *s, const int32_t *row_of, const double src[3], const double box_length[3],
-                               double *hist, int32_t decay, double c0, double c1, double scale, int32_t clip,
-                               double *out, double *d_now, double *d_prev, void *stream) {
+static int sw_obs_field_launch(swarm_t *s, const int32_t *row_of, const double src[3], const double box_length[3], double *hist,
+                               int32_t decay, double c0, double c1, double scale, int32_t clip, double *out, double *d_now,
+                               double *d_prev, double *out2, int64_t n_rows, void *stream) {
   if (!s || !s->state_bound || !src || !box_length || !hist) { sw_set_error("bad arguments"); return SWARM_ERR_INVALID; }
   if (decay < SWARM_DECAY_NONE || decay > SWARM_DECAY_INVERSE) { sw_set_error("unknown decay kind"); return SWARM_ERR_INVALID; }
   SW_CUDA(cudaSetDevice(s->cfg.device));
   const DevArrays &A = s->A;
   if (A.n == 0) return SWARM_OK;
-  k_obs_field<<<sw_blocks(A.n, 256), 256, 0, (cudaStream_t)stream>>>(A.n, A.x[0], A.y[0], A.z[0], row_of, src[0], src[1], src[2],
-                                                                     box_length[0], box_length[1], box_length[2], hist, decay,
-                                                                     c0, c1, scale, clip, out, d_now, d_prev);
+  const int blocks = sw_blocks(A.n, 256);
+  double *partial = nullptr;
+  unsigned int *ticket = nullptr;
+  if (out2) {
+    if (!out || decay == SWARM_DECAY_NONE) { sw_set_error("the mean needs a closed-form decay and a reward array"); return SWARM_ERR_INVALID; }
+    if (s->field_scratch_blocks < blocks) {
+      if (s->field_scratch) cudaFree(s->field_scratch);
+      s->field_scratch = nullptr; s->field_scratch_blocks = 0;
+      SW_CUDA(cudaMalloc((void **)&s->field_scratch, sizeof(double) * ((size_t)blocks + 1)));
+      SW_CUDA(cudaMemset(s->field_scratch, 0, sizeof(double) * ((size_t)blocks + 1)));   // [blocks]: the ticket
+      s->field_scratch_blocks = blocks;
+    }
+    partial = s->field_scratch;
+    ticket = (unsigned int *)(s->field_scratch + s->field_scratch_blocks);
+  }
+  k_obs_field<<<blocks, 256, 0, (cudaStream_t)stream>>>(A.n, A.x[0], A.y[0], A.z[0], row_of, src[0], src[1], src[2], box_length[0],
+                                                        box_length[1], box_length[2], hist, decay, c0, c1, scale, clip, out, d_now,
+                                                        d_prev, partial, ticket, out2, (long long)n_rows);
   s->launches += 1;
   SW_CUDA(cudaGetLastError());
   return SWARM_OK;
+}
+
+extern "C" int swarm_obs_field(swarm_t *s, const int32_t *row_of, const double src[3], const double box_length[3],
+                               double *hist, int32_t decay, double c0, double c1, double scale, int32_t clip,
+                               double *out, double *d_now, double *d_prev, void *stream) {
+  return sw_obs_field_launch(s, row_of, src, box_length, hist, decay, c0, c1, scale, clip, out, d_now, d_prev, nullptr, 0, stream);
+}
+
+extern "C" int swarm_obs_field_mean(swarm_t *s, const int32_t *row_of, int64_t n_rows, const double src[3],
+                                    const double box_length[3], double *hist, int32_t decay, double c0, double c1, double scale,
+                                    int32_t clip, double *out, double *out2, void *stream) {
+  if (!out2 || n_rows < 0) { sw_set_error("bad arguments"); return SWARM_ERR_INVALID; }
+  return sw_obs_field_launch(s, row_of, src, box_length, hist, decay, c0, c1, scale, clip, out, nullptr, nullptr, out2, n_rows, stream);
 }
 
 extern "C" int swarm_obs_pair_field(swarm_t *s, const int32_t *row_of, const int32_t *sensed_idx, int64_t n_sensed,
@@ -1081,7 +1153,7 @@ extern "C" int swarm_obs_vision(swarm_t *s, const int32_t *row_of, int64_t rows,
   const int gb = B < 4 * s->num_sms ? B : 4 * s->num_sms;
   const long long out_len = (long long)rows * n_cones * n_cols;
   if (n_cones * n_cols <= VISW_MAX_ACC && !getenv("SWARM_B200_VIS_V1") && !getenv("SWARM_B200_VIS_SERIAL")) {
-    // ---- fixed-capacity layout on the previous call's bounding box: memset, grid, fill, pack, cones -------------------
+    // ---- fixed-capacity layout on the previous call's bounding box: memset, fill, pack, cones -------------------
     VisBuild *VB = (VisBuild *)(base + o_build);
     VisPrev *VP = (VisPrev *)(base + o_prev);
     if (!(s->vis_prev_n == n && s->vis_prev_range == vision_range)) {
@@ -1092,18 +1164,19 @@ extern "C" int swarm_obs_vision(swarm_t *s, const int32_t *row_of, int64_t rows,
     }
     int *ids2 = (int *)(base + o_ids2), *rcol2 = (int *)(base + o_rcol2);
     double4 *rec2 = (double4 *)(base + o_rec2);
-    Vis2Ovf *ovf = (Vis2Ovf *)(base + o_ovf);
+    Vis2Ovf *ovf = (Vis2Ovf *)(base + o_build + 64);   // inside VisBuild's 256-byte slot
+    static_assert(sizeof(VisBuild) <= 64, "overflow counter sits behind VisBuild");
     int2 *ovfi = (int2 *)(base + o_ovfi);
-    SW_CUDA(cudaMemsetAsync(count, 0, sizeof(int) * (size_t)(ncell2 + 1), st));
-    k_vis2_grid<<<1, 32, 0, st>>>(VP, vision_range, ncell2, G, VB, ovf);
-    k_vis2_fill<<<gb > 0 ? gb : 1, T, 0, st>>>(n, A.x[0], A.y[0], A.z[0], G, count, ids2, ovf, ovfi, VB, out, out_len);
+    // one memset: this call's box accumulator, the overflow counter (both in the slot in front of count[]) and the cell counts
+    SW_CUDA(cudaMemsetAsync(VB, 0, (size_t)((char *)(count + ncell2 + 1) - (char *)VB), st));
+    k_vis2_fill<<<gb > 0 ? gb : 1, T, 0, st>>>(n, A.x[0], A.y[0], A.z[0], VP, vision_range, ncell2, G, count, ids2, ovf, ovfi, VB, out, out_len);
     k_vis2_pack<<<sw_blocks(ncell2 * 32, T), T, 0, st>>>(G, count, ids2, A.x[0], A.y[0], A.z[0], radii, A.species, s->P, type_col, n_type_col,
                                                         rec2, rcol2, VB, VP);
     const size_t smem = sizeof(double) * (size_t)(n_cones * n_cols) * VISW_THREADS;
     k_vis2_cones<4><<<sw_blocks(n * 4, VISW_THREADS), VISW_THREADS, smem, st>>>(
         n, row_of, G, count, rec2, rcol2, ovf, ovfi, A.x[0], A.y[0], A.z[0], radii, A.species, s->P, type_col, n_type_col, s->P.n_dims,
         A.theta, A.q0, A.q1, A.q2, A.q3, dirs, vision_range, half_angle, n_cones, n_cols, out);
-    s->launches += 4;
+    s->launches += 3;
     SW_CUDA(cudaGetLastError());
     return SWARM_OK;
   }

@@ -29,21 +29,30 @@ struct PolNet {
 };
 
 // DMAX / AMAX bound the unrolled loops: the network of the reference's tests (obs_dim <= 8, 4 actions) runs the <8, 4>
-// instance -- 13 multiply-adds per hidden unit instead of the 48 predicated ones of the widest instance (128 us -> the
-// kernel was a fifth of the C4 slice on the Engine path, profiles/r02_launches_engine.csv).
+// instance.  The parameters of one hidden unit sit in ONE shared-memory record, zero-padded to the instance's widths,
+//     rec[j] = { w1[0..DMAX) , wa[0..AMAX) , b1 , wv , 0 , 0 }        (DMAX + AMAX + 4 floats, 16-byte aligned)
+// so a unit costs (DMAX + AMAX + 4) / 4 broadcast LDS.128 and DMAX + AMAX + 1 unpredicated FFMAs; a padded term is
+// fma(0, 0, h) = h, so the sums are the ones of the unpadded network bit for bit.  The earlier form read every weight
+// with its own predicated LDS.32 (58 instructions per unit in SASS, 41 us at C4: profiles/r02_launches_engine.csv).
 template <int DMAX, int AMAX>
 __global__ void __launch_bounds__(POL_THREADS) k_policy_forward(long long n, PolNet N, const double *obs, const int *row_of,
                                                                 const long long *gid, u64 seed, u64 call, int sample,
                                                                 const double *act_force, const double *act_torque,
                                                                 double *f_swim, double *tqx, double *tqy, double *tqz, int *idx_out,
                                                                 float *logp_out, float *value_out, float *logits_out) {
-  extern __shared__ float sm[];
+  extern __shared__ float4 sm4[];
+  constexpr int REC = DMAX + AMAX + 4;   // floats per hidden unit
+  float *sm = reinterpret_cast<float *>(sm4);
   const int D = N.obs_dim, H = N.hidden, A = N.n_actions;
-  float *w1 = sm, *b1 = w1 + D * H, *wa = b1 + H, *ba = wa + H * A, *wv = ba + A;
-  for (int t = threadIdx.x; t < D * H; t += blockDim.x) w1[t] = N.w1[t];
-  for (int t = threadIdx.x; t < H; t += blockDim.x) { b1[t] = N.b1[t]; wv[t] = N.wv[t]; }
-  for (int t = threadIdx.x; t < H * A; t += blockDim.x) wa[t] = N.wa[t];
-  for (int t = threadIdx.x; t < A; t += blockDim.x) ba[t] = N.ba[t];
+  for (int t = threadIdx.x; t < H * REC; t += blockDim.x) {
+    const int j = t / REC, k = t - j * REC;
+    float v = 0.0f;
+    if (k < DMAX) { if (k < D) v = N.w1[k * H + j]; }
+    else if (k < DMAX + AMAX) { if (k - DMAX < A) v = N.wa[j * A + (k - DMAX)]; }
+    else if (k == DMAX + AMAX) v = N.b1[j];
+    else if (k == DMAX + AMAX + 1) v = N.wv[j];
+    sm[t] = v;
+  }
   __syncthreads();
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
@@ -53,18 +62,23 @@ __global__ void __launch_bounds__(POL_THREADS) k_policy_forward(long long n, Pol
 #pragma unroll
   for (int d = 0; d < DMAX; ++d) x[d] = (d < D) ? (float)obs[(long long)row * D + d] : 0.0f;
 #pragma unroll
-  for (int a = 0; a < AMAX; ++a) lg[a] = (a < A) ? ba[a] : -INFINITY;
+  for (int a = 0; a < AMAX; ++a) lg[a] = (a < A) ? N.ba[a] : -INFINITY;
   float val = N.bv[0];
+#pragma unroll 2
   for (int j = 0; j < H; ++j) {
-    float h = b1[j];
+    float r[REC];
 #pragma unroll
-    for (int d = 0; d < DMAX; ++d)
-      if (d < D) h = fmaf(x[d], w1[d * H + j], h);
+    for (int q = 0; q < REC / 4; ++q) {
+      const float4 v = sm4[j * (REC / 4) + q];
+      r[4 * q] = v.x; r[4 * q + 1] = v.y; r[4 * q + 2] = v.z; r[4 * q + 3] = v.w;
+    }
+    float h = r[DMAX + AMAX];
+#pragma unroll
+    for (int d = 0; d < DMAX; ++d) h = fmaf(x[d], r[d], h);
     h = fmaxf(h, 0.0f);
 #pragma unroll
-    for (int a = 0; a < AMAX; ++a)
-      if (a < A) lg[a] = fmaf(h, wa[j * A + a], lg[a]);
-    val = fmaf(h, wv[j], val);
+    for (int a = 0; a < AMAX; ++a) lg[a] = fmaf(h, r[DMAX + a], lg[a]);
+    val = fmaf(h, r[DMAX + AMAX + 1], val);
   }
   // log(softmax + 1e-8), max-shifted as jax.nn.softmax does
   float mx = -INFINITY;
@@ -127,7 +141,9 @@ extern "C" int swarm_policy_forward(swarm_t *s, const swarm_policy_t *net, const
   }
   if ((act_force_dev == nullptr) != (act_torque_dev == nullptr)) { sw_set_error("bind both action tables or none"); return SWARM_ERR_INVALID; }
   if (act_force_dev && !s->actions_bound) { sw_set_error("bind the action arrays before asking the policy to write them"); return SWARM_ERR_STATE; }
-  const size_t smem = sizeof(float) * ((size_t)net->obs_dim * net->hidden + 2 * (size_t)net->hidden + (size_t)net->hidden * net->n_actions + net->n_actions);
+  const int dmax = (net->obs_dim <= 8 && net->n_actions <= 4) ? 8 : ((net->obs_dim <= 16 && net->n_actions <= 8) ? 16 : POL_MAX_OBS);
+  const int amax = dmax == 8 ? 4 : (dmax == 16 ? 8 : POL_MAX_ACT);
+  const size_t smem = sizeof(float) * (size_t)net->hidden * (size_t)(dmax + amax + 4);
   if (smem > 200 * 1024) { sw_set_error("policy: parameters do not fit in shared memory"); return SWARM_ERR_INVALID; }
   SW_CUDA(cudaSetDevice(s->cfg.device));
   const DevArrays &A = s->A;

@@ -351,6 +351,18 @@ class DeviceSwarm:
         cut = (lambda t: None if t is None else t[:n_rows])
         return cut(out), cut(dn), cut(dp)
 
+    def obs_field_mean(self, row_of, n_rows, src, box_length, hist, decay, c0, c1, scale=1.0, clip=False):
+        """Rewards of a closed-form decay AND their (sum, mean) in one launch: (rewards[n_rows], red[2])."""
+        torch = self.torch
+        out = torch.empty(max(n_rows, 1), dtype=torch.float64, device=self.dev)
+        red = torch.empty(2, dtype=torch.float64, device=self.dev)
+        s3 = (C.c_double * 3)(*[float(v) for v in src])
+        b3 = (C.c_double * 3)(*[float(v) for v in box_length])
+        _lib.check(self.lib.swarm_obs_field_mean(
+            self.h, row_of.data_ptr() if row_of is not None else None, int(n_rows), s3, b3, hist.data_ptr(), int(decay),
+            float(c0), float(c1), float(scale), int(bool(clip)), out.data_ptr(), red.data_ptr(), self._stream()))
+        return out[:n_rows], red
+
     def obs_vision(self, row_of, n_rows, vision_range, half_angle, n_cones, radii, type_col, n_cols, dirs=None):
         torch = self.torch
         out = torch.empty((max(n_rows, 1), n_cones, n_cols), dtype=torch.float64, device=self.dev)  # zeroed by the call

@@ -42,9 +42,12 @@ class GradientSensing(Task):
     """reward_i = clip(scale * (decay(|p_i - src|) - decay(|p_i_prev - src|)), 0, inf), history
     updated on every call (gradient_sensing.py:92-126)."""
 
+    fused_mean = True   # call_device(view, want_mean=True) also leaves the reward mean on the device
+
     def __init__(self, source=np.array([0, 0, 0]), decay_function: callable = None,
                  box_length=np.array([1.0, 1.0, 0.0]), reward_scale_factor: int = 10, particle_type: int = 0):
         super().__init__(particle_type=particle_type)
+        self.last_mean = None
         self.box_length = np.asarray(box_length, dtype=float)
         with np.errstate(divide="ignore", invalid="ignore"):
             self.source = np.asarray(source, dtype=float) / self.box_length
@@ -67,12 +70,19 @@ class GradientSensing(Task):
         """Stores the source un-normalised, as the reference does (gradient_sensing.py:81-90)."""
         self.source = np.asarray(new_source, dtype=float)
 
-    def call_device(self, colloids):
+    def call_device(self, colloids, want_mean=False):
+        """want_mean=True: `self.last_mean` holds the device (sum, mean) of the returned rewards when the decay has a
+        closed form (one launch for both), None otherwise."""
         swarm, _ = resolve_swarm(colloids)
         if self._history.empty():
             raise KeyError("GradientSensing was not initialized")
         row_of, rows = swarm.row_map(self.particle_type)
         spec = _decay_spec(self.decay_fn)
+        self.last_mean = None
+        if spec is not None and want_mean and rows > 0:
+            out, self.last_mean = swarm.obs_field_mean(row_of, rows, self.source, self.box_length, self._history.hist, spec[0],
+                                                       spec[1], spec[2], scale=self.reward_scale_factor, clip=True)
+            return out
         if spec is not None:
             out, _, _ = swarm.obs_field(row_of, rows, self.source, self.box_length, self._history.hist, decay=spec[0],
                                         c0=spec[1], c1=spec[2], scale=self.reward_scale_factor, clip=True,

@@ -109,6 +109,33 @@ def test_field_observable_and_gradient_reward_match_oracle():
         assert np.max(np.abs(out.cpu().numpy() - ref)) < 1e-12
 
 
+def test_field_reward_and_mean_in_one_launch():
+    """swarm_obs_field_mean == swarm_obs_field followed by the mean: rewards bit for bit, (sum, mean) over the rows of the
+    selected type in a fixed order (twice the same bits), history advanced once."""
+    import torch
+
+    (o, d), rng = _pair(n=5000)
+    n, L, src = o.n, 300.0, (0.5, 0.4, 0.0)
+    hist0 = np.ascontiguousarray((o.pos / L).T.copy())
+    shift = rng.normal(size=(n, 3)) * 3.0
+    shift[:, 2] = 0.0
+    d.pos[:, :n] += torch.from_numpy(np.ascontiguousarray(shift.T)).to(d.dev)
+    row_of, rows = d.row_map(0)
+    assert 0 < rows < n                       # a proper subset: rows of the other type must not enter the sum
+    for kind, c0, c1 in ((1, 1.0, -1.0), (2, 2.0, 0.5), (3, 2.0, 0.5)):
+        ha = torch.from_numpy(hist0.copy()).to(d.dev)
+        hb, hc = ha.clone(), ha.clone()
+        ref, _, _ = d.obs_field(row_of, rows, src, (L, L, L), ha, decay=kind, c0=c0, c1=c1, scale=100.0, clip=True, want_dist=False)
+        out, red = d.obs_field_mean(row_of, rows, src, (L, L, L), hb, kind, c0, c1, scale=100.0, clip=True)
+        out2, red2 = d.obs_field_mean(row_of, rows, src, (L, L, L), hc, kind, c0, c1, scale=100.0, clip=True)
+        r = ref.cpu().numpy()
+        assert np.array_equal(out.cpu().numpy(), r) and torch.equal(ha, hb)
+        assert r.sum() > 0.0
+        got = red.cpu().numpy()
+        assert abs(got[0] - r.sum()) <= 1e-12 * r.sum() and abs(got[1] - r.mean()) <= 1e-12 * r.mean()
+        assert np.array_equal(got, red2.cpu().numpy())        # the ticket re-arms; same bits
+
+
 @pytest.mark.parametrize("name,clip", [("gradient_sensing.npz", True), ("concentration_field.npz", False)])
 def test_field_sequences_golden(golden, name, clip):
     """Sequences produced by the reference's GradientSensing / ConcentrationField (decay 1 - d)."""

@@ -71,6 +71,24 @@ def test_device_path_equals_object_path(tmp_path):
     assert np.all(z == 0.0)                                   # 2-D: planar (test_espresso_2d.py:59-82)
 
 
+def test_reward_mean_stays_on_the_device_in_one_launch(tmp_path):
+    """DeviceAgent(reward_mean=True) with GradientSensing: reward and its mean come from one launch
+    (swarm_obs_field_mean); the means equal the host mean of the per-agent rewards the trainer would take
+    (trainers/trainer.py:92-95)."""
+    e = _engine(tmp_path)
+    agent = _agent(sw.CounterPolicy(4, seed=7))
+    agent.reward_mean = True
+    ff = sw.ForceFunction({"0": agent})
+    agent.reset_agent(e.colloids)
+    e.integrate(5, ff)
+    e.finalize()
+    assert len(agent.reward_means) == len(agent.trajectory.rewards) == 5
+    assert agent.task.last_mean is not None          # the fused launch was taken
+    for red, r in zip(agent.reward_means, agent.trajectory.rewards):
+        red, r = red.cpu().numpy(), r.cpu().numpy()
+        assert abs(red[0] - r.sum()) <= 1e-12 * max(1.0, abs(r.sum())) and abs(red[1] - r.mean()) <= 1e-12 * max(1.0, abs(r.mean()))
+
+
 def test_fused_policy_drives_a_rollout(tmp_path):
     rng = np.random.default_rng(0)
     P = dict(w1=rng.normal(size=(1, 128)) * 0.5, b1=rng.normal(size=128) * 0.1, wa=rng.normal(size=(128, 4)) * 0.2,

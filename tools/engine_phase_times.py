@@ -11,17 +11,17 @@ def wrap(name):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(); r = f(self, *a, **k); e1.record(); log.append((name, e0, e1)); return r
     setattr(DeviceSwarm, name, g)
-for nm in ("obs_vision", "policy_forward", "run", "obs_field", "reduce_mean"): wrap(nm)
+for nm in ("obs_vision", "policy_forward", "run", "obs_field", "obs_field_mean", "reduce_mean"): wrap(nm)
 rec = bench.engine_record(types.SimpleNamespace(skin=2.0), 0, 60, 3)
 torch.cuda.synchronize()
 print({k: rec[k] for k in ("ms_per_step", "gpu_launches_per_slice")})
-# the single integrate(60) call: entries after warm-up (3 slices x 5 calls) up to 60 slices
-seq = log[15:15 + 300]
-dur, gap = collections.defaultdict(float), collections.defaultdict(float)
-for k, (name, e0, e1) in enumerate(seq):
-    dur[name] += e0.elapsed_time(e1)
-    if k: gap[name] += seq[k - 1][2].elapsed_time(e0)
-for name in dur: print(f"{name:16s} device {dur[name] / 60 * 1e3:8.1f} us   idle gap before it {gap[name] / 60 * 1e3:8.1f} us")
+# mean device time of the LAST 60 calls of every kind (the timed integrate(60)) and the idle gap in front of each
+byname = collections.defaultdict(list)
+for k, (name, e0, e1) in enumerate(log):
+    byname[name].append((e0.elapsed_time(e1), log[k - 1][2].elapsed_time(e0) if k else 0.0))
+for name, v in byname.items():
+    v = v[-60:]
+    print(f"{name:16s} device {sum(a for a, _ in v) / len(v) * 1e3:8.1f} us   idle gap before it {sum(b for _, b in v) / len(v) * 1e3:8.1f} us   ({len(v)} calls)")
 # host enqueue rate of one integrate(K) call (until the engine's final counter check starts waiting for the device)
 import time
 import swarmrl_b200 as sw
