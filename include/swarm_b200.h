@@ -302,6 +302,15 @@ int swarm_obs_field_mean(swarm_t *s, const int32_t *row_of_dev, int64_t n_rows, 
                          const double box_length[3], double *hist_dev, int32_t decay, double c0, double c1, double scale,
                          int32_t clip, double *out_dev, double *out2_dev, void *stream);
 
+/* swarm_obs_field_mean that allocates NOTHING.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments, same results (bit for bit) as swarm_obs_field_mean; the per-CTA sums live in a static device array of
+ * 32768 CTA slots (256 KiB per GPU that loads the library, held until exit), so a swarm of more than 8 388 608 particles
+ * is refused with SWARM_ERR_INVALID.  Every call shares that array: calls that overlap on one GPU race. */
+int swarm_obs_field_mean_noalloc(swarm_t *s, const int32_t *row_of_dev, int64_t n_rows, const double src[3],
+                                 const double box_length[3], double *hist_dev, int32_t decay, double c0, double c1,
+                                 double scale, int32_t clip, double *out_dev, double *out2_dev, void *stream);
+
 /* ---- fused policy forward ----------------------------------------------------
  * ActorCriticAgent.calc_action (agents/actor_critic.py:159-184) -> FlaxModel.compute_action
  * (networks/flax_network.py:153-195) -> GumbelDistribution (sampling_strategies/gumbel_distribution.py:

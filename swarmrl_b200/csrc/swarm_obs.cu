@@ -15,6 +15,7 @@
 //   range of the packed arrays.
 #include <math.h>
 #include <stdlib.h>
+#include <mutex>
 
 #include "swarm_common.cuh"
 
@@ -1048,6 +1049,56 @@ extern "C" int swarm_obs_field_mean(swarm_t *s, const int32_t *row_of, int64_t n
                                     int32_t clip, double *out, double *out2, void *stream) {
   if (!out2 || n_rows < 0) { sw_set_error("bad arguments"); return SWARM_ERR_INVALID; }
   return sw_obs_field_launch(s, row_of, src, box_length, hist, decay, c0, c1, scale, clip, out, nullptr, nullptr, out2, n_rows, stream);
+}
+
+// ---- swarm_obs_field_mean without any allocation ----------------------------------------------------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (CUDA graph capture, tight serving loops).  The per-CTA reward sums and the ticket of k_obs_field live in a file-scope
+// device array instead of swarm_t::field_scratch: SW_NOALLOC_MAX_BLOCKS CTAs of 256 particles = 8 388 608 particles,
+// 256 KiB + one 256-byte slot for the ticket, held by every GPU that loads the library until the process exits.
+// Host code must not pass the symbol itself to a kernel (in host code it is a stand-in, not a device address): its
+// address is resolved once per device with cudaGetSymbolAddress, that device current.  All calls share the array -- two
+// calls whose kernels overlap on one GPU (different streams) race on the sums and on the ticket.
+#define SW_NOALLOC_MAX_BLOCKS 32768
+#define SW_NOALLOC_MAX_DEVICES 64
+static __device__ __align__(256) double g_noalloc_field_scratch[SW_NOALLOC_MAX_BLOCKS + 32];   // [MAX_BLOCKS]: the ticket
+static double *g_noalloc_field_ptr[SW_NOALLOC_MAX_DEVICES];   // device address of the array, per device (nullptr: not resolved yet)
+static std::mutex g_noalloc_mutex;
+
+extern "C" int swarm_obs_field_mean_noalloc(swarm_t *s, const int32_t *row_of, int64_t n_rows, const double src[3],
+                                            const double box_length[3], double *hist, int32_t decay, double c0, double c1,
+                                            double scale, int32_t clip, double *out, double *out2, void *stream) {
+  if (!s || !s->state_bound || !src || !box_length || !hist || !out || !out2 || n_rows < 0) { sw_set_error("bad arguments"); return SWARM_ERR_INVALID; }
+  if (decay <= SWARM_DECAY_NONE || decay > SWARM_DECAY_INVERSE) { sw_set_error("the mean needs a closed-form decay"); return SWARM_ERR_INVALID; }
+  const DevArrays &A = s->A;
+  if (A.n > (long long)SW_NOALLOC_MAX_BLOCKS * 256) {
+    sw_set_error("swarm_obs_field_mean_noalloc: more than 8388608 particles (the static scratch holds 32768 CTA sums); use swarm_obs_field_mean");
+    return SWARM_ERR_INVALID;
+  }
+  const int dev = s->cfg.device;
+  if (dev < 0 || dev >= SW_NOALLOC_MAX_DEVICES) { sw_set_error("swarm_obs_field_mean_noalloc: device ordinal out of range"); return SWARM_ERR_INVALID; }
+  SW_CUDA(cudaSetDevice(dev));
+  double *scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_field_ptr[dev]) {
+      double *p = nullptr;
+      SW_CUDA(cudaGetSymbolAddress((void **)&p, g_noalloc_field_scratch));   // the address on the CURRENT device
+      g_noalloc_field_ptr[dev] = p;
+    }
+    scratch = g_noalloc_field_ptr[dev];
+  }
+  if (A.n == 0) return SWARM_OK;
+  const int blocks = sw_blocks(A.n, 256);
+  unsigned int *ticket = (unsigned int *)(scratch + SW_NOALLOC_MAX_BLOCKS);
+  // the ticket must start at zero whatever an earlier (possibly failed) call left; the sums are overwritten before they are read
+  SW_CUDA(cudaMemsetAsync(ticket, 0, sizeof(double), (cudaStream_t)stream));
+  k_obs_field<<<blocks, 256, 0, (cudaStream_t)stream>>>(A.n, A.x[0], A.y[0], A.z[0], row_of, src[0], src[1], src[2], box_length[0],
+                                                        box_length[1], box_length[2], hist, decay, c0, c1, scale, clip, out, nullptr,
+                                                        nullptr, scratch, ticket, out2, (long long)n_rows);
+  s->launches += 1;
+  SW_CUDA(cudaGetLastError());
+  return SWARM_OK;
 }
 
 extern "C" int swarm_obs_pair_field(swarm_t *s, const int32_t *row_of, const int32_t *sensed_idx, int64_t n_sensed,
