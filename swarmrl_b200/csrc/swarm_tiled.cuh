@@ -71,6 +71,29 @@ struct TileArgs {
                             // every flag of the previous launch (launch counter << 15; a launch runs < 2^15 epochs)
 };
 
+// Split CTA barrier of the step loop (mbarrier in shared memory): a warp ARRIVES as soon as its new positions are in
+// shared memory and WAITS only after the particle-local work of the next step.  With __syncthreads at the end of the
+// iteration every warp waited for the slowest warp's pair phase AND local work; now a warp waits only if another warp
+// has not finished its pair phase by the time the waiter has finished its own local work, and the latency-bound pair
+// phase of a slow warp overlaps the issue-bound local work of the fast ones.  Lane 0 arrives for its warp after
+// __syncwarp (orders the lanes' stores before the releasing arrive); every lane polls (acquire).
+__device__ __forceinline__ void tile_mbar_init(unsigned long long *b, unsigned int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((unsigned int)__cvta_generic_to_shared(b)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void tile_mbar_arrive_warp(unsigned long long *b) {
+  __syncwarp();
+  if ((threadIdx.x & 31) == 0)
+    asm volatile("mbarrier.arrive.release.cta.shared::cta.b64 _, [%0];" ::"r"((unsigned int)__cvta_generic_to_shared(b)) : "memory");
+}
+__device__ __forceinline__ void tile_mbar_wait(unsigned long long *b, unsigned int parity) {
+  const unsigned int a = (unsigned int)__cvta_generic_to_shared(b);
+  unsigned int ok;
+  do {
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.acquire.cta.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(a), "r"(parity) : "memory");
+  } while (!ok);
+}
+
 __device__ __forceinline__ void rim_write(RimRec *r, unsigned int flag, double x, double y) {
   const unsigned long long f = flag;
   const unsigned long long w0 = ((unsigned long long)(unsigned int)__double2loint(x) << 32) | f;
@@ -296,6 +319,9 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_tiled(const __grid_cons
     c.sw = NOISE ? sqrt(P.kT / P.sp_rin[k][0]) : 0.0;
     S[k] = c;
   }
+  __shared__ unsigned long long s_stepbar;
+  if (threadIdx.x == 0) tile_mbar_init(&s_stepbar, blockDim.x >> 5);   // one arrival per warp
+  unsigned int stepbar_parity = 0u;
   __syncthreads();
   if (act) {
     id = G.perm[slot];
@@ -642,12 +668,15 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_tiled(const __grid_cons
       if (exported) rim_write(&(G.rim + nxt * G.rim_stride)[slot], G.flag0 + e + 1u, xi, yi);
     }
     SW_TICK(1);   // pair forces + update
+    if constexpr (!HALO) tile_mbar_arrive_warp(&s_stepbar);   // this warp's positions of the next step are in shared memory
     if (actv && !last) local_inputs(R.step0 + (u64)(s + 1));   // step s+1's particle-local work: the rim records travel meanwhile
     // the next iteration is a synchronisation point: it republishes and reloads the halo behind its grid barrier
     const bool next_sync = (since + 1 >= K) || last;
     if constexpr (HALO) if (!next_sync) tile_halo_load((G.rim + nxt * G.rim_stride), G.flag0 + e + 1u, htab, hlist, s_nh, hlane, &sx[nxt][SW_TILE_MAXP], &sy[nxt][SW_TILE_MAXP]);
+    if constexpr (HALO) tile_mbar_arrive_warp(&s_stepbar);    // the halo of the next step is in shared memory
     SW_TICK(4);   // particle-local work of the next step / halo warp: the neighbours' records
-    __syncthreads();   // the positions of the next step -- tile and halo -- are in shared memory
+    tile_mbar_wait(&s_stepbar, stepbar_parity);   // the positions of the next step -- tile and halo -- are in shared memory
+    stepbar_parity ^= 1u;
     SW_TICK(5);
     ++s; ++since; ++e;
   }
