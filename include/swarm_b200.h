@@ -255,6 +255,21 @@ int swarm_dd_obs_field(swarm_t *s, int64_t n, const int32_t *n_dev, const swarm_
                        const double src[3], const double box_length[2], int32_t decay, double c0, double c1,
                        double scale, int32_t clip_nonneg, int32_t init_only, double *out_dev, void *stream);
 
+/* The same with the history in aux channels aux_base, aux_base + 1 and, with all_local = 1, for the ghosts as well (a
+ * ConcentrationField OBSERVABLE feeds the policy of every local particle: a ghost must take the action its owner
+ * computes; a task reward is owned-only).  observables/concentration_field.py:84-138. */
+int swarm_dd_obs_field_ch(swarm_t *s, int64_t n, const int32_t *n_dev, const swarm_dd_arrays_t *loc, double x_offset, double box_x,
+                          const double src[3], const double box_length[2], int32_t decay, double c0, double c1, double scale,
+                          int32_t clip_nonneg, int32_t init_only, int32_t aux_base, int32_t all_local, double *out_dev,
+                          void *stream);
+
+/* Periodic image count of every slot along the decomposed axis (int32, device), or NULL to unbind.  swarm_obs_vision then
+ * lets two slots see each other only when they sit in the same image: the reference evaluates vision cones on unfolded
+ * positions without a minimum image (observables/subdivided_vision_cones.py:113-157), and a rank's local frame places the
+ * ghosts from across the periodic seam next to its own particles.  With a device-resident count bound (swarm_bind_count)
+ * swarm_obs_vision also skips the slots past it.  Reset to NULL by swarm_bind_state. */
+int swarm_bind_images(swarm_t *s, const int32_t *image_dev);
+
 /* ---- observables / tasks -------------------------------------------------------------- */
 
 /* ConcentrationField.compute_observable (observables/concentration_field.py:84-138) and

@@ -104,6 +104,9 @@ SYMBOLS = {
                                  C.POINTER(DDArrays), _V, _V]),
     "swarm_dd_obs_field": (C.c_int, [_V, C.c_int64, _V, C.POINTER(DDArrays), C.c_double, C.c_double, _DP, _DP, C.c_int32,
                                      C.c_double, C.c_double, C.c_double, C.c_int32, C.c_int32, _V, _V]),
+    "swarm_dd_obs_field_ch": (C.c_int, [_V, C.c_int64, _V, C.POINTER(DDArrays), C.c_double, C.c_double, _DP, _DP, C.c_int32,
+                                        C.c_double, C.c_double, C.c_double, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _V, _V]),
+    "swarm_bind_images": (C.c_int, [_V, _V]),
     "swarm_apply_new_direction": (C.c_int, [_V, _V]),
     "swarm_relax": (C.c_int, [_V, C.c_int64, C.c_double, C.c_double, _V]),
     "swarm_run": (C.c_int, [_V, C.c_int64, C.c_uint64, _V]),

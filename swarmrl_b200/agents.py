@@ -240,6 +240,9 @@ class DeviceAgent(Agent):
                 self.trajectory.log_probs.append(logp)
                 self.trajectory.killed = self.task.kill_switch
             return
+        if getattr(swarm, "is_domain", False):
+            raise NotImplementedError("a domain-decomposed swarm needs a policy with a fused `act` (FusedActorCritic): its "
+                                      "sampling is keyed by the particle id, so a ghost takes its owner's action")
         out = self.policy(obs)
         idx, logp = out if isinstance(out, tuple) else (out, None)
         if self._all:

@@ -213,14 +213,15 @@ __device__ __forceinline__ double dd_decay(int kind, double c0, double c1, doubl
 }
 
 __global__ void k_dd_obs_field(long long n, const int *n_dev, DdArrays L, double x_off, double box_x, double s0, double s1, double s2, double b0,
-                               double b1, int decay, double c0, double c1, double scale, int clip, int init_only, double *out) {
+                               double b1, int decay, double c0, double c1, double scale, int clip, int init_only, double *out,
+                               double *ha, double *hb, int all_local) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  if (i >= dd_live(n, n_dev) || !L.owned[i]) { out[i] = 0.0; return; }
+  if (i >= dd_live(n, n_dev) || !(all_local || L.owned[i])) { out[i] = 0.0; return; }
   const double xg = L.x[i] + x_off + (double)L.image[i] * box_x;
   const double p0 = xg / b0, p1 = L.y[i] / b1;
-  const double h0 = L.aux[0][i], h1 = L.aux[1][i];
-  L.aux[0][i] = p0; L.aux[1][i] = p1;
+  const double h0 = ha[i], h1 = hb[i];
+  ha[i] = p0; hb[i] = p1;
   if (init_only) { out[i] = 0.0; return; }
   const double dn = sqrt((s0 - p0) * (s0 - p0) + (s1 - p1) * (s1 - p1) + s2 * s2);
   const double dp = sqrt((s0 - h0) * (s0 - h0) + (s1 - h1) * (s1 - h1) + s2 * s2);
@@ -229,19 +230,35 @@ __global__ void k_dd_obs_field(long long n, const int *n_dev, DdArrays L, double
   out[i] = v;
 }
 
-extern "C" int swarm_dd_obs_field(swarm_t *s, int64_t n, const int32_t *n_dev, const swarm_dd_arrays_t *loc, double x_offset, double box_x,
-                                  const double src[3], const double box_length[2], int32_t decay, double c0, double c1,
-                                  double scale, int32_t clip_nonneg, int32_t init_only, double *out_dev, void *stream) {
-  if (!s || !loc || !src || !box_length || !out_dev || n < 0 || !loc->aux[0] || !loc->aux[1]) {
-    sw_set_error("bad arguments (the history needs aux channels 0 and 1)"); return SWARM_ERR_INVALID;
+static int dd_obs_field(swarm_t *s, int64_t n, const int32_t *n_dev, const swarm_dd_arrays_t *loc, double x_offset, double box_x,
+                        const double src[3], const double box_length[2], int32_t decay, double c0, double c1, double scale,
+                        int32_t clip_nonneg, int32_t init_only, int32_t aux_base, int32_t all_local, double *out_dev, void *stream) {
+  if (!s || !loc || !src || !box_length || !out_dev || n < 0 || aux_base < 0 || aux_base + 2 > SWARM_DD_MAX_AUX ||
+      !loc->aux[aux_base] || !loc->aux[aux_base + 1]) {
+    sw_set_error("bad arguments (the history needs two aux channels)"); return SWARM_ERR_INVALID;
   }
   if (decay < SWARM_DECAY_NONE || decay > SWARM_DECAY_INVERSE) { sw_set_error("unknown decay kind"); return SWARM_ERR_INVALID; }
   SW_CUDA(cudaSetDevice(s->cfg.device));
   if (n == 0) return SWARM_OK;
   k_dd_obs_field<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(n, (const int *)n_dev, dd_arrays(loc), x_offset, box_x, src[0], src[1],
                                                                                src[2], box_length[0], box_length[1], decay, c0, c1,
-                                                                               scale, clip_nonneg, init_only, out_dev);
+                                                                               scale, clip_nonneg, init_only, out_dev, loc->aux[aux_base],
+                                                                               loc->aux[aux_base + 1], all_local);
   s->launches += 1;
   SW_CUDA(cudaGetLastError());
   return SWARM_OK;
+}
+
+extern "C" int swarm_dd_obs_field(swarm_t *s, int64_t n, const int32_t *n_dev, const swarm_dd_arrays_t *loc, double x_offset, double box_x,
+                                  const double src[3], const double box_length[2], int32_t decay, double c0, double c1,
+                                  double scale, int32_t clip_nonneg, int32_t init_only, double *out_dev, void *stream) {
+  return dd_obs_field(s, n, n_dev, loc, x_offset, box_x, src, box_length, decay, c0, c1, scale, clip_nonneg, init_only, 0, 0, out_dev, stream);
+}
+
+extern "C" int swarm_dd_obs_field_ch(swarm_t *s, int64_t n, const int32_t *n_dev, const swarm_dd_arrays_t *loc, double x_offset,
+                                     double box_x, const double src[3], const double box_length[2], int32_t decay, double c0, double c1,
+                                     double scale, int32_t clip_nonneg, int32_t init_only, int32_t aux_base, int32_t all_local,
+                                     double *out_dev, void *stream) {
+  return dd_obs_field(s, n, n_dev, loc, x_offset, box_x, src, box_length, decay, c0, c1, scale, clip_nonneg, init_only, aux_base, all_local,
+                      out_dev, stream);
 }

@@ -959,6 +959,7 @@ extern "C" int swarm_bind_state(swarm_t *s, int64_t n, const swarm_state_dev_t *
   A.species = st->species;
   A.gid = nullptr;
   A.n_dev = nullptr;
+  s->vis_image = nullptr;
   s->P.env_size = (int)(n / s->P.n_envs);
   if (s->P.env_size < 1) s->P.env_size = 1;
   if (!reuse) {

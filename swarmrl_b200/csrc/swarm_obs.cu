@@ -602,6 +602,11 @@ __global__ void __launch_bounds__(VISW_THREADS) k_vis_cones_warp(long long n, co
 // ---------------------------------------------------------------------------------------------
 #define VIS2_CAP 32
 struct Vis2Ovf { int n; int pad; };
+__device__ __forceinline__ long long vis_live(long long n, const int *n_dev) {
+  if (!n_dev) return n;
+  const long long m = (long long)__ldg(n_dev);
+  return m < n ? m : n;
+}
 
 // Grid over the previous call's box: a few dozen flops, so every CTA of k_vis2_fill derives it for itself (thread 0,
 // shared memory) and CTA 0 leaves the copy k_vis2_pack / k_vis2_cones read -- no launch of its own.
@@ -633,7 +638,7 @@ __device__ void vis2_make_grid(const VisPrev *prev, double range, long long ncel
   G->inv_cs = 1.0 / cs;
 }
 
-__global__ void __launch_bounds__(256) k_vis2_fill(long long n, const double *x, const double *y, const double *z,
+__global__ void __launch_bounds__(256) k_vis2_fill(long long n, const int *n_dev, const double *x, const double *y, const double *z,
                                                    const VisPrev *prev, double range, long long ncell_max, VisGrid *Gout,
                                                    int *count, int *ids, Vis2Ovf *ovf, int2 *ovf_items, VisBuild *B, double *out,
                                                    long long out_len) {
@@ -648,6 +653,7 @@ __global__ void __launch_bounds__(256) k_vis2_fill(long long n, const double *x,
   const long long gtid = (long long)blockIdx.x * blockDim.x + threadIdx.x, gsz = (long long)gridDim.x * blockDim.x;
   for (long long i = gtid; i < out_len; i += gsz) out[i] = 0.0;
   unsigned long long mn[3] = {0ULL, 0ULL, 0ULL}, mx[3] = {0ULL, 0ULL, 0ULL};
+  n = vis_live(n, n_dev);   // slots past the device-resident count (domain decomposition) hold stale particles
   for (long long i = gtid; i < n; i += gsz) {
     const double xi = x[i], yi = y[i], zi = z[i];
     const unsigned long long e[3] = {enc_double(xi), enc_double(yi), enc_double(zi)};
@@ -681,10 +687,11 @@ __global__ void __launch_bounds__(256) k_vis2_fill(long long n, const double *x,
 }
 
 // first call of a swarm: no previous box yet -- the box of the current positions
-__global__ void __launch_bounds__(256) k_vis2_bbox(long long n, const double *x, const double *y, const double *z, VisPrev *prev) {
+__global__ void __launch_bounds__(256) k_vis2_bbox(long long n, const int *n_dev, const double *x, const double *y, const double *z, VisPrev *prev) {
   __shared__ unsigned long long smn[3][8], smx[3][8];
   const long long gtid = (long long)blockIdx.x * blockDim.x + threadIdx.x, gsz = (long long)gridDim.x * blockDim.x;
   unsigned long long mn[3] = {0ULL, 0ULL, 0ULL}, mx[3] = {0ULL, 0ULL, 0ULL};
+  n = vis_live(n, n_dev);
   for (long long i = gtid; i < n; i += gsz) {
     const unsigned long long e[3] = {enc_double(x[i]), enc_double(y[i]), enc_double(z[i])};
 #pragma unroll
@@ -712,8 +719,8 @@ __global__ void __launch_bounds__(256) k_vis2_bbox(long long n, const double *x,
 // one warp per cell
 __global__ void __launch_bounds__(256) k_vis2_pack(const VisGrid *G, const int *count, const int *ids, const double *x, const double *y,
                                                    const double *z, const double *radii, const int *species, const __grid_constant__ DevParams P,
-                                                   const int *type_col, int n_type_col, double4 *rec, int *rcol, const VisBuild *B,
-                                                   VisPrev *prev) {
+                                                   const int *type_col, int n_type_col, double4 *rec, int *rcol, const int *image,
+                                                   int *rimg, const VisBuild *B, VisPrev *prev) {
   const long long gw = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (gw == 0 && lane < 3) { prev->mnc[lane] = B->mnc[lane]; prev->mx[lane] = B->mx[lane]; }   // the box for the next call
@@ -730,11 +737,16 @@ __global__ void __launch_bounds__(256) k_vis2_pack(const VisGrid *G, const int *
     rec[o] = make_double4(x[id], y[id], z[id], radii[id]);
     const int t = P.sp_type[species[id]];
     rcol[o] = (t >= 0 && t < n_type_col) ? type_col[t] : -1;
+    if (image) rimg[o] = image[id];
   }
 }
 
+// `image` (swarm_bind_images, domain decomposition): the periodic image count of every slot along the decomposed axis.  The
+// reference measures vision on UNFOLDED positions without a minimum image (subdivided_vision_cones.py:113-157), so two
+// slots that are close in a rank's local frame see each other only when they sit in the same image.
 template <int GS>
-__global__ void __launch_bounds__(VISW_THREADS) k_vis2_cones(long long n, const int *row_of, const VisGrid *G, const int *count,
+__global__ void __launch_bounds__(VISW_THREADS) k_vis2_cones(long long n, const int *n_dev, const int *image, const int *rimg,
+                                                             const int *row_of, const VisGrid *G, const int *count,
                                                              const double4 *rec, const int *rcol, const Vis2Ovf *ovf, const int2 *ovf_items,
                                                              const double *x, const double *y, const double *z, const double *radii,
                                                              const int *species, const __grid_constant__ DevParams P, const int *type_col,
@@ -744,12 +756,13 @@ __global__ void __launch_bounds__(VISW_THREADS) k_vis2_cones(long long n, const 
   extern __shared__ double sacc[];   // [nacc][VISW_THREADS]
   const int lane = threadIdx.x & (GS - 1);
   long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) / GS;
-  const bool in_range = i < n;
+  const bool in_range = i < vis_live(n, n_dev);
   if (!in_range) i = n - 1;
   const int row = in_range ? row_of[i] : -1;
   const int nacc = n_cones * n_cols;
   for (int a = 0; a < nacc; ++a) sacc[a * VISW_THREADS + threadIdx.x] = 0.0;
   const double xi = x[i], yi = y[i], zi = z[i];
+  const int img_i = image ? image[i] : 0;
   double ex, ey, ez;
   if (dirs) { ex = dirs[i]; ey = dirs[n + i]; ez = dirs[2 * n + i]; }
   else if (n_dims == 2) { sincos(theta[i], &ey, &ex); ez = 0.0; }
@@ -782,7 +795,9 @@ __global__ void __launch_bounds__(VISW_THREADS) k_vis2_cones(long long n, const 
             const long long o = c * VIS2_CAP + k;
             const double2 r01 = __ldg(reinterpret_cast<const double2 *>(&rec[o]));
             const double2 r23 = __ldg(reinterpret_cast<const double2 *>(&rec[o]) + 1);
-            visw_candidate(r01.x, r01.y, r23.x, r23.y, __ldg(&rcol[o]), xi, yi, zi, ex, ey, ez, range, half_angle, cone_w, n_cones, n_cols,
+            int col = __ldg(&rcol[o]);
+            if (image && __ldg(&rimg[o]) != img_i) col = -1;
+            visw_candidate(r01.x, r01.y, r23.x, r23.y, col, xi, yi, zi, ex, ey, ez, range, half_angle, cone_w, n_cones, n_cols,
                            rim, crim, sacc);
           }
         }
@@ -795,7 +810,8 @@ __global__ void __launch_bounds__(VISW_THREADS) k_vis2_cones(long long n, const 
       if (abs(ox - cx) > 1 || abs(oy - cy) > 1 || abs(oz - cz) > 1) continue;
       const int j = it.y;
       const int t = P.sp_type[species[j]];
-      const int col = (t >= 0 && t < n_type_col) ? type_col[t] : -1;
+      int col = (t >= 0 && t < n_type_col) ? type_col[t] : -1;
+      if (image && image[j] != img_i) col = -1;
       visw_candidate(x[j], y[j], z[j], radii[j], col, xi, yi, zi, ex, ey, ez, range, half_angle, cone_w, n_cones, n_cols, rim, crim, sacc);
     }
   }
@@ -1152,6 +1168,12 @@ extern "C" int swarm_reduce_mean(swarm_t *s, const double *in, int64_t n, double
   return SWARM_OK;
 }
 
+extern "C" int swarm_bind_images(swarm_t *s, const int32_t *image_dev) {
+  if (!s) { sw_set_error("bad arguments"); return SWARM_ERR_INVALID; }
+  s->vis_image = (const int *)image_dev;
+  return SWARM_OK;
+}
+
 extern "C" int swarm_obs_vision(swarm_t *s, const int32_t *row_of, int64_t rows, double vision_range, double half_angle,
                                 int32_t n_cones, const double *radii, const int32_t *type_col, int32_t n_type_col,
                                 int32_t n_cols, const double *dirs, double *out, void *stream) {
@@ -1186,6 +1208,7 @@ extern "C" int swarm_obs_vision(swarm_t *s, const int32_t *row_of, int64_t rows,
   if (ncell2 < 4096) ncell2 = 4096;
   if (ncell2 > (1LL << 20)) ncell2 = (1LL << 20);
   size_t o_ids2 = carve(sizeof(int) * (size_t)ncell2 * VIS2_CAP), o_rcol2 = carve(sizeof(int) * (size_t)ncell2 * VIS2_CAP);
+  size_t o_rimg2 = carve(s->vis_image ? sizeof(int) * (size_t)ncell2 * VIS2_CAP : 0);
   size_t o_rec2 = carve(sizeof(double4) * (size_t)ncell2 * VIS2_CAP), o_ovf = carve(sizeof(Vis2Ovf)), o_ovfi = carve(sizeof(int2) * (size_t)n);
   if (s->vis_bytes < off) {
     if (s->vis_buf) cudaFree(s->vis_buf);
@@ -1203,29 +1226,33 @@ extern "C" int swarm_obs_vision(swarm_t *s, const int32_t *row_of, int64_t rows,
   const int T = 256, B = sw_blocks(n, T);
   const int gb = B < 4 * s->num_sms ? B : 4 * s->num_sms;
   const long long out_len = (long long)rows * n_cones * n_cols;
-  if (n_cones * n_cols <= VISW_MAX_ACC && !getenv("SWARM_B200_VIS_V1") && !getenv("SWARM_B200_VIS_SERIAL")) {
+  const bool dd_view = A.n_dev || s->vis_image;   // a device-resident count / image counts: only the fixed-capacity kernels honour them
+  if (dd_view && n_cones * n_cols > VISW_MAX_ACC) {
+    sw_set_error("vision cones on a domain-decomposed swarm: n_cones * n_detected_types must be <= 32"); return SWARM_ERR_INVALID;
+  }
+  if (n_cones * n_cols <= VISW_MAX_ACC && (dd_view || (!getenv("SWARM_B200_VIS_V1") && !getenv("SWARM_B200_VIS_SERIAL")))) {
     // ---- fixed-capacity layout on the previous call's bounding box: memset, fill, pack, cones -------------------
     VisBuild *VB = (VisBuild *)(base + o_build);
     VisPrev *VP = (VisPrev *)(base + o_prev);
     if (!(s->vis_prev_n == n && s->vis_prev_range == vision_range)) {
       SW_CUDA(cudaMemsetAsync(VP, 0, sizeof(VisPrev), st));
-      k_vis2_bbox<<<gb > 0 ? gb : 1, T, 0, st>>>(n, A.x[0], A.y[0], A.z[0], VP);
+      k_vis2_bbox<<<gb > 0 ? gb : 1, T, 0, st>>>(n, A.n_dev, A.x[0], A.y[0], A.z[0], VP);
       s->launches += 1;
       s->vis_prev_n = n; s->vis_prev_range = vision_range;
     }
-    int *ids2 = (int *)(base + o_ids2), *rcol2 = (int *)(base + o_rcol2);
+    int *ids2 = (int *)(base + o_ids2), *rcol2 = (int *)(base + o_rcol2), *rimg2 = s->vis_image ? (int *)(base + o_rimg2) : nullptr;
     double4 *rec2 = (double4 *)(base + o_rec2);
     Vis2Ovf *ovf = (Vis2Ovf *)(base + o_build + 64);   // inside VisBuild's 256-byte slot
     static_assert(sizeof(VisBuild) <= 64, "overflow counter sits behind VisBuild");
     int2 *ovfi = (int2 *)(base + o_ovfi);
     // one memset: this call's box accumulator, the overflow counter (both in the slot in front of count[]) and the cell counts
     SW_CUDA(cudaMemsetAsync(VB, 0, (size_t)((char *)(count + ncell2 + 1) - (char *)VB), st));
-    k_vis2_fill<<<gb > 0 ? gb : 1, T, 0, st>>>(n, A.x[0], A.y[0], A.z[0], VP, vision_range, ncell2, G, count, ids2, ovf, ovfi, VB, out, out_len);
+    k_vis2_fill<<<gb > 0 ? gb : 1, T, 0, st>>>(n, A.n_dev, A.x[0], A.y[0], A.z[0], VP, vision_range, ncell2, G, count, ids2, ovf, ovfi, VB, out, out_len);
     k_vis2_pack<<<sw_blocks(ncell2 * 32, T), T, 0, st>>>(G, count, ids2, A.x[0], A.y[0], A.z[0], radii, A.species, s->P, type_col, n_type_col,
-                                                        rec2, rcol2, VB, VP);
+                                                        rec2, rcol2, s->vis_image, rimg2, VB, VP);
     const size_t smem = sizeof(double) * (size_t)(n_cones * n_cols) * VISW_THREADS;
     k_vis2_cones<4><<<sw_blocks(n * 4, VISW_THREADS), VISW_THREADS, smem, st>>>(
-        n, row_of, G, count, rec2, rcol2, ovf, ovfi, A.x[0], A.y[0], A.z[0], radii, A.species, s->P, type_col, n_type_col, s->P.n_dims,
+        n, A.n_dev, s->vis_image, rimg2, row_of, G, count, rec2, rcol2, ovf, ovfi, A.x[0], A.y[0], A.z[0], radii, A.species, s->P, type_col, n_type_col, s->P.n_dims,
         A.theta, A.q0, A.q1, A.q2, A.q3, dirs, vision_range, half_angle, n_cones, n_cols, out);
     s->launches += 3;
     SW_CUDA(cudaGetLastError());

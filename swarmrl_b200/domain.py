@@ -22,21 +22,26 @@ import numpy as np
 from . import _lib
 
 
-def slab_plan(box_x, world, rank, exchange_every, max_cut, margin=0.25):
-    """Geometry of rank `rank`'s slab.  Raises ValueError when the slabs are narrower than two halos."""
+def slab_plan(box_x, world, rank, exchange_every, max_cut, margin=0.25, halo_extra=0.0):
+    """Geometry of rank `rank`'s slab.  Raises ValueError when the slabs are narrower than two halos.
+
+    halo_extra widens the halo beyond what k steps of integration need: a per-agent observable with a finite range
+    (vision cones: `vision_range`) is exact for every particle within k * r_cut * (1 + margin) of the slab only if the
+    rank also holds everything within `halo_extra` of THOSE particles ("per slice a wider halo")."""
     world, rank, k = int(world), int(rank), int(exchange_every)
     if world < 1 or not (0 <= rank < world):
         raise ValueError("rank must lie in [0, world)")
     if k < 1:
         raise ValueError("exchange_every must be >= 1")
-    if not (max_cut > 0.0 and box_x > 0.0 and margin >= 0.0):
-        raise ValueError("box_x, max_cut must be positive and margin non-negative")
+    if not (max_cut > 0.0 and box_x > 0.0 and margin >= 0.0 and halo_extra >= 0.0):
+        raise ValueError("box_x, max_cut must be positive and margin, halo_extra non-negative")
     w = float(box_x) / world
-    h = k * float(max_cut) * (1.0 + float(margin))
+    h = k * float(max_cut) * (1.0 + float(margin)) + float(halo_extra)
     if w < 2.0 * h:
         raise ValueError(f"slab width {w:g} < 2 halos of {h:g}: lower exchange_every or the number of ranks")
     return {
-        "world": world, "rank": rank, "k": k, "box_x": float(box_x), "slab_w": w, "halo": h, "x0": rank * w,
+        "world": world, "rank": rank, "k": k, "box_x": float(box_x), "slab_w": w, "halo": h, "halo_extra": float(halo_extra),
+        "x0": rank * w,
         "left": (rank - 1) % world, "right": (rank + 1) % world,
         "image_shift_left": -1 if rank == 0 else 0,
         "image_shift_right": 1 if rank == world - 1 else 0,
@@ -132,11 +137,11 @@ class DomainSwarm:
     """This rank's slab (+ halos) of a periodic 2-D swarm; see the module docstring."""
 
     def __init__(self, box, dt, kT, seed, species, wca, *, exchange_every=8, margin=0.25, skin=0.4, world=1, rank=0,
-                 group=None, device=None, n_aux=2, max_neighbors=0, capacity_factor=1.3, persistent=True):
+                 group=None, device=None, n_aux=2, max_neighbors=0, capacity_factor=1.3, persistent=True, halo_extra=0.0):
         from .device import DeviceSwarm
 
         self.max_cut = float(np.max(np.asarray(wca["cut"], dtype=np.float64)))
-        self.plan = slab_plan(box[0], world, rank, exchange_every, self.max_cut, margin)
+        self.plan = slab_plan(box[0], world, rank, exchange_every, self.max_cut, margin, halo_extra)
         if not (0 <= n_aux <= _lib.DD_MAX_AUX):
             raise ValueError("n_aux must lie in [0, 4]")
         p = self.plan
@@ -167,7 +172,9 @@ class DomainSwarm:
         self.cap = int(cap)
         self.sets = []
         for _ in range(2):   # ping-pong halves: merge reads one, writes the other
-            s = {k: torch.zeros(self.cap, **f64) for k in _F64}
+            s = {k: torch.zeros(self.cap, **f64) for k in _F64 if k != "tqz"}
+            s["tq"] = torch.zeros((3, self.cap), **f64)   # rows x, y stay local (2-D: always 0); row z travels
+            s["tqz"] = s["tq"][2]
             s["gid"] = torch.zeros(self.cap, dtype=torch.int64, device=self.dev)
             for k in ("species", "image", "owned"):
                 s[k] = torch.zeros(self.cap, dtype=torch.int32, device=self.dev)
@@ -204,10 +211,11 @@ class DomainSwarm:
         st.species = s["species"].data_ptr()
         _lib.check(self.lib.swarm_bind_state(self.h, self.cap, C.byref(st)))   # cap = upper bound; live count below
         act = _lib.ActionsDev()
-        act.f_swim, act.tqx, act.tqy, act.tqz = s["f_swim"].data_ptr(), self.zeros.data_ptr(), self.zeros.data_ptr(), s["tqz"].data_ptr()
+        act.f_swim, act.tqx, act.tqy, act.tqz = s["f_swim"].data_ptr(), s["tq"][0].data_ptr(), s["tq"][1].data_ptr(), s["tqz"].data_ptr()
         _lib.check(self.lib.swarm_bind_actions(self.h, C.byref(act)))
         _lib.check(self.lib.swarm_bind_ids(self.h, s["gid"].data_ptr()))
         _lib.check(self.lib.swarm_bind_count(self.h, self.counts[self.cur].data_ptr()))
+        _lib.check(self.lib.swarm_bind_images(self.h, s["image"].data_ptr()))   # vision cones: same-image pairs only
         self.sw.n = self.cap
 
     @property
@@ -377,6 +385,24 @@ class DomainSwarm:
                 return self.out, None
             self.transport.all_reduce_sum(tot)
         return self.out, torch.cat([tot, tot / float(self.n_global)])
+
+    def field_eval(self, src, box_length, decay, c0, c1, scale=1.0, clip=False, init_only=False, aux_base=0, all_local=False,
+                   out=None):
+        """ConcentrationField / GradientSensing value per local slot with the history in aux channels `aux_base`,
+        `aux_base + 1` (swarm_dd_obs_field_ch); all_local=True evaluates the ghosts too (an observable that feeds the
+        policy: a ghost must take its owner's action), False the owned particles only (a reward).  Enqueue only."""
+        if self.n_aux < aux_base + 2:
+            raise ValueError("this history needs aux channels %d and %d" % (aux_base, aux_base + 1))
+        out = self.torch.empty(self.cap, dtype=self.torch.float64, device=self.dev) if out is None else out
+        a = self._dd(self.local)
+        s3 = (C.c_double * 3)(*[float(v) for v in src])
+        b2 = (C.c_double * 2)(float(box_length[0]), float(box_length[1]))
+        with self._timed("obs"):
+            _lib.check(self.lib.swarm_dd_obs_field_ch(self.h, self.cap, self.counts[self.cur].data_ptr(), C.byref(a), self.plan["x_offset"],
+                                                      self.plan["box_x"], s3, b2, int(decay), float(c0), float(c1), float(scale),
+                                                      int(bool(clip)), int(bool(init_only)), int(aux_base), int(bool(all_local)),
+                                                      out.data_ptr(), self._stream()))
+        return out
 
     def reward_means(self):
         """Global reward mean of every slice evaluated with defer=True since the last call: ONE all-reduce of the vector

@@ -224,7 +224,13 @@ class SwarmEngine(Engine):
     backend_factory = staticmethod(_default_backend)
 
     def __init__(self, md_params, n_dims=3, seed=42, out_folder=".", write_chunk_size=100, system=None,
-                 h5_group_tag=None, skin=None, persistent=True, async_writer=True):
+                 h5_group_tag=None, skin=None, persistent=True, async_writer=True, domain=None):
+        """domain: None (one GPU), or a dict for ONE swarm slab-decomposed over the ranks of a process group -- keys
+        world, rank, group (torch.distributed; None = default group), exchange_every, margin, halo_extra (the range of
+        the widest per-agent observable, e.g. `vision_range`), device, max_neighbors, capacity_factor: see
+        swarmrl_b200/domain_engine.py.  Every rank creates the same engine with the same particles and calls the same
+        methods; `get_particle_data` / `colloids` are then collectives, and rank 0 alone writes the trajectory."""
+        self._domain = None if domain is None else dict(domain)
         self.params = md_params
         self.out_folder = pathlib.Path(out_folder).resolve()
         self.seed = seed
@@ -503,7 +509,16 @@ class SwarmEngine(Engine):
         kw = dict(n_dims=self.n_dims, box=self._box_l, periodic=self.params.periodic, dt=self._time_step, kT=kT,
                   seed=int(self.seed), species=table, wca=wca, walls=walls,
                   skin=0.4 if self._skin is None else float(self._skin), persistent=self._persistent)
-        self._backend = type(self).backend_factory(**kw)
+        if self._domain is not None:
+            from .domain_engine import DomainBackend
+
+            if self._ext_force:
+                raise NotImplementedError("constant external forces are not supported on the domain-decomposed swarm")
+            if self.params.thermostat_type != "brownian":
+                raise NotImplementedError("the domain exchange carries no velocities: Brownian dynamics only")
+            self._backend = DomainBackend(**kw, **self._domain)
+        else:
+            self._backend = type(self).backend_factory(**kw)
         pos = np.array(self._pos, dtype=float).reshape(-1, 3)
         dirs = np.array(self._dir, dtype=float).reshape(-1, 3)
         if self.n_dims == 2:
@@ -541,7 +556,9 @@ class SwarmEngine(Engine):
         self.h5_time_steps_written = 0
         self._writer = None
         be = self._backend
-        if self._async_writer and be is not None and hasattr(be, "lib") and hasattr(be, "h") and self.n_colloids > 0:
+        self._writes_files = getattr(be, "rank", 0) == 0   # decomposed swarm: every rank takes the (collective) snapshot, rank 0 writes
+        if self._async_writer and be is not None and hasattr(be, "lib") and hasattr(be, "h") and self.n_colloids > 0 \
+                and not getattr(be, "is_domain", False):
             # CUDA backend: device snapshot ring -> pinned host -> writer thread (swarmrl_b200/trajectory.py); the hot
             # loop only enqueues.  `traj_holder` is the writer's pending chunk (filled by its thread).
             from .trajectory import AsyncTrajectoryWriter
@@ -558,6 +575,8 @@ class SwarmEngine(Engine):
             self._npz_chunks = 0
             return
         self._h5py = h5py
+        if not self._writes_files:
+            return
         n = self.n_colloids
         with h5py.File(self.h5_filename.as_posix(), "a") as f:
             g = f.require_group(self.h5_group_tag)
@@ -592,6 +611,9 @@ class SwarmEngine(Engine):
             return
         n_new = len(self.traj_holder["Times"])
         if n_new == 0:
+            return
+        if not getattr(self, "_writes_files", True):
+            self.h5_time_steps_written += n_new
             return
         if self._h5py is not None:
             with self._h5py.File(self.h5_filename, "a") as f:

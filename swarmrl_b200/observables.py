@@ -119,7 +119,13 @@ class _FieldHistory:
     def empty(self):
         return self.hist is None
 
-    def init_from(self, swarm, box_length, mask=None):
+    def init_from(self, swarm, box_length, mask=None, all_local=True):
+        if getattr(swarm, "is_domain", False):
+            # decomposed swarm: the history travels with the particle in the exchange record (domain_engine.py);
+            # all_local = the ghosts are evaluated too (an observable), False = owned particles only (a reward)
+            self.hist = swarm.new_history(box_length, all_local)
+            self.valid = np.ones(swarm.n, dtype=bool) if mask is None else np.asarray(mask, dtype=bool)
+            return
         torch = swarm.torch
         b = torch.tensor([float(v) for v in box_length], dtype=torch.float64, device=swarm.dev)
         self.hist = (swarm.pos[:, : swarm.n] / b[:, None]).contiguous()
@@ -140,7 +146,7 @@ class ConcentrationField(Observable):
     @property
     def _historic_positions(self):
         """dict view {str(id): normalised position}, as the reference stores it."""
-        if self._history.empty():
+        if self._history.empty() or not hasattr(self._history.hist, "cpu"):
             return {}
         h = self._history.hist.cpu().numpy().T
         return {str(i): h[i] for i in range(h.shape[0]) if self._history.valid[i]}

@@ -57,14 +57,14 @@ class GradientSensing(Task):
 
     @property
     def _historic_positions(self):
-        if self._history.empty():
+        if self._history.empty() or not hasattr(self._history.hist, "cpu"):
             return {}
         h = self._history.hist.cpu().numpy().T
         return {str(i): h[i] for i in range(h.shape[0]) if self._history.valid[i]}
 
     def initialize(self, colloids):
         swarm, _ = resolve_swarm(colloids)
-        self._history.init_from(swarm, self.box_length, mask=(swarm.ptype_host == int(self.particle_type)))
+        self._history.init_from(swarm, self.box_length, mask=(swarm.ptype_host == int(self.particle_type)), all_local=False)
 
     def change_source(self, new_source):
         """Stores the source un-normalised, as the reference does (gradient_sensing.py:81-90)."""
