@@ -326,9 +326,8 @@ class Rollout:
         self.step_idx += STEPS_PER_SLICE
         obs = d.obs_vision(self.row_of, self.rows, VISION["range"], VISION["half_angle"], VISION["n_cones"], self.radii,
                            self.type_col, 1)
-        rew, _, _ = d.obs_field(self.row_of, self.rows, (0.5, 0.5, 0.0), (BOX,) * 3, self.hist, decay=1, c0=1.0, c1=-1.0,
-                                scale=10.0, clip=True, want_dist=False)
-        mean = d.reduce_mean(rew)
+        # GradientSensing reward and its mean: one launch (swarm_obs_field_mean)
+        rew, mean = d.obs_field_mean(self.row_of, self.rows, (0.5, 0.5, 0.0), (BOX,) * 3, self.hist, 1, 1.0, -1.0, scale=10.0, clip=True)
         return obs, mean
 
     def slice_resident(self, k, time_run=False):

@@ -248,6 +248,25 @@ int swarm_dd_merge(swarm_t *s, const swarm_dd_geom_t *g, int64_t n_old, const in
                    const double *recv_left_dev, const double *recv_right_dev, int64_t cap_new,
                    const swarm_dd_arrays_t *new_loc, int32_t *counts8_dev, void *stream);
 
+/* ---- the exchange over peer memory (NVLink / NVSwitch P2P stores) instead of NCCL send / recv ---------------------
+ * No reference counterpart (see above).  Every rank allocates ONE exchange region (4 flags + two parities of its two
+ * receive buffers) and publishes its 64-byte CUDA IPC handle to its slab neighbours, which open it once.  Per exchange
+ * `epoch` = 1, 2, 3, ...: swarm_dd_pack (local send buffers) -> swarm_dd_push (the live records go into the neighbours'
+ * receive buffers of parity epoch & 1 with remote stores, then a system-scope release of flag = epoch) ; the receiver
+ * enqueues swarm_dd_wait (one thread polls its own two flags) in front of swarm_dd_merge, which reads
+ * swarm_dd_peer_recv(my_region, g, side, epoch & 1).  A flag that does not arrive within 20 s sets the sticky error bit 8
+ * of counts8_dev[3] instead of hanging.  All ranks must use the same geometry (buffer capacity and n_aux). */
+int64_t swarm_dd_peer_region_bytes(const swarm_dd_geom_t *g);
+int swarm_dd_peer_alloc(int32_t device, const swarm_dd_geom_t *g, void **region_out, unsigned char handle64_out[64]);
+int swarm_dd_peer_open(int32_t device, const unsigned char handle64[64], void **region_out);
+int swarm_dd_peer_close(void *region);
+int swarm_dd_peer_free(void *region);
+/* side 0: the buffer filled through my left face, 1: through my right face */
+double *swarm_dd_peer_recv(void *region, const swarm_dd_geom_t *g, int32_t side, int32_t parity);
+int swarm_dd_push(swarm_t *s, const swarm_dd_geom_t *g, const double *send_left_dev, const double *send_right_dev,
+                  void *left_neighbour_region, void *right_neighbour_region, uint64_t epoch, void *stream);
+int swarm_dd_wait(swarm_t *s, void *my_region, uint64_t epoch, int32_t *counts8_dev, void *stream);
+
 /* swarm_obs_field for the owned particles of a sub-domain, on global unfolded coordinates
  * x_global = x_local + x_offset + image * box_x; history (p_prev) in aux channels 0, 1; out_dev[n],
  * 0 for ghosts.  init_only = 1 just seeds the history. */

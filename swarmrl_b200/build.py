@@ -41,15 +41,16 @@ def needs_build() -> bool:
     return any(d.stat().st_mtime > t for d in deps)
 
 
-def build(force: bool = False, verbose: bool = False, timing: bool = False) -> pathlib.Path:
+def build(force: bool = False, verbose: bool = False, timing: bool = False, variant: bool = False) -> pathlib.Path:
     """timing=True builds libswarm_b200_timing.so with -DSW_TIMING (clock64 phase counters in the resident
-    kernel; select it with SWARM_B200_LIB=<path>) -- a profiling variant, never the default."""
-    if timing:
+    kernel; select it with SWARM_B200_LIB=<path>) -- a profiling variant, never the default.  variant=True builds
+    libswarm_b200_var_<tag>.so with the -D flags of the command line only (A/B runs of a compile-time choice)."""
+    if timing or variant:
         extra = [a for a in sys.argv if a.startswith("-D")]
         tag = "".join(a[2:].lower() for a in extra)
-        out = PKG / f"libswarm_b200_timing{('_' + tag) if tag else ''}.so"
+        out = PKG / (f"libswarm_b200_timing{('_' + tag) if tag else ''}.so" if timing else f"libswarm_b200_var_{tag}.so")
         srcs = [str(CSRC / s) for s in SOURCES if (CSRC / s).exists()]
-        res = subprocess.run([_nvcc(), *NVCC_FLAGS, "-DSW_TIMING", *extra, "-o", str(out), *srcs], capture_output=True, text=True)
+        res = subprocess.run([_nvcc(), *NVCC_FLAGS, *(["-DSW_TIMING"] if timing else []), *extra, "-o", str(out), *srcs], capture_output=True, text=True)
         if res.returncode != 0:
             raise RuntimeError("nvcc failed:\n" + res.stderr[-4000:])
         return out
@@ -67,5 +68,5 @@ def build(force: bool = False, verbose: bool = False, timing: bool = False) -> p
 
 
 if __name__ == "__main__":
-    p = build(force="--force" in sys.argv, verbose=True, timing="--timing" in sys.argv)
+    p = build(force="--force" in sys.argv, verbose=True, timing="--timing" in sys.argv, variant="--variant" in sys.argv)
     print("built", p)

@@ -16,6 +16,7 @@
 // ping-pong state, owned flag recomputed).  Migration needs nothing extra: a particle that left the
 // slab lies in a send band, the receiver finds it inside its own slab and owns it from then on.
 #include "swarm_common.cuh"
+#include <cstring>
 
 #define DD_FIXED 8  // x, y, theta, f_swim, tqz, gid, species, image
 
@@ -196,6 +197,159 @@ extern "C" int swarm_dd_merge(swarm_t *s, const swarm_dd_geom_t *g, int64_t n_ol
                                                              dd_arrays(new_loc), counts8_dev);
   k_dd_finish<<<1, 1, 0, st>>>(counts8_dev);
   s->launches += 2;
+  SW_CUDA(cudaGetLastError());
+  return SWARM_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Exchange over PEER MEMORY (NVLink / NVSwitch P2P stores) instead of NCCL send/recv.
+//
+// Every rank owns one exchange region, allocated here with cudaMalloc and exported with cudaIpcGetMemHandle:
+//     [ 4 flags, 256 bytes apart: left[0], left[1], right[0], right[1] ] [ recv_left[0] ][ recv_left[1] ][ recv_right[0] ][ recv_right[1] ]
+// (two parities of each receive buffer).  Exchange e (1, 2, 3, ...) uses parity e & 1:
+//   sender   k_dd_push: the LIVE records of its packed send buffers (count x fields doubles, not the buffer's capacity)
+//            go straight into the neighbours' receive buffers with coalesced remote stores; every CTA fences at system
+//            scope and takes a ticket, the last one stores flag = e with release semantics at system scope;
+//   receiver k_dd_wait: ONE thread polls its own two flags (local memory) with acquire loads at system scope; the merge
+//            kernel behind it in the stream then reads the records from local memory.
+// No collective, no proxy thread, no rendezvous: the data path of an exchange is two kernels on the sender's stream and a
+// one-thread kernel on the receiver's.  Two parities suffice: a sender overwrites parity p at exchange e + 2 after its own
+// merge of e + 1, which waited for the neighbour's push of e + 1, which the neighbour issued behind its merge of e.
+// A flag that does not arrive within SW_DD_WAIT_NS sets error bit 8 instead of hanging the GPU.
+// ---------------------------------------------------------------------------------------------------------------------
+#define SW_DD_FLAG_STRIDE 256
+#define SW_DD_WAIT_NS 20000000000ULL   // 20 s
+
+__device__ __forceinline__ unsigned long long dd_globaltimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
+// blockIdx.y = face (0: my send_left -> the left neighbour's recv_right, 1: my send_right -> the right neighbour's recv_left)
+__global__ void __launch_bounds__(256) k_dd_push(const double *send_left, const double *send_right, double *peer_of_left, double *peer_of_right,
+                                                  unsigned long long *flag_of_left, unsigned long long *flag_of_right, unsigned long long epoch,
+                                                  long long cap, int nfields, unsigned int *tickets) {
+  const int face = blockIdx.y;
+  const double *src = face ? send_right : send_left;
+  double *dst = face ? peer_of_right : peer_of_left;
+  const unsigned long long raw = *(const unsigned long long *)src;
+  const long long cnt = raw > (unsigned long long)cap ? cap : (long long)raw;
+  const long long total = cnt * nfields;
+  for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+    const long long f = t / cnt, j = t - f * cnt;
+    dst[1 + f * cap + j] = src[1 + f * cap + j];
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) *(unsigned long long *)dst = raw;   // the record count (beyond cap = overflow, seen by the merge)
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int t = atomicAdd(&tickets[face], 1u);
+    if (t == gridDim.x - 1) {
+      tickets[face] = 0u;
+      __threadfence_system();
+      unsigned long long *flag = face ? flag_of_right : flag_of_left;
+      asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(flag), "l"(epoch) : "memory");
+    }
+  }
+}
+
+__global__ void k_dd_wait(const unsigned long long *flag_left, const unsigned long long *flag_right, unsigned long long epoch, int *counts) {
+  const unsigned long long t0 = dd_globaltimer();
+  for (int side = 0; side < 2; ++side) {
+    const unsigned long long *f = side ? flag_right : flag_left;
+    for (;;) {
+      unsigned long long v;
+      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(f) : "memory");
+      if (v == epoch) break;
+      if (dd_globaltimer() - t0 > SW_DD_WAIT_NS) { atomicOr(&counts[3], 8); return; }   // sticky: the neighbour never delivered
+      __nanosleep(200);
+    }
+  }
+}
+
+extern "C" int64_t swarm_dd_peer_region_bytes(const swarm_dd_geom_t *g) {
+  if (!g) return -1;
+  return 4 * SW_DD_FLAG_STRIDE + 4 * (int64_t)sizeof(double) * swarm_dd_buffer_doubles(g);
+}
+
+extern "C" int swarm_dd_peer_alloc(int32_t device, const swarm_dd_geom_t *g, void **region_out, unsigned char handle64_out[64]) {
+  if (!g || !region_out || !handle64_out) { sw_set_error("bad arguments"); return SWARM_ERR_INVALID; }
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "the IPC handle travels as 64 bytes");
+  SW_CUDA(cudaSetDevice(device));
+  const size_t bytes = (size_t)swarm_dd_peer_region_bytes(g);
+  void *p = nullptr;
+  SW_CUDA(cudaMalloc(&p, bytes));
+  SW_CUDA(cudaMemset(p, 0, bytes));
+  SW_CUDA(cudaDeviceSynchronize());
+  cudaIpcMemHandle_t h;
+  cudaError_t e = cudaIpcGetMemHandle(&h, p);
+  if (e != cudaSuccess) { cudaFree(p); sw_set_error(cudaGetErrorString(e)); return SWARM_ERR_CUDA; }
+  memcpy(handle64_out, &h, 64);
+  *region_out = p;
+  return SWARM_OK;
+}
+
+extern "C" int swarm_dd_peer_open(int32_t device, const unsigned char handle64[64], void **region_out) {
+  if (!handle64 || !region_out) { sw_set_error("bad arguments"); return SWARM_ERR_INVALID; }
+  SW_CUDA(cudaSetDevice(device));
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, 64);
+  SW_CUDA(cudaIpcOpenMemHandle(region_out, h, cudaIpcMemLazyEnablePeerAccess));
+  return SWARM_OK;
+}
+
+extern "C" int swarm_dd_peer_close(void *region) {
+  if (region) SW_CUDA(cudaIpcCloseMemHandle(region));
+  return SWARM_OK;
+}
+
+extern "C" int swarm_dd_peer_free(void *region) {
+  if (region) SW_CUDA(cudaFree(region));
+  return SWARM_OK;
+}
+
+static inline unsigned long long *dd_flag(void *region, int side, int parity) {
+  return (unsigned long long *)((char *)region + (size_t)(2 * side + parity) * SW_DD_FLAG_STRIDE);
+}
+static inline double *dd_recv(void *region, const swarm_dd_geom_t *g, int side, int parity) {
+  return (double *)((char *)region + 4 * SW_DD_FLAG_STRIDE) + (size_t)(2 * side + parity) * (size_t)swarm_dd_buffer_doubles(g);
+}
+
+extern "C" double *swarm_dd_peer_recv(void *region, const swarm_dd_geom_t *g, int32_t side, int32_t parity) {
+  if (!region || !g) return nullptr;
+  return dd_recv(region, g, side ? 1 : 0, parity & 1);
+}
+
+extern "C" int swarm_dd_push(swarm_t *s, const swarm_dd_geom_t *g, const double *send_left_dev, const double *send_right_dev,
+                             void *left_neighbour_region, void *right_neighbour_region, uint64_t epoch, void *stream) {
+  if (!s || !send_left_dev || !send_right_dev || !left_neighbour_region || !right_neighbour_region || epoch == 0) {
+    sw_set_error("bad arguments"); return SWARM_ERR_INVALID;
+  }
+  int rc = dd_check(g);
+  if (rc) return rc;
+  SW_CUDA(cudaSetDevice(s->cfg.device));
+  if (!s->dd_tickets) {
+    SW_CUDA(cudaMalloc((void **)&s->dd_tickets, 256));
+    SW_CUDA(cudaMemset(s->dd_tickets, 0, 256));
+  }
+  const int par = (int)(epoch & 1ULL);
+  // my left face enters the left neighbour through ITS right face, and the other way round
+  k_dd_push<<<dim3(32, 2), 256, 0, (cudaStream_t)stream>>>(send_left_dev, send_right_dev, dd_recv(left_neighbour_region, g, 1, par),
+                                                           dd_recv(right_neighbour_region, g, 0, par), dd_flag(left_neighbour_region, 1, par),
+                                                           dd_flag(right_neighbour_region, 0, par), (unsigned long long)epoch, (long long)g->cap,
+                                                           DD_FIXED + g->n_aux, s->dd_tickets);
+  s->launches += 1;
+  SW_CUDA(cudaGetLastError());
+  return SWARM_OK;
+}
+
+extern "C" int swarm_dd_wait(swarm_t *s, void *my_region, uint64_t epoch, int32_t *counts8_dev, void *stream) {
+  if (!s || !my_region || !counts8_dev || epoch == 0) { sw_set_error("bad arguments"); return SWARM_ERR_INVALID; }
+  SW_CUDA(cudaSetDevice(s->cfg.device));
+  const int par = (int)(epoch & 1ULL);
+  k_dd_wait<<<1, 1, 0, (cudaStream_t)stream>>>(dd_flag(my_region, 0, par), dd_flag(my_region, 1, par), (unsigned long long)epoch, counts8_dev);
+  s->launches += 1;
   SW_CUDA(cudaGetLastError());
   return SWARM_OK;
 }

@@ -856,6 +856,7 @@ extern "C" int swarm_destroy(swarm_t *s) {
   if (s->red_scratch) cudaFree(s->red_scratch);
   if (s->field_scratch) cudaFree(s->field_scratch);
   if (s->vis_buf) cudaFree(s->vis_buf);
+  if (s->dd_tickets) cudaFree(s->dd_tickets);
   delete s;
   return SWARM_OK;
 }

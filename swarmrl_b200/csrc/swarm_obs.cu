@@ -824,6 +824,140 @@ __global__ void __launch_bounds__(VISW_THREADS) k_vis2_cones(long long n, const 
   }
 }
 
+// k_vis2_cones with a CANDIDATE QUEUE (round 2).  In k_vis2_cones a warp walks the stencil cells of its 32 / GS observers
+// in lock step and runs the whole candidate evaluation (square root, two divisions, the cone search) in every iteration
+// in which ANY of its lanes holds a particle inside the range -- nearly always, although only one candidate in three is
+// (pi r^2 of the 9 r^2 the stencil covers) and a cell of ~3 particles fills 3 of an observer's 4 lanes.  Here the walk
+// only SCREENS: squared distance against range^2 (1 + 1e-9) -- a superset of the exact test, which visw_candidate
+// repeats -- and appends the survivors to the observer's queue in shared memory (position by warp ballot: the order,
+// and with it the summation order, is fixed).  The expensive evaluation then runs on full queues: every pass gives each
+// lane of a group one candidate, ~3 passes per warp instead of ~9.  Same cones and weights as k_vis2_cones, candidate by
+// candidate; the sums associate differently (<= 1 ulp per term).
+#define VISQ_CAP 32
+template <int GS>
+__global__ void __launch_bounds__(VISW_THREADS) k_vis2_cones_q(long long n, const int *n_dev, const int *image, const int *rimg,
+                                                               const int *row_of, const VisGrid *G, const int *count,
+                                                               const double4 *rec, const int *rcol, const Vis2Ovf *ovf, const int2 *ovf_items,
+                                                               const double *x, const double *y, const double *z, const double *radii,
+                                                               const int *species, const __grid_constant__ DevParams P, const int *type_col,
+                                                               int n_type_col, int n_dims, const double *theta, const double *q0,
+                                                               const double *q1, const double *q2, const double *q3, const double *dirs,
+                                                               double range, double half_angle, int n_cones, int n_cols, double *out) {
+  extern __shared__ double sacc[];   // [nacc][VISW_THREADS], then the queues [VISW_THREADS / GS][VISQ_CAP]
+  const int nacc = n_cones * n_cols;
+  int *qu = reinterpret_cast<int *>(sacc + (size_t)nacc * VISW_THREADS) + (threadIdx.x / GS) * VISQ_CAP;
+  const int lane = threadIdx.x & (GS - 1);
+  const int gshift = (threadIdx.x & 31) & ~(GS - 1);   // first lane of this observer's group within the warp
+  long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) / GS;
+  const bool in_range = i < vis_live(n, n_dev);
+  if (!in_range) i = n - 1;
+  const int row = in_range ? row_of[i] : -1;
+  for (int a = 0; a < nacc; ++a) sacc[a * VISW_THREADS + threadIdx.x] = 0.0;
+  const double xi = x[i], yi = y[i], zi = z[i];
+  const int img_i = image ? image[i] : 0;
+  double ex, ey, ez;
+  if (dirs) { ex = dirs[i]; ey = dirs[n + i]; ez = dirs[2 * n + i]; }
+  else if (n_dims == 2) { sincos(theta[i], &ey, &ex); ez = 0.0; }
+  else {
+    double a = q0[i], b = q1[i], c = q2[i], d = q3[i];
+    ex = 2 * (b * d + a * c); ey = 2 * (c * d - a * b); ez = a * a - b * b - c * c + d * d;
+  }
+  {
+    double en = sqrt(ex * ex + ey * ey + ez * ez);
+    ex /= en; ey /= en; ez /= en;
+  }
+  const double cone_w = half_angle * 2.0 / (double)n_cones;
+  __shared__ double rim[VIS_MAX_ACC + 1], crim[VIS_MAX_ACC + 1];
+  for (int t = threadIdx.x; t <= n_cones; t += blockDim.x) {
+    rim[t] = -half_angle + (double)t * half_angle * 2.0 / (double)n_cones;
+    crim[t] = cos(rim[t]);
+  }
+  __syncthreads();
+  const int ncx = G->nc[0], ncy = G->nc[1], ncz = G->nc[2];
+  const int cx = vis_coord(xi, G->lo[0], G->inv_cs, ncx);
+  const int cy = vis_coord(yi, G->lo[1], G->inv_cs, ncy);
+  const int cz = vis_coord(zi, G->lo[2], G->inv_cs, ncz);
+  const double r2max = range * range * (1.0 + 1e-9);
+  int qn = 0;   // entries in this group's queue: the same number in its GS lanes
+  // one pass: every group gives each of its lanes one queued candidate (fewer when it holds fewer)
+  auto pass = [&]() {
+    const int take = qn < GS ? qn : GS;
+    if (lane < take) {
+      const int en = qu[qn - take + lane];
+      if (en >= 0) {
+        const double2 r01 = __ldg(reinterpret_cast<const double2 *>(&rec[en]));
+        const double2 r23 = __ldg(reinterpret_cast<const double2 *>(&rec[en]) + 1);
+        visw_candidate(r01.x, r01.y, r23.x, r23.y, __ldg(&rcol[en]), xi, yi, zi, ex, ey, ez, range, half_angle, cone_w, n_cones, n_cols,
+                       rim, crim, sacc);
+      } else {
+        const int j = ~en;
+        const int t = P.sp_type[species[j]];
+        const int col = (t >= 0 && t < n_type_col) ? type_col[t] : -1;
+        visw_candidate(x[j], y[j], z[j], radii[j], col, xi, yi, zi, ex, ey, ez, range, half_angle, cone_w, n_cones, n_cols, rim, crim, sacc);
+      }
+    }
+    qn -= take;
+  };
+  auto push = [&](bool ok, int en) {
+    const unsigned int b = (__ballot_sync(0xffffffffu, ok) >> gshift) & ((1u << GS) - 1u);
+    if (ok) qu[qn + __popc(b & ((1u << lane) - 1u))] = en;
+    qn += __popc(b);
+    __syncwarp();
+    if (__any_sync(0xffffffffu, qn > VISQ_CAP - GS)) { pass(); __syncwarp(); }   // a queue could not take another round: one pass for all
+  };
+  // the stencil walk is warp-uniform (27 offsets, each cell's count padded to the warp's maximum): the ballot needs all lanes
+  for (int dz = (ncz > 1 ? -1 : 0); dz <= (ncz > 1 ? 1 : 0); ++dz)
+    for (int dy = -1; dy <= 1; ++dy)
+      for (int dx = -1; dx <= 1; ++dx) {
+        const int xx = cx + dx, yy = cy + dy, zz = cz + dz;
+        const bool valid = row >= 0 && xx >= 0 && xx < ncx && yy >= 0 && yy < ncy && zz >= 0 && zz < ncz;
+        const long long c = valid ? ((long long)zz * ncy + yy) * ncx + xx : 0;
+        int m = valid ? __ldg(&count[c]) : 0;
+        if (m > VIS2_CAP) m = VIS2_CAP;
+        const int mw = (int)__reduce_max_sync(0xffffffffu, (unsigned int)m);
+        for (int k0 = 0; k0 < mw; k0 += GS) {
+          const int k = k0 + lane;
+          bool ok = false;
+          const long long o = c * VIS2_CAP + k;
+          if (k < m) {
+            const double2 r01 = __ldg(reinterpret_cast<const double2 *>(&rec[o]));
+            const double rz = __ldg(reinterpret_cast<const double *>(&rec[o]) + 2);
+            const double ddx = r01.x - xi, ddy = r01.y - yi, ddz = rz - zi;
+            const double d2 = ddx * ddx + ddy * ddy + ddz * ddz;
+            ok = d2 > 0.0 && d2 <= r2max && __ldg(&rcol[o]) >= 0;
+            if (ok && image && __ldg(&rimg[o]) != img_i) ok = false;
+          }
+          push(ok, (int)o);
+        }
+      }
+  // particles beyond the capacity of their cell (dense clusters): one list, empty in all but pathological packings
+  const int no = ovf->n;
+  for (int k0 = 0; k0 < no; k0 += GS) {
+    const int k = k0 + lane;
+    bool ok = false;
+    int j = 0;
+    if (k < no && row >= 0) {
+      const int2 it = ovf_items[k];
+      const int ox = it.x % ncx, oy = (it.x / ncx) % ncy, oz = it.x / (ncx * ncy);
+      j = it.y;
+      if (abs(ox - cx) <= 1 && abs(oy - cy) <= 1 && abs(oz - cz) <= 1 && !(image && image[j] != img_i)) {
+        const double ddx = x[j] - xi, ddy = y[j] - yi, ddz = z[j] - zi;
+        const double d2 = ddx * ddx + ddy * ddy + ddz * ddz;
+        ok = d2 > 0.0 && d2 <= r2max;
+      }
+    }
+    push(ok, ~j);
+  }
+  while (__any_sync(0xffffffffu, qn > 0)) pass();
+  __syncwarp();
+  for (int a = 0; a < nacc; ++a) {
+    double v = sacc[a * VISW_THREADS + threadIdx.x];
+#pragma unroll
+    for (int off = GS / 2; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+    if (lane == 0 && row >= 0) out[(long long)row * nacc + a] = v;
+  }
+}
+
 // ---- concentration field / gradient sensing ---------------------------------------------------
 __device__ __forceinline__ double decay_eval(int kind, double c0, double c1, double d) {
   switch (kind) {
@@ -1251,9 +1385,14 @@ extern "C" int swarm_obs_vision(swarm_t *s, const int32_t *row_of, int64_t rows,
     k_vis2_pack<<<sw_blocks(ncell2 * 32, T), T, 0, st>>>(G, count, ids2, A.x[0], A.y[0], A.z[0], radii, A.species, s->P, type_col, n_type_col,
                                                         rec2, rcol2, s->vis_image, rimg2, VB, VP);
     const size_t smem = sizeof(double) * (size_t)(n_cones * n_cols) * VISW_THREADS;
-    k_vis2_cones<4><<<sw_blocks(n * 4, VISW_THREADS), VISW_THREADS, smem, st>>>(
-        n, A.n_dev, s->vis_image, rimg2, row_of, G, count, rec2, rcol2, ovf, ovfi, A.x[0], A.y[0], A.z[0], radii, A.species, s->P, type_col, n_type_col, s->P.n_dims,
-        A.theta, A.q0, A.q1, A.q2, A.q3, dirs, vision_range, half_angle, n_cones, n_cols, out);
+    if (getenv("SWARM_B200_VIS_NOQUEUE"))
+      k_vis2_cones<4><<<sw_blocks(n * 4, VISW_THREADS), VISW_THREADS, smem, st>>>(
+          n, A.n_dev, s->vis_image, rimg2, row_of, G, count, rec2, rcol2, ovf, ovfi, A.x[0], A.y[0], A.z[0], radii, A.species, s->P, type_col, n_type_col, s->P.n_dims,
+          A.theta, A.q0, A.q1, A.q2, A.q3, dirs, vision_range, half_angle, n_cones, n_cols, out);
+    else
+      k_vis2_cones_q<4><<<sw_blocks(n * 4, VISW_THREADS), VISW_THREADS, smem + sizeof(int) * (VISW_THREADS / 4) * VISQ_CAP, st>>>(
+          n, A.n_dev, s->vis_image, rimg2, row_of, G, count, rec2, rcol2, ovf, ovfi, A.x[0], A.y[0], A.z[0], radii, A.species, s->P, type_col, n_type_col, s->P.n_dims,
+          A.theta, A.q0, A.q1, A.q2, A.q3, dirs, vision_range, half_angle, n_cones, n_cols, out);
     s->launches += 3;
     SW_CUDA(cudaGetLastError());
     return SWARM_OK;

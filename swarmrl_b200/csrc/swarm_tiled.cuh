@@ -71,7 +71,11 @@ struct TileArgs {
                             // every flag of the previous launch (launch counter << 15; a launch runs < 2^15 epochs)
 };
 
-// Split CTA barrier of the step loop (mbarrier in shared memory): a warp ARRIVES as soon as its new positions are in
+// -DSW_TILE_MBAR (A/B build, NOT the default): split CTA barrier of the step loop.  Measured on the same box against the
+// plain __syncthreads at the end of the iteration (profiles/r02_mbar_ab.txt): 0.455-0.482 ms per 100-step launch with the
+// mbarrier against 0.445-0.459 ms without -- the polling loop of 23 warps costs more issue slots than the overlap of a
+// slow warp's pair phase with the others' local work wins, so __syncthreads stays.
+// Split CTA barrier (mbarrier in shared memory): a warp ARRIVES as soon as its new positions are in
 // shared memory and WAITS only after the particle-local work of the next step.  With __syncthreads at the end of the
 // iteration every warp waited for the slowest warp's pair phase AND local work; now a warp waits only if another warp
 // has not finished its pair phase by the time the waiter has finished its own local work, and the latency-bound pair
@@ -668,15 +672,23 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_tiled(const __grid_cons
       if (exported) rim_write(&(G.rim + nxt * G.rim_stride)[slot], G.flag0 + e + 1u, xi, yi);
     }
     SW_TICK(1);   // pair forces + update
+#ifdef SW_TILE_MBAR
     if constexpr (!HALO) tile_mbar_arrive_warp(&s_stepbar);   // this warp's positions of the next step are in shared memory
+#endif
     if (actv && !last) local_inputs(R.step0 + (u64)(s + 1));   // step s+1's particle-local work: the rim records travel meanwhile
     // the next iteration is a synchronisation point: it republishes and reloads the halo behind its grid barrier
     const bool next_sync = (since + 1 >= K) || last;
     if constexpr (HALO) if (!next_sync) tile_halo_load((G.rim + nxt * G.rim_stride), G.flag0 + e + 1u, htab, hlist, s_nh, hlane, &sx[nxt][SW_TILE_MAXP], &sy[nxt][SW_TILE_MAXP]);
+#ifdef SW_TILE_MBAR
     if constexpr (HALO) tile_mbar_arrive_warp(&s_stepbar);    // the halo of the next step is in shared memory
+#endif
     SW_TICK(4);   // particle-local work of the next step / halo warp: the neighbours' records
+#ifndef SW_TILE_MBAR
+    __syncthreads();   // the positions of the next step -- tile and halo -- are in shared memory
+#else
     tile_mbar_wait(&s_stepbar, stepbar_parity);   // the positions of the next step -- tile and halo -- are in shared memory
     stepbar_parity ^= 1u;
+#endif
     SW_TICK(5);
     ++s; ++since; ++e;
   }

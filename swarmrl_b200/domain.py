@@ -137,8 +137,18 @@ class DomainSwarm:
     """This rank's slab (+ halos) of a periodic 2-D swarm; see the module docstring."""
 
     def __init__(self, box, dt, kT, seed, species, wca, *, exchange_every=8, margin=0.25, skin=0.4, world=1, rank=0,
-                 group=None, device=None, n_aux=2, max_neighbors=0, capacity_factor=1.3, persistent=True, halo_extra=0.0):
+                 group=None, device=None, n_aux=2, max_neighbors=0, capacity_factor=1.3, persistent=True, halo_extra=0.0,
+                 peer="auto"):
+        """peer: move the halo records with P2P stores into the neighbours' memory (swarm_dd_push / swarm_dd_wait, CUDA IPC)
+        instead of NCCL send / recv.  "auto" = when the process group is nccl (one GPU per rank on one node); True forces
+        it (ranks sharing one GPU over gloo: the tests); False keeps torch.distributed.  SWARM_B200_DD_PEER=0/1 overrides."""
+        import os
+
         from .device import DeviceSwarm
+
+        env = os.environ.get("SWARM_B200_DD_PEER")
+        self._peer_req = peer if env is None else (env not in ("0", "", "false"))
+        self.peer = None   # set by _alloc: dict(region, left, right) when the peer path is active
 
         self.max_cut = float(np.max(np.asarray(wca["cut"], dtype=np.float64)))
         self.plan = slab_plan(box[0], world, rank, exchange_every, self.max_cut, margin, halo_extra)
@@ -193,6 +203,30 @@ class DomainSwarm:
         self.counts_host = torch.zeros((2, 8), dtype=torch.int32).pin_memory()
         self.out = torch.zeros(self.cap, **f64)
         _lib.check(self.lib.swarm_reserve(self.h, self.cap))
+        self._peer_setup()
+
+    def _peer_setup(self):
+        """Exchange region of this rank + the two neighbours' regions (CUDA IPC); see csrc/swarm_dd.cu."""
+        t, p = self.transport, self.plan
+        want = self._peer_req
+        if want == "auto":
+            want = t.world > 1 and t.backend == "nccl"
+        if not want or t.world < 2:
+            return
+        region = C.c_void_p()
+        handle = C.create_string_buffer(64)
+        _lib.check(self.lib.swarm_dd_peer_alloc(self.sw.device_index, C.byref(self.geom), C.byref(region), handle))
+        mine = (bytes(handle.raw), int(self.geom.cap), int(self.geom.n_aux))
+        every = [None] * t.world
+        t.dist.all_gather_object(every, mine, group=t.group)    # also the barrier between "zeroed" and "first push"
+        if any((c, a) != mine[1:] for _, c, a in every):
+            raise RuntimeError("the ranks of a domain-decomposed swarm must use the same exchange-buffer geometry")
+        opened = {}
+        for nb in {p["left"], p["right"]}:
+            r = C.c_void_p()
+            _lib.check(self.lib.swarm_dd_peer_open(self.sw.device_index, every[nb][0], C.byref(r)))
+            opened[nb] = r
+        self.peer = dict(region=region, left=opened[p["left"]], right=opened[p["right"]], opened=opened)
 
     def _dd(self, s):
         a = _lib.DDArrays()
@@ -300,9 +334,19 @@ class DomainSwarm:
         a_old, a_new = self._dd(old), self._dd(new)
         _lib.check(self.lib.swarm_dd_pack(self.h, C.byref(g), self.cap, c_old.data_ptr(), C.byref(a_old),
                                           b["send_l"].data_ptr(), b["send_r"].data_ptr(), self._stream()))
-        self.transport.exchange(b["send_l"], b["send_r"], b["recv_l"], b["recv_r"])
+        if self.peer is not None:
+            # records straight into the neighbours' memory (P2P stores + a flag); my own arrive the same way
+            pr, epoch = self.peer, self.exchanges + 1
+            _lib.check(self.lib.swarm_dd_push(self.h, C.byref(g), b["send_l"].data_ptr(), b["send_r"].data_ptr(), pr["left"], pr["right"],
+                                              epoch, self._stream()))
+            _lib.check(self.lib.swarm_dd_wait(self.h, pr["region"], epoch, c_new.data_ptr(), self._stream()))
+            recv_l = self.lib.swarm_dd_peer_recv(pr["region"], C.byref(g), 0, epoch & 1)
+            recv_r = self.lib.swarm_dd_peer_recv(pr["region"], C.byref(g), 1, epoch & 1)
+        else:
+            self.transport.exchange(b["send_l"], b["send_r"], b["recv_l"], b["recv_r"])
+            recv_l, recv_r = b["recv_l"].data_ptr(), b["recv_r"].data_ptr()
         _lib.check(self.lib.swarm_dd_merge(self.h, C.byref(g), self.cap, c_old.data_ptr(), C.byref(a_old),
-                                           b["recv_l"].data_ptr(), b["recv_r"].data_ptr(), self.cap, C.byref(a_new),
+                                           recv_l, recv_r, self.cap, C.byref(a_new),
                                            c_new.data_ptr(), self._stream()))
         self.cur ^= 1
         self.since_exchange = 0
@@ -318,7 +362,7 @@ class DomainSwarm:
         err = int(self.counts_host[0, 3]) | int(self.counts_host[1, 3])
         if err:
             why = [m for bit, m in ((1, "exchange buffer overflow"), (2, "an owned particle outran the halo"),
-                                    (4, "local capacity exceeded")) if err & bit]
+                                    (4, "local capacity exceeded"), (8, "a slab neighbour never delivered its halo records")) if err & bit]
             raise OverflowError("domain exchange failed: " + ", ".join(why))
         self.n, self.n_owned = int(self.counts_host[self.cur, 0]), int(self.counts_host[self.cur, 1])
         # a Verlet-list overflow halts the integrator kernels of this rank (every later launch returns at once) while
@@ -417,4 +461,18 @@ class DomainSwarm:
         return v / float(self.n_global)
 
     def close(self):
+        pr, self.peer = self.peer, None
+        if pr is not None and getattr(self.sw, "h", None):
+            # neighbours may still be reading / writing: meet first when the process group is alive; without one (interpreter
+            # exit) only the imported mappings are dropped and the own region is left to the driver's process teardown
+            self.torch.cuda.synchronize(self.dev)
+            dist = self.transport.dist
+            alive = dist.is_initialized()
+            if alive:
+                dist.barrier(group=self.transport.group)
+            for r in pr["opened"].values():
+                self.lib.swarm_dd_peer_close(r)
+            if alive:
+                dist.barrier(group=self.transport.group)
+                self.lib.swarm_dd_peer_free(pr["region"])
         self.sw.close()

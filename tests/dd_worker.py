@@ -57,7 +57,8 @@ def main():
     st = d.stats()
     assert not st.overflow
     gid, x, y, th = d.owned_host()
-    np.savez(f"{out}.{rank}.npz", gid=gid, x=x, y=y, theta=th, means=np.array(means), exchanges=d.exchanges)
+    np.savez(f"{out}.{rank}.npz", gid=gid, x=x, y=y, theta=th, means=np.array(means), exchanges=d.exchanges,
+             peer=int(d.peer is not None))
     dist.barrier()
     dist.destroy_process_group()
 

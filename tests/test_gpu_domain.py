@@ -52,10 +52,15 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _run_ranks(world, tmp_path, kT, backend="gloo"):
+def _run_ranks(world, tmp_path, kT, backend="gloo", peer=None):
+    import os
+
     port, out = _free_port(), str(tmp_path / "dd")
+    env = dict(os.environ)
+    if peer is not None:
+        env["SWARM_B200_DD_PEER"] = "1" if peer else "0"
     procs = [subprocess.Popen([sys.executable, str(HERE / "dd_worker.py"), str(r), str(world), str(port), out, backend, repr(kT)],
-                              stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True) for r in range(world)]
+                              stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env) for r in range(world)]
     logs = [p.communicate(timeout=600)[0] for p in procs]
     for p, lg in zip(procs, logs):
         assert p.returncode == 0, lg[-3000:]
@@ -96,15 +101,29 @@ def test_ranks_sharing_one_gpu_match_single_swarm(tmp_path, world):
     assert min(owned) > 0.5 * W.CASE["n"] / world
 
 
-def test_nccl_two_gpus_match_single_swarm(tmp_path):
+@pytest.mark.parametrize("world", [2, 3])
+def test_peer_memory_exchange_between_ranks_sharing_one_gpu(tmp_path, world):
+    """The exchange over peer memory (swarm_dd_push / swarm_dd_wait: remote stores into the neighbour's CUDA-IPC region and
+    a system-scope flag) instead of torch.distributed: same trajectories.  Two processes on ONE device map each other's
+    memory exactly as two GPUs do over NVLink; the device time-slices between them, so this is slow but exact."""
+    import dd_worker as W
+
+    parts = _run_ranks(world, tmp_path, KT_300, peer=True)
+    _check(parts, _single_gpu_reference(KT_300), W.CASE["n"])
+    assert all(int(q["peer"]) == 1 for q in parts)
+
+
+@pytest.mark.parametrize("peer", [True, False])
+def test_nccl_two_gpus_match_single_swarm(tmp_path, peer):
     import torch
 
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     import dd_worker as W
 
-    parts = _run_ranks(2, tmp_path, KT_300, backend="nccl")
+    parts = _run_ranks(2, tmp_path, KT_300, backend="nccl", peer=peer)
     _check(parts, _single_gpu_reference(KT_300), W.CASE["n"])
+    assert all(int(q["peer"]) == int(peer) for q in parts)
 
 
 def test_halo_too_thin_is_rejected():
