@@ -49,6 +49,39 @@ __device__ __forceinline__ void bd2d_pair(const DevParams &P, double xi, double 
   }
 }
 
+// -DSW_TILE_PAIR4 (A/B build, NOT the default; profiles/r02_pair4_ab.txt: 0.42-0.59 ms per launch against 0.385-0.494 ms
+// with bd2d_pair -- the step is short of issue slots, and a warp with ONE contact now issues four chains).
+// Four Verlet entries at once.  bd2d_pair evaluates entry after entry, each behind its own branch: a warp then runs the WCA
+// chain (reciprocal + Newton steps + two corrected quotients, ~18 dependent fp64 operations, ~160 cycles) once for every
+// entry index at which ANY of its lanes is in contact -- two to three times per step in a clustering swarm, one after the
+// other, with only ~6 warps per scheduler to cover the latency.  Here the four cut-off tests come first, then ONE branch
+// (any of my four entries in contact) guards four INDEPENDENT chains that the scheduler interleaves; an entry that is
+// not in contact runs its chain on r2 = 1 and is not accumulated.  The accumulation keeps the entry order and touches
+// the same values with the same operations as bd2d_pair, so the force is the same bit for bit.
+__device__ __forceinline__ void bd2d_pair4(const DevParams &P, double xi, double yi, int ti, const int en[4], const double xj[4],
+                                           const double yj[4], int nvalid, double &Fx, double &Fy) {
+  double dx[4], dy[4], r2[4];
+  bool in[4];
+  int tj[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    tj[k] = en[k] >> SW_TYPE_SHIFT;
+    dx[k] = sw_min_image(xi - xj[k], P.box[0], P.inv_box[0], P.periodic[0]);
+    dy[k] = sw_min_image(yi - yj[k], P.box[1], P.inv_box[1], P.periodic[1]);
+    r2[k] = sw_r2(dx[k], dy[k], 0.0);
+    const double cut = P.wca_cut[ti][tj[k]];
+    in[k] = (k < nvalid) && r2[k] < __dmul_rn(cut, cut) && r2[k] > 0.0;
+  }
+  if (in[0] || in[1] || in[2] || in[3]) {
+    double fac[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) fac[k] = swm_wca_factor(in[k] ? r2[k] : 1.0, P.wca_sigma[ti][tj[k]], P.wca_eps[ti][tj[k]]);
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      if (in[k]) { Fx = fma(fac[k], dx[k], Fx); Fy = fma(fac[k], dy[k], Fy); }
+  }
+}
+
 // forces that depend on the particle alone: walls + swim + external (added AFTER the pair forces,
 // in the oracle's order: walls, swim, external)
 struct Bd2dSelf { double wx, wy, sx, sy; };

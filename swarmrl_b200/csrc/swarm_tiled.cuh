@@ -641,9 +641,14 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_tiled(const __grid_cons
 #pragma unroll
       for (int k = 0; k < SW_RES_NBR; ++k) fetch(nb[k], xj[k], yj[k]);
       double Fx = 0.0, Fy = 0.0;
+#ifndef SW_TILE_PAIR4
 #pragma unroll
       for (int k = 0; k < SW_RES_NBR; ++k)
         if (k < cnt) bd2d_pair(P, xi, yi, ti, nb[k] >> SW_TYPE_SHIFT, xj[k], yj[k], Fx, Fy);
+#else
+      static_assert(SW_RES_NBR == 4, "bd2d_pair4 takes the four register-resident entries");
+      bd2d_pair4(P, xi, yi, ti, nb, xj, yj, cnt, Fx, Fy);
+#endif
       for (int k0 = SW_RES_NBR; k0 < cnt; k0 += 4) {
         int en4[4];
         double xe[4], ye[4];
@@ -657,9 +662,13 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_tiled(const __grid_cons
         }
 #pragma unroll
         for (int u = 0; u < 4; ++u) fetch(en4[u], xe[u], ye[u]);
+#ifndef SW_TILE_PAIR4
 #pragma unroll
         for (int u = 0; u < 4; ++u)
           if (k0 + u < cnt) bd2d_pair(P, xi, yi, ti, en4[u] >> SW_TYPE_SHIFT, xe[u], ye[u], Fx, Fy);
+#else
+        bd2d_pair4(P, xi, yi, ti, en4, xe, ye, cnt - k0, Fx, Fy);
+#endif
       }
       // walls, swim, external: added after the pair forces, in the oracle's order
       if (P.walls) { Fx += swx[ptid]; Fy += swy[ptid]; }
