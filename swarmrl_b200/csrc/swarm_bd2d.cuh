@@ -302,7 +302,7 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_resident(const __grid_c
         swm_sincos(th, ey, ex);
         sf = bd2d_self_forces(P, ti, xi, yi, ex, ey, fsw);
         if (NOISE) {
-          if (PIPE) swm_boxmuller_xyt(rw, g0, g1, g3);
+          if (PIPE) swm_boxmuller_xyt(rw, ((R.step0 + (u64)(s + 1)) & 1ULL) != 0ULL, g0, g1, g3);
           else swm_gaussians_xyt(P.rk, pid, R.step0 + (u64)(s + 1), g0, g1, g3);
         }
       }
@@ -575,11 +575,21 @@ __global__ void __launch_bounds__(SW_ENV_THREADS) k_bd2d_env(const __grid_consta
   unsigned mask = 0u;
   double xr = xi, yr = yi;
   bool need = true;
+  double g3_keep = 0.0;     // cosine normal of the last even step's rotational pair
+  bool g3_have = false;
   for (long long s = 0; s < R.n_steps; ++s) {
     double ex, ey, g0 = 0.0, g1 = 0.0, g3 = 0.0;
-    swm_sincos(th, ey, ex);
+    if (NOISE) {
+      // normals and director in one pass (the bits of swm_gaussians_xyt + swm_sincos); the rotational normal of an odd
+      // step is the cosine kept from the even step before it
+      const u64 step = R.step0 + (u64)s;
+      if ((step & 1ULL) && g3_have) swm_step_inputs<true>(P.rk, pid, step, th, g0, g1, g3, g3_keep, ey, ex);
+      else swm_step_inputs<false>(P.rk, pid, step, th, g0, g1, g3, g3_keep, ey, ex);
+      g3_have = !(step & 1ULL);
+    } else {
+      swm_sincos(th, ey, ex);
+    }
     const Bd2dSelf sf = bd2d_self_forces(P, ti, xi, yi, ex, ey, fsw);
-    if (NOISE) swm_gaussians_xyt(P.rk, pid, R.step0 + (u64)s, g0, g1, g3);
     double Fx = 0.0, Fy = 0.0;
     if (prefilter) {
       // A Verlet list in one register: bit j of `mask` = agent j was within cut-off + skin of this agent when the

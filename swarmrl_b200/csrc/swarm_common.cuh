@@ -230,19 +230,25 @@ __device__ __forceinline__ void sw_philox4x32_10_rk(unsigned int c0, unsigned in
   }
   out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
 }
-__device__ __forceinline__ void sw_noise_words_rk(const unsigned int *rk, u64 id, u64 step, u64 stream, u64 r[4]) {
+// ONE block of a draw: words 2 blk, 2 blk + 1 of sw_noise_words (blk = 0, 1) -- a Box-Muller pair needs exactly one block
+__device__ __forceinline__ void sw_noise_block_rk(const unsigned int *rk, u64 id, u64 step, u64 stream, unsigned int blk, u64 &w0, u64 &w1) {
   const unsigned int c0 = (unsigned int)step, c1 = (unsigned int)(step >> 32), c2 = (unsigned int)id;
-  const unsigned int c3 = ((unsigned int)((id >> 32) & 0xFFFFFFULL) << 8) | ((unsigned int)(stream & 0x7FULL) << 1);
-  unsigned int a[4], b[4];
+  const unsigned int c3 = ((unsigned int)((id >> 32) & 0xFFFFFFULL) << 8) | ((unsigned int)(stream & 0x7FULL) << 1) | blk;
+  unsigned int a[4];
   sw_philox4x32_10_rk(c0, c1, c2, c3, rk, a);
-  sw_philox4x32_10_rk(c0, c1, c2, c3 | 1u, rk, b);
-#pragma unroll
-  for (int k = 0; k < 4; ++k) r[k] = ((u64)a[k] << 32) | (u64)b[k];
+  w0 = ((u64)a[0] << 32) | (u64)a[1];
+  w1 = ((u64)a[2] << 32) | (u64)a[3];
+}
+__device__ __forceinline__ void sw_noise_words_rk(const unsigned int *rk, u64 id, u64 step, u64 stream, u64 r[4]) {
+  sw_noise_block_rk(rk, id, step, stream, 0u, r[0], r[1]);
+  sw_noise_block_rk(rk, id, step, stream, 1u, r[2], r[3]);
 }
 
 // The thermostat's four 64-bit noise words of (seed, particle id, step, stream) -- oracle: orc_noise_words.  Two
 // Philox4x32-10 blocks b = 0, 1: key = (seed lo, seed hi), counter = (step lo, step hi, id lo,
-// id[32..55] << 8 | stream << 1 | b); word k = block0[k] << 32 | block1[k].  The key is the SEED, uniform over the
+// id[32..55] << 8 | stream << 1 | b); words 2b, 2b + 1 = block b's (out[0] << 32 | out[1]), (out[2] << 32 | out[3]) -- each
+// Box-Muller pair (words 0,1 and 2,3) comes from ONE block, so a consumer of one pair draws one block (the 2-D Brownian
+// step shares its rotational pair between two steps: swm_gaussians_xyt).  The key is the SEED, uniform over the
 // swarm, so its ten-round schedule costs nothing per particle; the 20 rounds are ~85 instructions where the
 // Philox4x64-10 block of round 1 (64-bit multiplies out of 32-bit ones) took 248.  Stream map: DESIGN.md section 3.
 __host__ __device__ __forceinline__ void sw_noise_words(u64 seed, u64 id, u64 step, u64 stream, u64 r[4]) {
@@ -252,8 +258,8 @@ __host__ __device__ __forceinline__ void sw_noise_words(u64 seed, u64 id, u64 st
   unsigned int a[4], b[4];
   sw_philox4x32_10(c0, c1, c2, c3, k0, k1, a);
   sw_philox4x32_10(c0, c1, c2, c3 | 1u, k0, k1, b);
-#pragma unroll
-  for (int k = 0; k < 4; ++k) r[k] = ((u64)a[k] << 32) | (u64)b[k];
+  r[0] = ((u64)a[0] << 32) | (u64)a[1]; r[1] = ((u64)a[2] << 32) | (u64)a[3];
+  r[2] = ((u64)b[0] << 32) | (u64)b[1]; r[3] = ((u64)b[2] << 32) | (u64)b[3];
 }
 
 __device__ __forceinline__ double sw_u01(u64 r) {

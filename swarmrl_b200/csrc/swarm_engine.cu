@@ -300,7 +300,11 @@ __device__ __forceinline__ bool phase_step(const DevParams &P, const DevArrays &
     } else {
       const double gt1 = P.sp_gt[sp][1], gt2 = P.sp_gt[sp][2], gr0 = P.sp_gr[sp][0];
       double g[4] = {0.0, 0.0, 0.0, 0.0};
-      if (NOISE) swm_gaussians(P.seed, pid, step, 0, g);
+      if (NOISE) {
+        swm_gaussians(P.seed, pid, step, 0, g);
+        // the rotational normal of an odd step is the cosine of the even step's pair 1 (swm_gaussians_xyt, swarm_math.cuh)
+        if (step & 1ULL) { double ge[4]; swm_gaussians(P.seed, pid, step - 1ULL, 0, ge); g[3] = ge[2]; }
+      }
       double vx, vy;
       if (gt1 == gt2) {
         vx = F[0] / gt2; vy = F[1] / gt2;

@@ -112,33 +112,6 @@ __device__ __forceinline__ void swm_sincos2pi(u64 r, double &sn, double &cs) {
   sn = s0; cs = c0;
 }
 
-// three of the four normals of (seed, id, step, stream 0): g0, g1 (pair 0) and g3 (sine of pair 1) --
-// what a 2-D Brownian step consumes (x, y, theta).  Same values as sw_gaussians()[0,1,3] to ~1e-15.
-__device__ __forceinline__ void swm_gaussians_xyt(u64 seed, u64 id, u64 step, double &g0, double &g1, double &g3) {
-  u64 r[4];
-  sw_noise_words(seed, id, step, 0ULL, r);
-  const double m0 = swm_sqrt(-2.0 * swm_log01(swm_u01(r[0])));
-  const double m1 = swm_sqrt(-2.0 * swm_log01(swm_u01(r[2])));
-  double s0, c0, s1, c1;
-  swm_sincos2pi(r[1], s0, c0);
-  swm_sincos2pi(r[3], s1, c1);
-  g0 = m0 * c0; g1 = m0 * s0; g3 = m1 * s1;
-}
-
-// The same three normals from Philox words drawn earlier (swm_philox_xyt): the resident kernel draws the words of
-// step s+1 in the shadow of step s's neighbour loads and transforms them in the shadow of the grid barrier.
-__device__ __forceinline__ void swm_philox_xyt(u64 seed, u64 id, u64 step, u64 r[4]) {
-  sw_noise_words(seed, id, step, 0ULL, r);
-}
-__device__ __forceinline__ void swm_boxmuller_xyt(const u64 r[4], double &g0, double &g1, double &g3) {
-  const double m0 = swm_sqrt(-2.0 * swm_log01(swm_u01(r[0])));
-  const double m1 = swm_sqrt(-2.0 * swm_log01(swm_u01(r[2])));
-  double s0, c0, s1, c1;
-  swm_sincos2pi(r[1], s0, c0);
-  swm_sincos2pi(r[3], s1, c1);
-  g0 = m0 * c0; g1 = m0 * s0; g3 = m1 * s1;
-}
-
 // (sin, cos)(theta) of the 2-D director.  theta / (2 pi) with a two-term reciprocal (product error recovered by one
 // fma), quadrant by the round-to-nearest magic constant, then the polynomials of swm_sincos2pi on t in [-1/8, 1/8]
 // turns: <= 1.2e-16 absolute against mpmath for |theta| <= 1e6 (tools/gen_coeffs.py), no slow-path call in the hot
@@ -176,14 +149,36 @@ __device__ __forceinline__ void swm_uniforms(u64 seed, u64 id, u64 step, u64 str
   for (int k = 0; k < 4; ++k) u[k] = swm_u01(r[k]) - 0.5;
 }
 
-// the same draws with the key schedule of the seed precomputed (DevParams.rk, a constant-bank operand): the hot kernels
+// ---------------------------------------------------------------------------------------------
+// The normals of a 2-D Brownian step (oracle: orc_bd2d_normals).  A step consumes three: two for the translation, one for
+// the rotation -- but a Box-Muller pair yields two, so a draw of four would throw one away every step.  Instead
+//   translation of step s : pair 0 (block 0) of the draw (seed, id, s, stream 0):       g0 = m0 cos, g1 = m0 sin
+//   rotation of step s    : pair 1 (block 1) of the draw of the EVEN step s & ~1:       its sine on the even step,
+//                                                                                       its cosine on the odd one
+// (sine and cosine of one pair are independent standard normals), so two steps cost three blocks and three pairs
+// instead of four and four: ~60 of a step's ~700 instructions.  A kernel that keeps the cosine from the even step
+// (k_bd2d_tiled, k_bd2d_env) takes the short path on the odd step; one that does not simply draws block 1 of step s - 1
+// again -- the values are the same.  The key schedule of the seed is precomputed (DevParams.rk, a constant-bank operand).
+// ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ void swm_philox_xyt(const unsigned int *rk, u64 id, u64 step, u64 r[4]) {
-  sw_noise_words_rk(rk, id, step, 0ULL, r);
+  sw_noise_block_rk(rk, id, step, 0ULL, 0u, r[0], r[1]);
+  sw_noise_block_rk(rk, id, step & ~1ULL, 0ULL, 1u, r[2], r[3]);
+}
+// the three normals from words drawn earlier (the resident kernel draws the words of step s+1 in the shadow of step s's
+// neighbour loads and transforms them in the shadow of the grid barrier)
+__device__ __forceinline__ void swm_boxmuller_xyt(const u64 r[4], bool odd, double &g0, double &g1, double &g3) {
+  const double m0 = swm_sqrt(-2.0 * swm_log01(swm_u01(r[0])));
+  const double m1 = swm_sqrt(-2.0 * swm_log01(swm_u01(r[2])));
+  double s0, c0, s1, c1;
+  swm_sincos2pi(r[1], s0, c0);
+  swm_sincos2pi(r[3], s1, c1);
+  const double gs = m1 * s1, gc = m1 * c1;
+  g0 = m0 * c0; g1 = m0 * s0; g3 = odd ? gc : gs;
 }
 __device__ __forceinline__ void swm_gaussians_xyt(const unsigned int *rk, u64 id, u64 step, double &g0, double &g1, double &g3) {
   u64 r[4];
-  sw_noise_words_rk(rk, id, step, 0ULL, r);
-  swm_boxmuller_xyt(r, g0, g1, g3);
+  swm_philox_xyt(rk, id, step, r);
+  swm_boxmuller_xyt(r, (step & 1ULL) != 0ULL, g0, g1, g3);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -202,15 +197,21 @@ __device__ __forceinline__ void swm_quadrant(unsigned q, double ps, double pc, d
   sn = s0; cs = c0;
 }
 
+// SHORT = the odd step of a pair whose cosine normal `g3_keep` was kept from the even step: block 0 and ONE Box-Muller
+// pair only.  Otherwise both blocks: g3 = the sine (even step) or the cosine (odd step) of pair 1 of the even step's draw,
+// and g3_keep receives the cosine for the odd step that follows an even one.
+template <bool SHORT>
 __device__ __forceinline__ void swm_step_inputs(const unsigned int *rk, u64 id, u64 step, double th, double &g0, double &g1,
-                                                double &g3, double &sn, double &cs) {
-  u64 r[4];
-  sw_noise_words_rk(rk, id, step, 0ULL, r);
-  // ---- arguments of the three (sin, cos) pairs: t in [-1/8, 1/8] turns, quadrant q --------------------------------
-  double t[3];
-  unsigned q[3];
+                                                double &g3, double &g3_keep, double &sn, double &cs) {
+  constexpr int NP = SHORT ? 1 : 2;   // Box-Muller pairs evaluated
+  u64 r[4] = {0ULL, 0ULL, 0ULL, 0ULL};
+  sw_noise_block_rk(rk, id, step, 0ULL, 0u, r[0], r[1]);
+  if constexpr (!SHORT) sw_noise_block_rk(rk, id, step & ~1ULL, 0ULL, 1u, r[2], r[3]);
+  // ---- arguments of the (sin, cos) pairs: t in [-1/8, 1/8] turns, quadrant q; chain NP is the director ---------------
+  double t[NP + 1];
+  unsigned q[NP + 1];
 #pragma unroll
-  for (int i = 0; i < 2; ++i) {
+  for (int i = 0; i < NP; ++i) {
     const u64 k = r[2 * i + 1] >> 12;
     q[i] = (unsigned)((k + (1ULL << 49)) >> 50);
     t[i] = fma((double)q[i], -0.25, swm_u01(r[2 * i + 1]));
@@ -223,33 +224,33 @@ __device__ __forceinline__ void swm_step_inputs(const unsigned int *rk, u64 id, 
     const double bigc = 6755399441055744.0;
     const double qs = fma(4.0, turns, bigc);
     const double qd = qs - bigc;
-    q[2] = (unsigned)__double2loint(qs);
-    t[2] = big ? 0.0 : fma(qd, -0.25, turns) + rem;
+    q[NP] = (unsigned)__double2loint(qs);
+    t[NP] = big ? 0.0 : fma(qd, -0.25, turns) + rem;
   }
   // ---- polynomials, coefficient by coefficient ---------------------------------------------------------------------
-  double z[3], ps[3], pc[3];
+  double z[NP + 1], ps[NP + 1], pc[NP + 1];
 #pragma unroll
-  for (int i = 0; i < 3; ++i) { z[i] = t[i] * t[i]; ps[i] = SWM_SIN[8]; pc[i] = SWM_COS[9]; }
+  for (int i = 0; i <= NP; ++i) { z[i] = t[i] * t[i]; ps[i] = SWM_SIN[8]; pc[i] = SWM_COS[9]; }
 #pragma unroll
   for (int k = 7; k >= 0; --k) {
     const double c = SWM_SIN[k];
 #pragma unroll
-    for (int i = 0; i < 3; ++i) ps[i] = fma(ps[i], z[i], c);
+    for (int i = 0; i <= NP; ++i) ps[i] = fma(ps[i], z[i], c);
   }
 #pragma unroll
-  for (int i = 0; i < 3; ++i) ps[i] *= t[i];
+  for (int i = 0; i <= NP; ++i) ps[i] *= t[i];
 #pragma unroll
   for (int k = 8; k >= 0; --k) {
     const double c = SWM_COS[k];
 #pragma unroll
-    for (int i = 0; i < 3; ++i) pc[i] = fma(pc[i], z[i], c);
+    for (int i = 0; i <= NP; ++i) pc[i] = fma(pc[i], z[i], c);
   }
-  // ---- the two logarithms (swm_log01), side by side ----------------------------------------------------------------
-  double lg[2];
+  // ---- the logarithms (swm_log01), side by side ----------------------------------------------------------------------
+  double lg[NP];
   {
-    double s2[2], zz[2], p[2], ed[2];
+    double s2[NP], zz[NP], p[NP], ed[NP];
 #pragma unroll
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < NP; ++i) {
       const double u = swm_u01(r[2 * i]);
       int hi = __double2hiint(u), lo = __double2loint(u);
       int e = (hi >> 20) - 1023;
@@ -265,22 +266,30 @@ __device__ __forceinline__ void swm_step_inputs(const unsigned int *rk, u64 id, 
     for (int k = 9; k >= 0; --k) {
       const double c = SWM_LOG[k];
 #pragma unroll
-      for (int i = 0; i < 2; ++i) p[i] = fma(p[i], zz[i], c);
+      for (int i = 0; i < NP; ++i) p[i] = fma(p[i], zz[i], c);
     }
 #pragma unroll
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < NP; ++i) {
       const double rr = fma(s2[i] * zz[i], p[i], ed[i] * SWM_K[2]);
       lg[i] = fma(ed[i], SWM_K[1], fma(2.0, s2[i], rr));
     }
   }
-  const double m0 = swm_sqrt(-2.0 * lg[0]), m1 = swm_sqrt(-2.0 * lg[1]);
-  double s0, c0, s1, c1;
+  const double m0 = swm_sqrt(-2.0 * lg[0]);
+  double s0, c0;
   swm_quadrant(q[0], ps[0], pc[0], s0, c0);
-  swm_quadrant(q[1], ps[1], pc[1], s1, c1);
-  g0 = m0 * c0; g1 = m0 * s0; g3 = m1 * s1;
-  (void)c1;
+  g0 = m0 * c0; g1 = m0 * s0;
+  if constexpr (SHORT) {
+    g3 = g3_keep;
+  } else {
+    const double m1 = swm_sqrt(-2.0 * lg[NP - 1]);
+    double s1, c1;
+    swm_quadrant(q[NP - 1], ps[NP - 1], pc[NP - 1], s1, c1);
+    const double gs = m1 * s1, gc = m1 * c1;
+    g3 = (step & 1ULL) ? gc : gs;
+    g3_keep = gc;
+  }
   if (big) sincos(th, &sn, &cs);
-  else swm_quadrant(q[2], ps[2], pc[2], sn, cs);
+  else swm_quadrant(q[NP], ps[NP], pc[NP], sn, cs);
 }
 
 // all four normals with the fast kernels (parity hook / 3-D)

@@ -43,9 +43,9 @@
 #define SW_TILE_HT 1024                     // halo hash table: remote slots this tile's lists point at (load factor <= 1/2)
 #define SW_TILE_W (SW_TILE_MAXP + SW_TILE_HT)   // positions per buffer: the tile, then its halo
 #define SW_TILE_RAW 0x08000000              // entry flag: remote slot that did not fit the halo table (read directly)
-// dynamic shared memory in doubles: x, y double-buffered over tile + halo; 7 per-thread columns; the list cache and the
+// dynamic shared memory in doubles: x, y double-buffered over tile + halo; 8 per-thread columns; the list cache and the
 // hash table / compact list as ints
-#define SW_TILE_DSM_DOUBLES (4 * SW_TILE_W + 7 * SW_TILE_MAXP + (SW_TILE_SNBR * SW_TILE_MAXP + 2 * SW_TILE_HT) / 2)
+#define SW_TILE_DSM_DOUBLES (4 * SW_TILE_W + 8 * SW_TILE_MAXP + (SW_TILE_SNBR * SW_TILE_MAXP + 2 * SW_TILE_HT) / 2)
 
 // A rim record is four 8-byte words, each {flag (low half), 32 bits of data (high half)}: x lo, x hi, y lo, y hi -- the
 // layout of NCCL's LL protocol.  An aligned 8-byte store is single-copy atomic, so a word whose flag matches carries
@@ -295,7 +295,8 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_tiled(const __grid_cons
   double *sxr = col, *syr = col + SW_TILE_MAXP, *sthr = col + 2 * SW_TILE_MAXP;  // checkpoint = state at the last rebuild
   double *sfx = col + 3 * SW_TILE_MAXP, *sfy = col + 4 * SW_TILE_MAXP;           // constant external force
   double *swx = col + 5 * SW_TILE_MAXP, *swy = col + 6 * SW_TILE_MAXP;           // wall force of the coming step
-  int *snb = (int *)(col + 7 * SW_TILE_MAXP);    // [SW_TILE_SNBR][SW_TILE_MAXP]: list entries beyond the register-resident ones
+  double *sgk = col + 7 * SW_TILE_MAXP;                                          // cosine normal kept from the even step (local_inputs)
+  int *snb = (int *)(col + 8 * SW_TILE_MAXP);    // [SW_TILE_SNBR][SW_TILE_MAXP]: list entries beyond the register-resident ones
   int *htab = snb + SW_TILE_SNBR * SW_TILE_MAXP; // [SW_TILE_HT]: remote slot at each halo position, -1 = free
   int *hlist = htab + SW_TILE_HT;                // [s_nh]: the occupied halo positions, compact
   __shared__ int s_nh;                           // halo records of this tile
@@ -388,8 +389,17 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_tiled(const __grid_cons
 
   // ---- particle-local inputs of the first step ---------------------------------------------------------------------
   double g0 = 0.0, g1 = 0.0, g3 = 0.0, ex = 1.0, ey = 0.0;
+  bool keep_ok = false;   // sgk[ptid] holds the cosine normal of the even step just before `step` (uniform over the grid)
   auto local_inputs = [&](u64 step) {
-    if (NOISE) swm_step_inputs(P.rk, pid, step, th, g0, g1, g3, ey, ex);
+    if (NOISE) {
+      // an odd step right after its even partner takes the short path (one Philox block, one Box-Muller pair); anything
+      // else -- even steps, a launch that starts on an odd step, the first step after a rollback -- draws both.  The kept
+      // normal lives in this thread's shared-memory slot, not in a register pair the pair phase would have to spill.
+      double keep = 0.0;
+      if (keep_ok && (step & 1ULL)) { keep = sgk[ptid]; swm_step_inputs<true>(P.rk, pid, step, th, g0, g1, g3, keep, ey, ex); }
+      else { swm_step_inputs<false>(P.rk, pid, step, th, g0, g1, g3, keep, ey, ex); sgk[ptid] = keep; }
+      keep_ok = !(step & 1ULL);
+    }
     else swm_sincos(th, ey, ex);
     if (P.walls) {
       const Bd2dSelf sf = bd2d_self_forces(P, ti, xi, yi, ex, ey, fsw);
@@ -520,6 +530,7 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_tiled(const __grid_cons
             since = 0; need = false;
           }
           s = s_ck;
+          keep_ok = false;   // the kept normal belongs to the step pair that was abandoned
           viol = false; dmax2 = 0.0;
           if (actv) {
             sx[cur][ptid] = xi; sy[cur][ptid] = yi;

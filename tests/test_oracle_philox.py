@@ -51,7 +51,7 @@ def test_philox4x32_random123_known_answers(ctr, key, want):
 
 def test_noise_words_layout():
     """key = (seed lo, seed hi); counter = (step lo, step hi, id lo, id[32..55] << 8 | stream << 1 | block);
-    word k = block0[k] << 32 | block1[k]."""
+    words 2b, 2b + 1 = block b's (out[0] << 32 | out[1]), (out[2] << 32 | out[3]) -- one block per Box-Muller pair."""
     rng = np.random.default_rng(5)
     for _ in range(50):
         seed, step = (int(v) for v in rng.integers(0, 2**63, 2, dtype=np.uint64) * 2 + 1)
@@ -61,7 +61,7 @@ def test_noise_words_layout():
         c3 = (((pid >> 32) & 0xFFFFFF) << 8) | (stream << 1)
         a = _philox4x32_py([step & 0xFFFFFFFF, step >> 32, pid & 0xFFFFFFFF, c3], key)
         b = _philox4x32_py([step & 0xFFFFFFFF, step >> 32, pid & 0xFFFFFFFF, c3 | 1], key)
-        want = [(x << 32) | y for x, y in zip(a, b)]
+        want = [(a[0] << 32) | a[1], (a[2] << 32) | a[3], (b[0] << 32) | b[1], (b[2] << 32) | b[3]]
         assert [int(v) for v in oracle.noise_words(seed, pid, step, stream)] == want
     # neighbouring ids / steps / streams never share a word
     seen = set()
