@@ -356,7 +356,7 @@ __device__ __forceinline__ void sw_prefetch_l2(const void *p) { asm volatile("pr
 template <bool NOISE>
 __device__ __forceinline__ bool bd2d_step_stream(const DevParams &P, const DevArrays &A, const Bd2dSpecies *S, int cur, u64 step,
                                                  bool last, long long i, long long i_next, double lim2, bool have_g,
-                                                 double pg0, double pg1, double pg3) {
+                                                 double pg0, double pg1, double pg3, bool keep_ok) {
   const int nxt = cur ^ 1;
   // every per-particle input is requested up front: without __restrict__ the compiler keeps each load
   // behind the stores of the previous particle and next to its first use, which serialised four DRAM
@@ -396,13 +396,30 @@ __device__ __forceinline__ bool bd2d_step_stream(const DevParams &P, const DevAr
       if (k0 + u < cnt) bd2d_pair(P, xi, yi, ti, en[u] >> SW_TYPE_SHIFT, xj[u], yj[u], Fx, Fy);
   }
   double ex, ey;
+  double g0 = pg0, g1 = pg1, g3 = pg3;  // drawn behind the previous step's barrier for the thread's first particle
+#ifndef SW_STREAM_SEPARATE_INPUTS
+  // normals and director in one pass (swm_step_inputs: the bits of swm_gaussians_xyt + swm_sincos, coefficient loads
+  // shared between the chains): 8 M particles on one GPU 41.05 -> 39.31 ms per slice (profiles/r02_stream_old_new_ab.txt)
+  if (NOISE && !have_g) {
+#ifndef SW_STREAM_NO_KEEP
+    // the cosine normal of the even step waits in the particle's slot of A.gkeep (8 M particles: 39.45 -> 37.34 ms per slice)
+    double keep = 0.0;
+    if (keep_ok && (step & 1ULL)) { keep = A.gkeep[i]; swm_step_inputs<true>(P.rk, pid, step, th, g0, g1, g3, keep, ey, ex); }
+    else { swm_step_inputs<false>(P.rk, pid, step, th, g0, g1, g3, keep, ey, ex); if (!(step & 1ULL)) A.gkeep[i] = keep; }
+#else
+    double keep;
+    swm_step_inputs<false>(P.rk, pid, step, th, g0, g1, g3, keep, ey, ex);
+#endif
+  }
+  else swm_sincos(th, ey, ex);
+#else
   swm_sincos(th, ey, ex);
+  if (NOISE && !have_g) swm_gaussians_xyt_keep(P.rk, pid, step, keep_ok, &A.gkeep[i], g0, g1, g3);   // keep_ok: step - 1 ran in this launch
+#endif
   const Bd2dSelf sf = bd2d_self_forces(P, ti, xi, yi, ex, ey, fsw);
   Fx += sf.wx; Fy += sf.wy;
   Fx += sf.sx; Fy += sf.sy;
   if (A.fex) { Fx += fxe; Fy += fye; }
-  double g0 = pg0, g1 = pg1, g3 = pg3;  // drawn behind the previous step's barrier for the thread's first particle
-  if (NOISE && !have_g) swm_gaussians_xyt(P.rk, pid, step, g0, g1, g3);
   const double dt = P.dt;
   double xn = xi, yn = yi, thn = th, vx, vy;
   const double w = swm_div_r(tqz, c.gr0, c.r_gr0);
@@ -465,7 +482,7 @@ __global__ void __launch_bounds__(SW_STREAM_THREADS, SW_STREAM_MINB) k_bd2d_stre
   const long long i0 = lo + threadIdx.x;
   __shared__ double s_g[SW_STREAM_PRE][3][SW_STREAM_THREADS];  // a thread only touches its own column
   bool have_g = false;
-  auto step_barrier = [&](bool moved, bool draw, u64 next_step) -> bool {
+  auto step_barrier = [&](bool moved, bool draw, u64 next_step, bool keep_ok) -> bool {
     const int any = __syncthreads_or(moved);
     if (threadIdx.x == 0) grid_arrive64(&ctl->bar64, epoch, any != 0);
     have_g = false;
@@ -475,7 +492,7 @@ __global__ void __launch_bounds__(SW_STREAM_THREADS, SW_STREAM_MINB) k_bd2d_stre
         const long long i = i0 + k * gstride;
         if (i >= hi) break;
         double a, b, c;
-        swm_gaussians_xyt(P.rk, sw_pid(A, i), next_step, a, b, c);
+        swm_gaussians_xyt_keep(P.rk, sw_pid(A, i), next_step, keep_ok, &A.gkeep[i], a, b, c);
         s_g[k][0][threadIdx.x] = a; s_g[k][1][threadIdx.x] = b; s_g[k][2][threadIdx.x] = c;
       }
       have_g = true;
@@ -492,7 +509,7 @@ __global__ void __launch_bounds__(SW_STREAM_THREADS, SW_STREAM_MINB) k_bd2d_stre
   if (!R.force_rebuild) {
     bool moved = false;
     for (long long i = lo + threadIdx.x; i < hi; i += gstride) moved |= moved_since_build<2>(P, A, 0, i);
-    need = step_barrier(moved, R.n_steps > 0, R.step0);
+    need = step_barrier(moved, R.n_steps > 0, R.step0, false);
   }
   long long s = 0;
   for (; s < R.n_steps; ++s) {
@@ -514,9 +531,9 @@ __global__ void __launch_bounds__(SW_STREAM_THREADS, SW_STREAM_MINB) k_bd2d_stre
       const bool pre = NOISE && have_g && k < SW_STREAM_PRE;
       const int kk = pre ? k : 0;
       moved |= bd2d_step_stream<NOISE>(P, A, S, cur, R.step0 + (u64)s, last, i, (i + gstride < hi) ? i + gstride : -1, lim2,
-                                       pre, s_g[kk][0][threadIdx.x], s_g[kk][1][threadIdx.x], s_g[kk][2][threadIdx.x]);
+                                       pre, s_g[kk][0][threadIdx.x], s_g[kk][1][threadIdx.x], s_g[kk][2][threadIdx.x], s > 0);
     }
-    need = step_barrier(moved, !last, R.step0 + (u64)s + 1);
+    need = step_barrier(moved, !last, R.step0 + (u64)s + 1, true);
   }
   if (s & 1) {
     for (long long i = lo + threadIdx.x; i < hi; i += gstride) {

@@ -74,6 +74,7 @@ struct DevArrays {
   const long long *okey;      // Verlet entries of a particle are kept in ascending okey[slot] (NULL => ascending slot): the force
                               // summation order when slots are spatially sorted and no longer the particle ids
   double *xr, *yr, *zr;        // positions at the last Verlet rebuild
+  double *gkeep;               // k_bd2d_stream: cosine normal of the even step's rotational pair, per slot (swm_gaussians_xyt_keep)
   int *head, *next, *cellof;   // linked cells
   int *nbr, *nbr_cnt;          // Verlet list: nbr[k * n_pad + i], k < cap
   int cap;

@@ -976,6 +976,7 @@ extern "C" int swarm_bind_state(swarm_t *s, int64_t n, const swarm_state_dev_t *
     if ((rc = sw_alloc(s, (void **)&A.xr, nb))) return rc;
     if ((rc = sw_alloc(s, (void **)&A.yr, nb))) return rc;
     if ((rc = sw_alloc(s, (void **)&A.zr, nb))) return rc;
+    if ((rc = sw_alloc(s, (void **)&A.gkeep, nb))) return rc;
     if ((rc = sw_alloc(s, (void **)&s->zeros, nb))) return rc;
     if ((rc = sw_alloc(s, (void **)&A.next, sizeof(int) * (size_t)A.n_pad, 0xFF))) return rc;
     if ((rc = sw_alloc(s, (void **)&A.cellof, sizeof(int) * (size_t)A.n_pad))) return rc;

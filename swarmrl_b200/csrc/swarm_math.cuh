@@ -172,13 +172,41 @@ __device__ __forceinline__ void swm_boxmuller_xyt(const u64 r[4], bool odd, doub
   double s0, c0, s1, c1;
   swm_sincos2pi(r[1], s0, c0);
   swm_sincos2pi(r[3], s1, c1);
-  const double gs = m1 * s1, gc = m1 * c1;
-  g0 = m0 * c0; g1 = m0 * s0; g3 = odd ? gc : gs;
+  g0 = m0 * c0; g1 = m0 * s0; g3 = m1 * (odd ? c1 : s1);
 }
 __device__ __forceinline__ void swm_gaussians_xyt(const unsigned int *rk, u64 id, u64 step, double &g0, double &g1, double &g3) {
   u64 r[4];
   swm_philox_xyt(rk, id, step, r);
   swm_boxmuller_xyt(r, (step & 1ULL) != 0ULL, g0, g1, g3);
+}
+
+// swm_gaussians_xyt for a kernel that keeps the even step's cosine normal in memory (k_bd2d_stream: one slot per particle):
+// keep_ok = the slot was written by the step just before `step`.  Same values, bit for bit.
+__device__ __forceinline__ void swm_gaussians_xyt_keep(const unsigned int *rk, u64 id, u64 step, bool keep_ok, double *slot,
+                                                       double &g0, double &g1, double &g3) {
+#ifdef SW_STREAM_NO_KEEP
+  if (true) { swm_gaussians_xyt(rk, id, step, g0, g1, g3); return; }   // A/B: every step draws both blocks, no slot traffic
+#endif
+  if (keep_ok && (step & 1ULL)) {
+    u64 w0, w1;
+    sw_noise_block_rk(rk, id, step, 0ULL, 0u, w0, w1);
+    const double m0 = swm_sqrt(-2.0 * swm_log01(swm_u01(w0)));
+    double s0, c0;
+    swm_sincos2pi(w1, s0, c0);
+    g0 = m0 * c0; g1 = m0 * s0; g3 = *slot;
+  } else {
+    u64 r[4];
+    swm_philox_xyt(rk, id, step, r);
+    const double m0 = swm_sqrt(-2.0 * swm_log01(swm_u01(r[0])));
+    const double m1 = swm_sqrt(-2.0 * swm_log01(swm_u01(r[2])));
+    double s0, c0, s1, c1;
+    swm_sincos2pi(r[1], s0, c0);
+    swm_sincos2pi(r[3], s1, c1);
+    const double gs = m1 * s1, gc = m1 * c1;
+    g0 = m0 * c0; g1 = m0 * s0;
+    if (step & 1ULL) g3 = gc;
+    else { g3 = gs; *slot = gc; }
+  }
 }
 
 // ---------------------------------------------------------------------------------------------
