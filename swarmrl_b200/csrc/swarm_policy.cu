@@ -64,7 +64,7 @@ __global__ void __launch_bounds__(POL_THREADS) k_policy_forward(long long n, Pol
 #pragma unroll
   for (int a = 0; a < AMAX; ++a) lg[a] = (a < A) ? N.ba[a] : -INFINITY;
   float val = N.bv[0];
-#pragma unroll 2
+#pragma unroll 4
   for (int j = 0; j < H; ++j) {
     float r[REC];
 #pragma unroll

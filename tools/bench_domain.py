@@ -130,7 +130,9 @@ def measure(world, rank, local, swarm, *, steps=100, slices=5, warmup=2, k=33, s
         "local_particles_sum": float(cnt[0]), "owned_sum": float(cnt[1]), "redundancy": float(cnt[0]) / n,
         "bytes_per_exchange_capacity": bytes_per_exchange,
         "bytes_per_exchange_live": int(2 * (8 + d.n_aux) * 8 * d.plan["halo"] / d.plan["box_x"] * n),
-        "timeline_ms_per_slice_max_over_ranks": {"integrate": float(ms[1]) / slices, "exchange(pack+nccl+merge)": float(ms[2]) / slices,
+        "transport": ("peer memory: P2P stores into the neighbours' CUDA-IPC regions + system-scope flag (swarm_dd_push / swarm_dd_wait)"
+                      if d.peer is not None else ("nccl send/recv (torch.distributed)" if world > 1 else "self-exchange (device copy)")),
+        "timeline_ms_per_slice_max_over_ranks": {"integrate": float(ms[1]) / slices, "exchange(pack+transport+merge)": float(ms[2]) / slices,
                                                  "reward": float(ms[3]) / slices},
         "reward_mean": float(red[1]), "skin": skin, "dtype": "f64", "scaling": "strong"}
     if keep:
@@ -202,6 +204,7 @@ def parity_selfcheck(world, rank, local, *, n=20000, steps=61, slices=2, k=4, sk
     d.stats()
     full, owned_total = gather_owned(d, world, rank, group)
     ex = d.exchanges
+    transport = "peer memory (swarm_dd_push / swarm_dd_wait)" if d.peer is not None else ("nccl" if world > 1 else "self-exchange")
     d.close()
     if rank != 0:
         return None
@@ -224,7 +227,7 @@ def parity_selfcheck(world, rank, local, *, n=20000, steps=61, slices=2, k=4, sk
     s.close()
     err = max(rel_err(full[0], p[:, 0]), rel_err(full[1], p[:, 1]), rel_err(full[2], th))
     return {"n_agents": n, "steps": steps * slices, "exchange_every": k, "exchanges": ex, "noise": kT > 0,
-            "transport": "nccl" if world > 1 else "self-exchange", "against": "single-GPU engine (DeviceSwarm, no decomposition)",
+            "transport": transport, "against": "single-GPU engine (DeviceSwarm, no decomposition)",
             "max_rel_err": err, "tolerance": 1e-9, "every_particle_owned_once": bool(owned_total == n and not np.isnan(full).any()),
             "reward_mean_abs_err": float(np.max(np.abs(np.array(means) - np.array(means_ref)))), "pass": bool(err < 1e-9 and owned_total == n)}
 
