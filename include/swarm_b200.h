@@ -128,7 +128,7 @@ int swarm_set_thermostat(swarm_t *s, double kT, uint64_t seed);
  * velocity Verlet steps: v and omega of the bound state are INPUTS as well as outputs, every species
  * needs mass > 0 and rinertia > 0 (espresso.py:391-400; isotropic rinertia in 3-D), every run starts
  * with a force recalculation at the current (x, v) as ESPResSo does after particle properties change.
- * The domain exchange (swarm_dd_*) carries no velocities and refuses to run under LANGEVIN. */
+ * On a decomposed swarm the caller ships vx, vy, wz as aux channels of the exchange record and cuts runs with swarm_run_part. */
 typedef enum { SWARM_INTEGRATOR_BROWNIAN = 0, SWARM_INTEGRATOR_LANGEVIN = 1 } swarm_integrator_t;
 int swarm_set_integrator(swarm_t *s, int32_t kind);
 
@@ -148,6 +148,16 @@ int swarm_relax(swarm_t *s, int64_t n_iter, double gamma, double max_disp, void 
  * external force/torque + Philox noise, fused.  step0 = global index of the first step (the
  * Philox counter).  Enqueues only; call swarm_sync_stats to learn whether it ran to completion. */
 int swarm_run(swarm_t *s, int64_t n_steps, uint64_t step0, void *stream);
+
+/* One integrator.run cut in parts, for the Langevin integrator on a decomposed swarm (no reference counterpart: ESPResSo
+ * runs single-rank; the domain exchange sits between the parts).  A velocity-Verlet chunk of n steps is n + 1 force
+ * evaluations, the first a recalculation and the last closing the final step; SWARM_RUN_LEAVE_OPEN stops a part between
+ * the two half kicks of its last step (positions at t_n, velocities at t_n - dt/2: the state the exchange ships) and
+ * SWARM_RUN_CONTINUE starts the next part by closing that step, so the parts together are the uncut run, bit for bit.
+ * Flags are ignored by the Brownian integrator, where swarm_run_part == swarm_run. */
+#define SWARM_RUN_CONTINUE 1
+#define SWARM_RUN_LEAVE_OPEN 2
+int swarm_run_part(swarm_t *s, int64_t n_steps, uint64_t step0, int32_t flags, void *stream);
 
 /* Synchronises `stream` and reports counters of the last run. */
 int swarm_sync_stats(swarm_t *s, void *stream, swarm_stats_t *out);
@@ -215,7 +225,7 @@ int swarm_bind_count(swarm_t *s, const int32_t *n_dev);
  * [halo, halo + slab_w), kept region [0, slab_w + 2 halo); the local swarm_t is created with
  * box = (slab_w + 2 halo, L_y, .), periodic = (0, 1, 0).  Exchange buffers are SoA records of
  * (x, y, theta, f_swim, tqz, gid, species, image, aux...) doubles behind an 8-byte record count. */
-#define SWARM_DD_MAX_AUX 4
+#define SWARM_DD_MAX_AUX 8
 typedef struct {
   double slab_w;
   double halo;

@@ -65,7 +65,8 @@ class Stats(C.Structure):
     ]
 
 
-DD_MAX_AUX = 4
+DD_MAX_AUX = 8
+RUN_CONTINUE, RUN_LEAVE_OPEN = 1, 2
 
 
 class DDGeom(C.Structure):
@@ -118,6 +119,7 @@ SYMBOLS = {
     "swarm_apply_new_direction": (C.c_int, [_V, _V]),
     "swarm_relax": (C.c_int, [_V, C.c_int64, C.c_double, C.c_double, _V]),
     "swarm_run": (C.c_int, [_V, C.c_int64, C.c_uint64, _V]),
+    "swarm_run_part": (C.c_int, [_V, C.c_int64, C.c_uint64, C.c_int32, _V]),
     "swarm_sync_stats": (C.c_int, [_V, _V, C.POINTER(Stats)]),
     "swarm_set_max_neighbors": (C.c_int, [_V, C.c_int32]),
     "swarm_debug_timing": (C.c_int, [_V, C.POINTER(C.c_int64)]),

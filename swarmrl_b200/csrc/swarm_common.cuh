@@ -150,6 +150,7 @@ struct swarm {
   size_t vis_bytes = 0;
   long long vis_prev_n = -1;   // the bounding box of the previous vision call is usable for this n / range
   double vis_prev_range = 0.0;
+  int run_flags = 0;                    // swarm_run_part: SWARM_RUN_* of the run being enqueued
   unsigned int *dd_tickets = nullptr;   // swarm_dd_push: one ticket counter per face
   const int *vis_image = nullptr;   // swarm_bind_images: periodic image count per slot (domain decomposition), or NULL
   Ctl *ctl_host = nullptr;  // pinned

@@ -160,11 +160,8 @@ extern "C" int64_t swarm_dd_buffer_doubles(const swarm_dd_geom_t *g) {
 extern "C" int swarm_dd_pack(swarm_t *s, const swarm_dd_geom_t *g, int64_t n, const int32_t *n_dev, const swarm_dd_arrays_t *loc,
                              double *send_left_dev, double *send_right_dev, void *stream) {
   if (!s || !loc || !send_left_dev || !send_right_dev || n < 0) { sw_set_error("bad arguments"); return SWARM_ERR_INVALID; }
-  if (s->integrator != SWARM_INTEGRATOR_BROWNIAN) {
-    // a halo record carries x, y, theta and the aux channels; v and omega, state under velocity Verlet, do not travel
-    sw_set_error("the domain exchange supports the Brownian integrator only");
-    return SWARM_ERR_STATE;
-  }
+  // a halo record carries x, y, theta and the aux channels.  Under the Langevin integrator v and omega are state: the caller
+  // binds vx, vy, wz to three aux channels of the record (DomainSwarm(velocities=True)) and cuts its runs with swarm_run_part
   int rc = dd_check(g);
   if (rc) return rc;
   SW_CUDA(cudaSetDevice(s->cfg.device));

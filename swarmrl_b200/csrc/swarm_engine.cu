@@ -1399,8 +1399,12 @@ static int sw_run_common(swarm *s, RunArgs R, cudaStream_t st) {
   const bool noise = (R.mode == MODE_BD || R.mode == MODE_LV) && (s->P.kT > 0.0);
   // velocity Verlet: n steps are n + 1 force evaluations (see RunArgs); the kernels count evaluations
   const bool lv = (R.mode == MODE_LV);
-  if (lv) R.n_steps += 1;
-  const bool lv_resume = lv && s->lv_resume;
+  // swarm_run_part: a chunk cut in parts (the domain exchange sits between them).  CONTINUE = the previous part left its last
+  // step open: start by closing it, no recalculation.  LEAVE_OPEN = stop between the half kicks of the last step (n evaluations).
+  const bool part_cont = lv && (s->run_flags & SWARM_RUN_CONTINUE), part_open = lv && (s->run_flags & SWARM_RUN_LEAVE_OPEN);
+  s->run_flags = 0;
+  if (lv && !part_open) R.n_steps += 1;
+  const bool lv_resume = lv && (s->lv_resume || part_cont);
   s->lv_resume = false;
   // bound the length of one cooperative launch (32-bit barrier counter, watchdog friendliness)
   const long long max_chunk = s->persistent ? 8192 : 1024;
@@ -1412,7 +1416,7 @@ static int sw_run_common(swarm *s, RunArgs R, cudaStream_t st) {
     Rc.steps_base = done;   // the kernels report steps_base + their own count: steps of the whole swarm_run
     if (done > 0) Rc.force_rebuild = 0;
     Rc.lv_first = (lv && done == 0 && !lv_resume) ? 1 : 0;
-    Rc.lv_close = (lv && done + Rc.n_steps == R.n_steps) ? 1 : 0;
+    Rc.lv_close = (lv && !part_open && done + Rc.n_steps == R.n_steps) ? 1 : 0;
     // only the last sub-launch of a chunk materialises v / omega on its final step: handled by
     // Rc.n_steps bookkeeping -- earlier sub-launches also write them, harmlessly.
     bool done_resident = false;
@@ -1460,6 +1464,15 @@ extern "C" int swarm_run(swarm_t *s, int64_t n_steps, uint64_t step0, void *stre
   RunArgs R{};
   R.n_steps = n_steps; R.step0 = step0; R.mode = (s->integrator == SWARM_INTEGRATOR_LANGEVIN) ? MODE_LV : MODE_BD;
   return sw_run_common(s, R, (cudaStream_t)stream);
+}
+
+extern "C" int swarm_run_part(swarm_t *s, int64_t n_steps, uint64_t step0, int32_t flags, void *stream) {
+  if (!s) return SWARM_ERR_INVALID;
+  if (flags & ~(SWARM_RUN_CONTINUE | SWARM_RUN_LEAVE_OPEN)) { sw_set_error("unknown swarm_run_part flags"); return SWARM_ERR_INVALID; }
+  s->run_flags = flags;
+  const int rc = swarm_run(s, n_steps, step0, stream);
+  s->run_flags = 0;
+  return rc;
 }
 
 extern "C" int swarm_set_integrator(swarm_t *s, int32_t kind) {

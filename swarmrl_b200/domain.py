@@ -138,8 +138,11 @@ class DomainSwarm:
 
     def __init__(self, box, dt, kT, seed, species, wca, *, exchange_every=8, margin=0.25, skin=0.4, world=1, rank=0,
                  group=None, device=None, n_aux=2, max_neighbors=0, capacity_factor=1.3, persistent=True, halo_extra=0.0,
-                 peer="auto"):
-        """peer: move the halo records with P2P stores into the neighbours' memory (swarm_dd_push / swarm_dd_wait, CUDA IPC)
+                 peer="auto", velocities=False):
+        """velocities: ship vx, vy, omega_z with every halo record (three more aux channels) and cut the runs with
+        swarm_run_part, so that the Langevin integrator (velocity Verlet: velocities are state) works on the decomposed swarm.
+
+        peer: move the halo records with P2P stores into the neighbours' memory (swarm_dd_push / swarm_dd_wait, CUDA IPC)
         instead of NCCL send / recv.  "auto" = when the process group is nccl (one GPU per rank on one node); True forces
         it (ranks sharing one GPU over gloo: the tests); False keeps torch.distributed.  SWARM_B200_DD_PEER=0/1 overrides."""
         import os
@@ -152,8 +155,11 @@ class DomainSwarm:
 
         self.max_cut = float(np.max(np.asarray(wca["cut"], dtype=np.float64)))
         self.plan = slab_plan(box[0], world, rank, exchange_every, self.max_cut, margin, halo_extra)
+        self.velocities = bool(velocities)
+        self._vel_base = int(n_aux)          # aux channels [vel_base, vel_base + 3) = vx, vy, omega_z
+        n_aux = int(n_aux) + (3 if self.velocities else 0)
         if not (0 <= n_aux <= _lib.DD_MAX_AUX):
-            raise ValueError("n_aux must lie in [0, 4]")
+            raise ValueError(f"n_aux (+ 3 velocity channels) must lie in [0, {_lib.DD_MAX_AUX}]")
         p = self.plan
         self.box = (float(box[0]), float(box[1]))
         self.n_aux = int(n_aux)
@@ -242,6 +248,9 @@ class DomainSwarm:
         st.x, st.y, st.z, st.theta = s["x"].data_ptr(), s["y"].data_ptr(), self.zeros.data_ptr(), s["theta"].data_ptr()
         st.vx, st.vy, st.vz = (self.vel[a].data_ptr() for a in range(3))
         st.wx, st.wy, st.wz = (self.omega[a].data_ptr() for a in range(3))
+        if self.velocities:   # state under velocity Verlet: they live in the exchange record's aux channels
+            vb = self._vel_base
+            st.vx, st.vy, st.wz = (s["aux"][vb + c].data_ptr() for c in range(3))
         st.species = s["species"].data_ptr()
         _lib.check(self.lib.swarm_bind_state(self.h, self.cap, C.byref(st)))   # cap = upper bound; live count below
         act = _lib.ActionsDev()
@@ -328,6 +337,9 @@ class DomainSwarm:
     # --------------------------------------------------------------- exchange
     def exchange(self):
         """halo refresh + migration, enqueued only: the new particle count stays on the device (see `sync`)."""
+        if getattr(self.sw, "thermostat_type", "brownian") != "brownian" and not self.velocities:
+            raise RuntimeError("this decomposed swarm ships no velocities: Brownian integrator only (create it with velocities=True "
+                               "for the Langevin integrator)")
         b, g = self.bufs, self.geom
         old, new = self.sets[self.cur], self.sets[self.cur ^ 1]
         c_old, c_new = self.counts[self.cur], self.counts[self.cur ^ 1]
@@ -378,13 +390,20 @@ class DomainSwarm:
     def run(self, n_steps, step0):
         """integrator.run(n_steps) (espresso.py:1304-1306) on the decomposed swarm."""
         done, k = 0, self.plan["k"]
+        # velocity Verlet: the parts of one run between two exchanges neither recalculate nor close a step (swarm_run_part),
+        # so the cut run is the uncut one; the exchange in between ships x(t_n) and v(t_n - dt/2) of every record
+        lv = self.velocities and getattr(self.sw, "thermostat_type", "brownian") == "langevin"
         while done < n_steps:
             if self.since_exchange >= k:
                 with self._timed("exchange"):
                     self.exchange()
             m = min(k - self.since_exchange, n_steps - done)
             with self._timed("run"):
-                _lib.check(self.lib.swarm_run(self.h, int(m), int(step0 + done), self._stream()))
+                if lv:
+                    flags = (_lib.RUN_CONTINUE if done > 0 else 0) | (_lib.RUN_LEAVE_OPEN if done + m < n_steps else 0)
+                    _lib.check(self.lib.swarm_run_part(self.h, int(m), int(step0 + done), flags, self._stream()))
+                else:
+                    _lib.check(self.lib.swarm_run(self.h, int(m), int(step0 + done), self._stream()))
             self.since_exchange += m
             done += m
 
@@ -413,7 +432,7 @@ class DomainSwarm:
         mean of an EPISODE's rewards after the episode (trainer.py:92-95), so the ranks need not meet in an all-reduce
         after every slice -- `reward_means()` reduces all deferred sums in one collective."""
         torch = self.torch
-        if self.n_aux < 2:
+        if self._vel_base < 2:
             raise ValueError("the field history needs n_aux >= 2")
         a = self._dd(self.local)
         s3 = (C.c_double * 3)(*[float(v) for v in src])
@@ -435,7 +454,7 @@ class DomainSwarm:
         """ConcentrationField / GradientSensing value per local slot with the history in aux channels `aux_base`,
         `aux_base + 1` (swarm_dd_obs_field_ch); all_local=True evaluates the ghosts too (an observable that feeds the
         policy: a ghost must take its owner's action), False the owned particles only (a reward).  Enqueue only."""
-        if self.n_aux < aux_base + 2:
+        if self._vel_base < aux_base + 2:
             raise ValueError("this history needs aux channels %d and %d" % (aux_base, aux_base + 1))
         out = self.torch.empty(self.cap, dtype=self.torch.float64, device=self.dev) if out is None else out
         a = self._dd(self.local)

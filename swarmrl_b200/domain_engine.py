@@ -20,11 +20,12 @@ How the agent pipeline stays exact on a decomposed swarm
     particle in the exchange record's aux channels (`new_history`);
   * vision is measured on unfolded positions without a minimum image, as in the reference: pairs are seen only within
     one periodic image (swarm_bind_images);
+  * `thermostat_type="langevin"`: velocities are state under velocity Verlet, so vx, vy, omega_z travel as three more aux
+    channels and the runs between two exchanges are cut with swarm_run_part (no recalculation, no closing half kick at a cut);
   * rewards are evaluated for owned particles; their sum stays on the device and `all_reduce_means` reduces a whole
     rollout's sums in ONE collective.
 
-Not supported on the decomposed swarm (raises): 3-D, walls, constant external force, the Langevin integrator,
-`new_direction` actions, policies without a fused `act` (their sampling is keyed by row, not by particle id).
+Not supported on the decomposed swarm (raises): 3-D, walls, constant external force, `new_direction` actions, policies without a fused `act` (their sampling is keyed by row, not by particle id).
 """
 from __future__ import annotations
 
@@ -46,7 +47,7 @@ class DomainBackend:
 
     def __init__(self, n_dims, box, periodic, dt, kT, seed, species, wca, walls=None, skin=0.4, persistent=True, *,
                  world=1, rank=0, group=None, exchange_every=8, margin=0.25, halo_extra=0.0, device=None,
-                 max_neighbors=0, capacity_factor=1.3):
+                 max_neighbors=0, capacity_factor=1.3, velocities=False):
         if int(n_dims) != 2:
             raise NotImplementedError("the domain-decomposed swarm is 2-D (slabs along x)")
         if walls is not None:
@@ -57,9 +58,9 @@ class DomainBackend:
         self.box = np.array([float(b) for b in box])
         self.world, self.rank = int(world), int(rank)
         self.dd = DomainSwarm((self.box[0], self.box[1]), dt, kT, seed, species, wca, exchange_every=exchange_every,
-                              margin=margin, skin=skin, world=world, rank=rank, group=group, device=device, n_aux=_lib.DD_MAX_AUX,
+                              margin=margin, skin=skin, world=world, rank=rank, group=group, device=device, n_aux=4,
                               max_neighbors=max_neighbors, capacity_factor=capacity_factor, persistent=persistent,
-                              halo_extra=halo_extra)
+                              halo_extra=halo_extra, velocities=velocities)
         self.sw = self.dd.sw
         self.torch, self.dev, self.lib, self.h = self.dd.torch, self.dd.dev, self.dd.lib, self.dd.h
         self.type_of_species = self.sw.type_of_species
@@ -90,9 +91,10 @@ class DomainBackend:
         self.sw.set_thermostat(kT, seed)
 
     def set_integrator(self, thermostat_type):
-        if thermostat_type != "brownian":
-            raise NotImplementedError("the domain exchange carries no velocities: Brownian dynamics only")
+        if thermostat_type != "brownian" and not self.dd.velocities:
+            raise NotImplementedError("this decomposed swarm ships no velocities: create it with velocities=True for Langevin")
         self.sw.set_integrator(thermostat_type)
+        self.thermostat_type = thermostat_type
 
     def set_max_neighbors(self, cap):
         self.sw.set_max_neighbors(cap)
@@ -182,8 +184,8 @@ class DomainBackend:
 
     def new_history(self, box_length, all_local):
         """Two aux channels seeded with the current normalised positions (the reference's `initialize`)."""
-        if self._hist_used + 2 > self.dd.n_aux:
-            raise ValueError("at most %d position histories fit the exchange record" % (self.dd.n_aux // 2))
+        if self._hist_used + 2 > self.dd._vel_base:
+            raise ValueError("at most %d position histories fit the exchange record" % (self.dd._vel_base // 2))
         h = DomainHistory(self._hist_used, all_local)
         self._hist_used += 2
         self.dd.field_eval((0.0, 0.0, 0.0), (box_length[0], box_length[1]), _lib.DECAY_LINEAR, 0.0, 0.0, init_only=True,
@@ -254,7 +256,10 @@ class DomainBackend:
 
         xg = unfold_global(s["x"][:n][own].cpu().numpy(), s["image"][:n][own].cpu().numpy(), dd.plan)
         y, th = s["y"][:n][own].cpu().numpy(), s["theta"][:n][own].cpu().numpy()
-        v = dd.vel[:, :n][:, own].cpu().numpy()
+        if dd.velocities:
+            v = self.torch.stack([s["aux"][dd._vel_base + c][:n][own] for c in range(2)]).cpu().numpy()
+        else:
+            v = dd.vel[:, :n][:, own].cpu().numpy()
         part = (gid, xg, y, th, v)
         if self.world > 1:
             parts = [None] * self.world

@@ -514,9 +514,7 @@ class SwarmEngine(Engine):
 
             if self._ext_force:
                 raise NotImplementedError("constant external forces are not supported on the domain-decomposed swarm")
-            if self.params.thermostat_type != "brownian":
-                raise NotImplementedError("the domain exchange carries no velocities: Brownian dynamics only")
-            self._backend = DomainBackend(**kw, **self._domain)
+            self._backend = DomainBackend(**kw, velocities=(self.params.thermostat_type == "langevin"), **self._domain)
         else:
             self._backend = type(self).backend_factory(**kw)
         pos = np.array(self._pos, dtype=float).reshape(-1, 3)

@@ -15,7 +15,7 @@ sys.path.insert(0, str(ROOT / "tests"))
 CASE = dict(n=4096, L=160.0, slices=3, steps_per_slice=12, k=5, vision_range=6.0, n_cones=5, relax_iters=1000)
 
 
-def build_engine(tmp, domain):
+def build_engine(tmp, domain, thermostat="brownian"):
     import swarmrl_b200 as sw
     from helpers import jittered_lattice
     from swarmrl_b200.units import UnitRegistry
@@ -26,13 +26,19 @@ def build_engine(tmp, domain):
     md = sw.MDParams(ureg=ureg, fluid_dyn_viscosity=ureg.Quantity(8.9e-4, "pascal * second"),
                      WCA_epsilon=ureg.Quantity(297.0, "kelvin") * ureg.boltzmann_constant,
                      temperature=ureg.Quantity(300.0, "kelvin"), box_length=ureg.Quantity(3 * [L], "micrometer"),
-                     time_step=dt, time_slice=dt * CASE["steps_per_slice"], write_interval=dt * CASE["steps_per_slice"] * 2)
+                     time_step=dt, time_slice=dt * CASE["steps_per_slice"], write_interval=dt * CASE["steps_per_slice"] * 2,
+                     thermostat_type=thermostat)
     e = sw.SwarmEngine(md_params=md, n_dims=2, seed=11, out_folder=tmp, write_chunk_size=100, domain=domain)
     rng = np.random.default_rng(5)
     pos = jittered_lattice(n, L, 2, rng, jitter=0.3)
     th = rng.uniform(0, 2 * np.pi, n)
     dirs = np.stack([np.cos(th), np.sin(th), np.zeros(n)], axis=1)
-    e.add_colloids_at(ureg.Quantity(pos, "micrometer"), dirs, radius_colloid=ureg.Quantity(1.0, "micrometer"), type_colloid=0)
+    kw = {}
+    if thermostat == "langevin":   # espresso.py:391-400: mass and rinertia are mandatory; velocity relaxation time = 50 steps
+        eta = md.fluid_dyn_viscosity.m_as("sim_dyn_viscosity")
+        gt, gr = 6 * np.pi * eta * 1.0, 8 * np.pi * eta * 1.0
+        kw = dict(mass=ureg.Quantity(gt * 1e-3 / 0.02, "sim_mass"), rinertia=ureg.Quantity(gr * 1e-3 / 0.02, "sim_rinertia"))
+    e.add_colloids_at(ureg.Quantity(pos, "micrometer"), dirs, radius_colloid=ureg.Quantity(1.0, "micrometer"), type_colloid=0, **kw)
     return e
 
 
@@ -55,10 +61,10 @@ def build_agent():
     return sw.DeviceAgent(0, sw.FusedActorCritic(P), task, obs, actions, reward_mean=True)
 
 
-def rollout(tmp, domain):
+def rollout(tmp, domain, thermostat="brownian"):
     import swarmrl_b200 as sw
 
-    e = build_engine(tmp, domain)
+    e = build_engine(tmp, domain, thermostat)
     agent = build_agent()
     ff = sw.ForceFunction({"0": agent})
     agent.reset_agent(e.colloids)
@@ -72,12 +78,13 @@ def rollout(tmp, domain):
     else:
         means = np.array([m.cpu().numpy() for m in agent.reward_means])
         extra = dict(exchanges=0, owned=CASE["n"])
-    return dict(pos=data["Unwrapped_Positions"], dirs=data["Directors"], means=means, step_idx=e.step_idx, **extra)
+    return dict(pos=data["Unwrapped_Positions"], dirs=data["Directors"], vel=data["Velocities"], means=means, step_idx=e.step_idx, **extra)
 
 
 def main():
     rank, world, port, out = int(sys.argv[1]), int(sys.argv[2]), int(sys.argv[3]), sys.argv[4]
     backend = sys.argv[5] if len(sys.argv) > 5 else "gloo"
+    thermostat = sys.argv[6] if len(sys.argv) > 6 else "brownian"
     import torch
     import torch.distributed as dist
 
@@ -86,7 +93,7 @@ def main():
     if world > 1:
         dist.init_process_group(backend, init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
     domain = dict(world=world, rank=rank, exchange_every=CASE["k"], margin=0.25, halo_extra=CASE["vision_range"], device=dev)
-    res = rollout(pathlib.Path(out).parent / f"traj{rank}", domain)
+    res = rollout(pathlib.Path(out).parent / f"traj{rank}", domain, thermostat)
     np.savez(f"{out}.{rank}.npz", **res)
     if world > 1:
         dist.barrier()

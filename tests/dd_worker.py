@@ -16,6 +16,14 @@ sys.path.insert(0, str(ROOT / "tests"))
 CASE = dict(n=4096, L=160.0, dt=1e-3, seed=42, k=4, steps=61, slices=2)
 
 
+def langevin_species():
+    """mass / rinertia such that the velocity relaxation time is 50 time steps (tests/test_gpu_langevin.py)"""
+    from helpers import stokes
+
+    gt, gr = stokes(1.0)
+    return [dict(type=0, gamma_t=(gt,) * 3, gamma_r=(gr,) * 3, mass=gt * CASE["dt"] / 0.02, rinertia=(gr * CASE["dt"] / 0.02,) * 3)]
+
+
 def build_case():
     from helpers import jittered_lattice, species_for, stokes
 
@@ -33,6 +41,7 @@ def main():
     rank, world, port, out = int(sys.argv[1]), int(sys.argv[2]), int(sys.argv[3]), sys.argv[4]
     backend = sys.argv[5] if len(sys.argv) > 5 else "gloo"
     kT = float(sys.argv[6]) if len(sys.argv) > 6 else 300.0 / 293.0
+    langevin = len(sys.argv) > 7 and sys.argv[7] == "langevin"
     import torch
     import torch.distributed as dist
     from helpers import wca_for
@@ -43,9 +52,13 @@ def main():
     dist.init_process_group(backend, init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
     pos, theta, acts, sp = build_case()
     L = CASE["L"]
+    if langevin:
+        sp = langevin_species()
     d = DomainSwarm((L, L), CASE["dt"], kT, CASE["seed"], sp, wca_for([1.0]), exchange_every=CASE["k"], world=world,
-                    rank=rank, device=dev, skin=0.4)
+                    rank=rank, device=dev, skin=0.4, velocities=langevin)
     d.scatter(pos, theta)
+    if langevin:
+        d.sw.set_integrator("langevin")   # velocity Verlet: v, omega travel with the records, runs are cut with swarm_run_part
     d.field_reward((0.5, 0.5, 0.0), (L, L), init_only=True)
     step, means = 0, []
     for f, t in acts:

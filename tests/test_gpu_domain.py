@@ -19,7 +19,7 @@ HERE = pathlib.Path(__file__).resolve().parent
 TOL = 1e-9
 
 
-def _single_gpu_reference(kT):
+def _single_gpu_reference(kT, langevin=False):
     import torch
 
     import dd_worker as W
@@ -28,8 +28,12 @@ def _single_gpu_reference(kT):
     pos, theta, acts, sp = W.build_case()
     C = W.CASE
     n, L = C["n"], C["L"]
+    if langevin:
+        sp = W.langevin_species()
     d = DeviceSwarm(2, (L, L, L), True, C["dt"], kT, C["seed"], sp, wca_for([1.0]), skin=0.4)
     d.set_state(pos, np.zeros(n, dtype=np.int32), theta=theta)
+    if langevin:
+        d.set_integrator("langevin")
     row_of, rows = d.row_map(0)
     hist = (d.pos[:, :n] / L).contiguous()
     step, means = 0, []
@@ -52,14 +56,14 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _run_ranks(world, tmp_path, kT, backend="gloo", peer=None):
+def _run_ranks(world, tmp_path, kT, backend="gloo", peer=None, extra=()):
     import os
 
     port, out = _free_port(), str(tmp_path / "dd")
     env = dict(os.environ)
     if peer is not None:
         env["SWARM_B200_DD_PEER"] = "1" if peer else "0"
-    procs = [subprocess.Popen([sys.executable, str(HERE / "dd_worker.py"), str(r), str(world), str(port), out, backend, repr(kT)],
+    procs = [subprocess.Popen([sys.executable, str(HERE / "dd_worker.py"), str(r), str(world), str(port), out, backend, repr(kT), *extra],
                               stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env) for r in range(world)]
     logs = [p.communicate(timeout=600)[0] for p in procs]
     for p, lg in zip(procs, logs):
@@ -111,6 +115,17 @@ def test_peer_memory_exchange_between_ranks_sharing_one_gpu(tmp_path, world):
     parts = _run_ranks(world, tmp_path, KT_300, peer=True)
     _check(parts, _single_gpu_reference(KT_300), W.CASE["n"])
     assert all(int(q["peer"]) == 1 for q in parts)
+
+
+@pytest.mark.parametrize("world", [1, 2])
+def test_langevin_integrator_on_the_decomposed_swarm(tmp_path, world):
+    """thermostat_type="langevin" (velocity Verlet, velocities are state): vx, vy, omega_z travel as aux channels of the
+    exchange record and the runs between two exchanges are cut with swarm_run_part -- no recalculation and no closing half
+    kick at a cut -- so the decomposed run reproduces the single-GPU Langevin run, noise on."""
+    import dd_worker as W
+
+    parts = _run_ranks(world, tmp_path, KT_300, extra=("langevin",))
+    _check(parts, _single_gpu_reference(KT_300, langevin=True), W.CASE["n"])
 
 
 @pytest.mark.parametrize("peer", [True, False])

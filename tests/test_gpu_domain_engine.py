@@ -26,9 +26,9 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _run_ranks(world, tmp_path, backend="gloo"):
+def _run_ranks(world, tmp_path, backend="gloo", thermostat="brownian"):
     port, out = _free_port(), str(tmp_path / "dde")
-    procs = [subprocess.Popen([sys.executable, str(HERE / "dd_engine_worker.py"), str(r), str(world), str(port), out, backend],
+    procs = [subprocess.Popen([sys.executable, str(HERE / "dd_engine_worker.py"), str(r), str(world), str(port), out, backend, thermostat],
                               stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True) for r in range(world)]
     logs = [p.communicate(timeout=900)[0] for p in procs]
     for p, lg in zip(procs, logs):
@@ -74,6 +74,19 @@ def test_nccl_two_gpus_reproduce_the_single_gpu_rollout(tmp_path, single):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     _check(_run_ranks(2, tmp_path, backend="nccl"), single)
+
+
+def test_langevin_thermostat_on_two_ranks_reproduces_the_single_gpu_rollout(tmp_path, tmp_path_factory):
+    """MDParams(thermostat_type="langevin") with domain=...: velocities travel with the halo records, the runs between
+    exchanges are cut with swarm_run_part; positions, directors, velocities and reward means as on one GPU."""
+    import dd_engine_worker as W
+
+    ref = W.rollout(tmp_path_factory.mktemp("single_lv"), None, "langevin")
+    parts = _run_ranks(2, tmp_path, thermostat="langevin")
+    _check(parts, ref)
+    for q in parts:
+        assert rel_err(q["vel"], ref["vel"]) < 1e-8
+    assert np.abs(ref["vel"]).max() > 0.0
 
 
 def test_vision_beyond_the_halo_band_is_refused(tmp_path):
