@@ -49,6 +49,24 @@ __device__ __forceinline__ void bd2d_pair(const DevParams &P, double xi, double 
   }
 }
 
+// bd2d_pair for an entry that knows whether its separation needs the minimum image (k_bd2d_tiled, SW_TILE_WRAP): for a zero
+// image shift the minimum image returns d - L * 0 = d, so skipping it leaves every bit as it is and saves two
+// multiplies, a rounding and a subtraction per dimension and entry.
+__device__ __forceinline__ void bd2d_pair_w(const DevParams &P, double xi, double yi, int ti, int tj, bool wrap, double xj, double yj,
+                                            double &Fx, double &Fy) {
+  double dx = xi - xj, dy = yi - yj;
+  if (wrap) {
+    dx = sw_min_image(dx, P.box[0], P.inv_box[0], P.periodic[0]);
+    dy = sw_min_image(dy, P.box[1], P.inv_box[1], P.periodic[1]);
+  }
+  double r2 = sw_r2(dx, dy, 0.0);
+  double cut = P.wca_cut[ti][tj];
+  if (r2 < __dmul_rn(cut, cut) && r2 > 0.0) {
+    double fac = swm_wca_factor(r2, P.wca_sigma[ti][tj], P.wca_eps[ti][tj]);
+    Fx = fma(fac, dx, Fx); Fy = fma(fac, dy, Fy);
+  }
+}
+
 // -DSW_TILE_PAIR4 (A/B build, NOT the default; profiles/r02_pair4_ab.txt: 0.42-0.59 ms per launch against 0.385-0.494 ms
 // with bd2d_pair -- the step is short of issue slots, and a warp with ONE contact now issues four chains).
 // Four Verlet entries at once.  bd2d_pair evaluates entry after entry, each behind its own branch: a warp then runs the WCA

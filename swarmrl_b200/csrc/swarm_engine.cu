@@ -1644,7 +1644,7 @@ extern "C" int swarm_tiled_neighbors_dump(swarm_t *s, int32_t *pairs, int64_t ca
   std::vector<std::pair<int, int>> out;
   for (long long sl = 0; sl < n; ++sl)
     for (int k = 0; k < cnt[(size_t)sl]; ++k)
-      out.emplace_back(perm[(size_t)sl], perm[(size_t)(nbr[(size_t)k * (size_t)s->A.n_pad + (size_t)sl] & SW_IDX_MASK)]);
+      out.emplace_back(perm[(size_t)sl], perm[(size_t)(nbr[(size_t)k * (size_t)s->A.n_pad + (size_t)sl] & SW_TILE_JMASK)]);
   std::sort(out.begin(), out.end());
   int64_t c = 0;
   for (const auto &pr : out) {

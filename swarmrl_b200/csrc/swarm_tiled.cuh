@@ -43,6 +43,8 @@
 #define SW_TILE_HT 1024                     // halo hash table: remote slots this tile's lists point at (load factor <= 1/2)
 #define SW_TILE_W (SW_TILE_MAXP + SW_TILE_HT)   // positions per buffer: the tile, then its halo
 #define SW_TILE_RAW 0x08000000              // entry flag: remote slot that did not fit the halo table (read directly)
+#define SW_TILE_WRAP 0x04000000             // entry flag: the pair's separation needs the minimum image (set at the rebuild)
+#define SW_TILE_JMASK 0x03FFFFFF            // slot / buffer index of an entry (below the two flags)
 // dynamic shared memory in doubles: x, y double-buffered over tile + halo; 8 per-thread columns; the list cache and the
 // hash table / compact list as ints
 #define SW_TILE_DSM_DOUBLES (4 * SW_TILE_W + 8 * SW_TILE_MAXP + (SW_TILE_SNBR * SW_TILE_MAXP + 2 * SW_TILE_HT) / 2)
@@ -181,14 +183,21 @@ __device__ __forceinline__ int tile_search(const DevParams &P, const DevArrays &
   auto consider = [&](int j, double xj, double yj, int spj, long long kj) {
     if (j == (int)slot) return;
     const int tj = P.sp_type[spj];
-    const double ddx = sw_min_image(xi - xj, P.box[0], P.inv_box[0], P.periodic[0]);
-    const double ddy = sw_min_image(yi - yj, P.box[1], P.inv_box[1], P.periodic[1]);
+    const double rx = xi - xj, ry = yi - yj;
+    const double ddx = sw_min_image(rx, P.box[0], P.inv_box[0], P.periodic[0]);
+    const double ddy = sw_min_image(ry, P.box[1], P.inv_box[1], P.periodic[1]);
     const double rl = __dadd_rn(P.wca_cut[ti][tj], P.skin);
     if (sw_r2(ddx, ddy, 0.0) < __dmul_rn(rl, rl)) {
+      // Does this pair need the minimum image at all?  Its image shift rint(d / L) is constant until the next rebuild (the
+      // separation changes by less than the skin, far below L / 2 in a box of at least four list radii), and it is zero
+      // for all but the pairs across a periodic face or between particles with different winding numbers: the step then
+      // takes d = x_i - x_j as it is -- the value the minimum image returns for a zero shift, bit for bit.
+      const double reach = 4.0 * (rl + P.skin);
+      const bool wrap = ddx != rx || ddy != ry || (P.periodic[0] && P.box[0] < reach) || (P.periodic[1] && P.box[1] < reach);
       if (cnt < T.cap) {
         int k = cnt++;
         while (k > 0 && lkey[k - 1] > kj) { loc[k] = loc[k - 1]; lkey[k] = lkey[k - 1]; --k; }
-        loc[k] = j | (tj << SW_TYPE_SHIFT);
+        loc[k] = j | (tj << SW_TYPE_SHIFT) | (wrap ? SW_TILE_WRAP : 0);
         lkey[k] = kj;
       } else {
         over = true;
@@ -414,33 +423,35 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_tiled(const __grid_cons
   // buffers -- own tile [0, ppc), halo [SW_TILE_MAXP, SW_TILE_W) -- or, flagged SW_TILE_RAW, a remote slot that did not
   // fit the halo table.
   auto translate = [&](int en) -> int {
-    const int j = en & SW_IDX_MASK;
+    const int j = en & SW_TILE_JMASK;
+    const int keep = en & (~SW_IDX_MASK | SW_TILE_WRAP);   // type and the minimum-image flag travel with the entry
     const unsigned int l = (unsigned int)(j - base);
-    if (l < (unsigned int)ppc) return (en & ~SW_IDX_MASK) | (int)l;
+    if (l < (unsigned int)ppc) return keep | (int)l;
     exported = true;
     unsigned int h = ((unsigned int)j * 2654435761u) >> 22;   // 10 bits
 #pragma unroll 1
     for (int probe = 0; probe < 64; ++probe) {
       const int old = atomicCAS(&htab[h], -1, j);
-      if (old == -1 || old == j) return (en & ~SW_IDX_MASK) | (SW_TILE_MAXP + (int)h);
+      if (old == -1 || old == j) return keep | (SW_TILE_MAXP + (int)h);
       h = (h + 1u) & (SW_TILE_HT - 1);
     }
-    return (en & ~SW_IDX_MASK) | SW_TILE_RAW | j;
+    return keep | SW_TILE_RAW | j;
   };
   // the same mapping for a list entry read from memory inside the step loop (beyond the cached ones): lookup only
   auto translate_ro = [&](int en) -> int {
-    const int j = en & SW_IDX_MASK;
+    const int j = en & SW_TILE_JMASK;
+    const int keep = en & (~SW_IDX_MASK | SW_TILE_WRAP);
     const unsigned int l = (unsigned int)(j - base);
-    if (l < (unsigned int)ppc) return (en & ~SW_IDX_MASK) | (int)l;
+    if (l < (unsigned int)ppc) return keep | (int)l;
     unsigned int h = ((unsigned int)j * 2654435761u) >> 22;
 #pragma unroll 1
     for (int probe = 0; probe < 64; ++probe) {
       const int v = htab[h];
-      if (v == j) return (en & ~SW_IDX_MASK) | (SW_TILE_MAXP + (int)h);
+      if (v == j) return keep | (SW_TILE_MAXP + (int)h);
       if (v == -1) break;
       h = (h + 1u) & (SW_TILE_HT - 1);
     }
-    return (en & ~SW_IDX_MASK) | SW_TILE_RAW | j;
+    return keep | SW_TILE_RAW | j;
   };
   auto load_list = [&]() {
     cnt = T.nbr_cnt[slot];
@@ -645,8 +656,8 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_tiled(const __grid_cons
       // every entry is an index into the position buffer (own tile, then halo): plain LDS.  A raw remote entry (halo
       // table full) is the exception and reads its record itself.
       auto fetch = [&](int en, double &x, double &y) {
-        if (en & SW_TILE_RAW) rim_read(&(G.rim + cur * G.rim_stride)[en & (SW_TILE_RAW - 1)], G.flag0 + e, x, y);
-        else { const int l = en & SW_IDX_MASK; x = sx[cur][l]; y = sy[cur][l]; }
+        if (en & SW_TILE_RAW) rim_read(&(G.rim + cur * G.rim_stride)[en & SW_TILE_JMASK], G.flag0 + e, x, y);
+        else { const int l = en & SW_TILE_JMASK; x = sx[cur][l]; y = sy[cur][l]; }
       };
       double xj[SW_RES_NBR], yj[SW_RES_NBR];
 #pragma unroll
@@ -655,7 +666,7 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_tiled(const __grid_cons
 #ifndef SW_TILE_PAIR4
 #pragma unroll
       for (int k = 0; k < SW_RES_NBR; ++k)
-        if (k < cnt) bd2d_pair(P, xi, yi, ti, nb[k] >> SW_TYPE_SHIFT, xj[k], yj[k], Fx, Fy);
+        if (k < cnt) bd2d_pair_w(P, xi, yi, ti, nb[k] >> SW_TYPE_SHIFT, (nb[k] & SW_TILE_WRAP) != 0, xj[k], yj[k], Fx, Fy);
 #else
       static_assert(SW_RES_NBR == 4, "bd2d_pair4 takes the four register-resident entries");
       bd2d_pair4(P, xi, yi, ti, nb, xj, yj, cnt, Fx, Fy);
@@ -676,7 +687,7 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_tiled(const __grid_cons
 #ifndef SW_TILE_PAIR4
 #pragma unroll
         for (int u = 0; u < 4; ++u)
-          if (k0 + u < cnt) bd2d_pair(P, xi, yi, ti, en4[u] >> SW_TYPE_SHIFT, xe[u], ye[u], Fx, Fy);
+          if (k0 + u < cnt) bd2d_pair_w(P, xi, yi, ti, en4[u] >> SW_TYPE_SHIFT, (en4[u] & SW_TILE_WRAP) != 0, xe[u], ye[u], Fx, Fy);
 #else
         bd2d_pair4(P, xi, yi, ti, en4, xe, ye, cnt - k0, Fx, Fy);
 #endif
