@@ -219,19 +219,37 @@ class DomainSwarm:
             want = t.world > 1 and t.backend == "nccl"
         if not want or t.world < 2:
             return
+        # Every step is agreed on by ALL ranks (all_gather of the outcome): if CUDA IPC is not available to one of them (a
+        # container without shared IPC, a device without peer access) every rank falls back to torch.distributed send / recv.
         region = C.c_void_p()
         handle = C.create_string_buffer(64)
-        _lib.check(self.lib.swarm_dd_peer_alloc(self.sw.device_index, C.byref(self.geom), C.byref(region), handle))
-        mine = (bytes(handle.raw), int(self.geom.cap), int(self.geom.n_aux))
+        ok = self.lib.swarm_dd_peer_alloc(self.sw.device_index, C.byref(self.geom), C.byref(region), handle) == 0
+        mine = (bytes(handle.raw) if ok else None, int(self.geom.cap), int(self.geom.n_aux))
         every = [None] * t.world
         t.dist.all_gather_object(every, mine, group=t.group)    # also the barrier between "zeroed" and "first push"
         if any((c, a) != mine[1:] for _, c, a in every):
             raise RuntimeError("the ranks of a domain-decomposed swarm must use the same exchange-buffer geometry")
         opened = {}
-        for nb in {p["left"], p["right"]}:
-            r = C.c_void_p()
-            _lib.check(self.lib.swarm_dd_peer_open(self.sw.device_index, every[nb][0], C.byref(r)))
-            opened[nb] = r
+        if all(h is not None for h, _, _ in every):
+            for nb in {p["left"], p["right"]}:
+                r = C.c_void_p()
+                if self.lib.swarm_dd_peer_open(self.sw.device_index, every[nb][0], C.byref(r)) != 0:
+                    ok = False
+                    break
+                opened[nb] = r
+        else:
+            ok = False
+        verdict = [None] * t.world
+        t.dist.all_gather_object(verdict, bool(ok), group=t.group)
+        if not all(verdict):
+            for r in opened.values():
+                self.lib.swarm_dd_peer_close(r)
+            t.dist.barrier(group=t.group)
+            if region:
+                self.lib.swarm_dd_peer_free(region)
+            if self._peer_req is True:
+                raise RuntimeError("the peer-memory exchange was requested but CUDA IPC is not available: " + _lib.last_error())
+            return
         self.peer = dict(region=region, left=opened[p["left"]], right=opened[p["right"]], opened=opened)
 
     def _dd(self, s):
