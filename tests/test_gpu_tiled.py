@@ -129,3 +129,55 @@ def test_small_swarms_keep_the_resident_kernel_by_default():
     _, d = _pair(1000, 125.0, 0.0)
     d.run_checked(10, 0)
     assert d.tiling_stats()["tiled"] == 0
+
+
+@pytest.mark.parametrize("mode", [2, 0])
+def test_shared_rotational_pair_does_not_depend_on_where_a_launch_starts(mode):
+    """The rotational normal of an odd step is the cosine kept from the even step before it (swarm_math.cuh): a launch that
+    STARTS on an odd step, or ends on an even one, has no kept value and must draw the even step's block again -- so cutting a
+    run at odd and even steps must not change a single bit, in the tiled kernel (mode 2: the value lives in shared memory) and
+    in the resident one (mode 0: drawn afresh every step)."""
+    _, whole = _pair(20000, 800.0, KT_300, skin=1.0)
+    whole.set_tiling(mode)
+    st = whole.run_checked(50, 0)
+    assert st.steps_done == 50 and not st.overflow
+    p0, v0, e0 = whole.particle_data_host()
+    _, cut = _pair(20000, 800.0, KT_300, skin=1.0)
+    cut.set_tiling(mode)
+    step = 0
+    for n in (7, 10, 1, 2, 30):   # launches starting on steps 0, 7, 17, 18, 20
+        st = cut.run_checked(n, step)
+        assert st.steps_done == n and not st.overflow
+        step += n
+    p1, v1, e1 = cut.particle_data_host()
+    assert np.array_equal(p0, p1) and np.array_equal(e0, e1)
+    assert cut.tiling_stats()["tiled"] == (1 if mode == 2 else 0)
+
+
+def test_environment_kernel_keeps_the_cosine_across_an_odd_cut():
+    """k_bd2d_env (batched environments, one warp each) holds the kept normal in a register: same check."""
+    from swarmrl_b200.device import DeviceSwarm
+
+    rng = np.random.default_rng(3)
+    E, m, L = 64, 32, 40.0
+    sp, wca = species_for([1.0]), wca_for([1.0])
+    pos = np.concatenate([jittered_lattice(m, L, 2, rng) for _ in range(E)])
+    th = rng.uniform(0, 2 * np.pi, E * m)
+    gt, gr = sp[0]["gamma_t"][0], sp[0]["gamma_r"][0]
+
+    def make():
+        d = DeviceSwarm(2, (L, L, L), True, 1e-3, KT_300, 42, sp, wca, skin=0.4, n_envs=E)
+        d.set_state(pos, np.zeros(E * m, dtype=np.int32), theta=th)
+        d.set_actions_host(np.full(E * m, 5.0 * gt), np.tile([0, 0, gr * 4 * np.pi / 180], (E * m, 1)))
+        return d
+
+    a = make()
+    a.run_checked(40, 0)
+    b = make()
+    step = 0
+    for n in (5, 8, 1, 26):
+        b.run_checked(n, step)
+        step += n
+    pa, _, ea = a.particle_data_host()
+    pb, _, eb = b.particle_data_host()
+    assert np.array_equal(pa, pb) and np.array_equal(ea, eb)
