@@ -277,6 +277,13 @@ int swarm_dd_push(swarm_t *s, const swarm_dd_geom_t *g, const double *send_left_
                   void *left_neighbour_region, void *right_neighbour_region, uint64_t epoch, void *stream);
 int swarm_dd_wait(swarm_t *s, void *my_region, uint64_t epoch, int32_t *counts8_dev, void *stream);
 
+/* Lean exchange bookkeeping: with on = 1 the last kernel of swarm_dd_merge also clears what the NEXT exchange starts from -- the
+ * record counts of the send buffers of the last swarm_dd_pack and the counts8 buffer passed as n_old_dev (which must then be
+ * the counts8 buffer of the old half, the next merge's output) -- so the next pack / merge skip their four memset launches
+ * when they are handed exactly those buffers (any other buffer is cleared as before).  For callers that alternate
+ * pack -> transport -> merge on two fixed halves, as DomainSwarm does. */
+int swarm_dd_set_lean(swarm_t *s, int32_t on);
+
 /* swarm_obs_field for the owned particles of a sub-domain, on global unfolded coordinates
  * x_global = x_local + x_offset + image * box_x; history (p_prev) in aux channels 0, 1; out_dev[n],
  * 0 for ghosts.  init_only = 1 just seeds the history. */

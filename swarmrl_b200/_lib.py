@@ -108,6 +108,7 @@ SYMBOLS = {
     "swarm_dd_obs_field_ch": (C.c_int, [_V, C.c_int64, _V, C.POINTER(DDArrays), C.c_double, C.c_double, _DP, _DP, C.c_int32,
                                         C.c_double, C.c_double, C.c_double, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _V, _V]),
     "swarm_bind_images": (C.c_int, [_V, _V]),
+    "swarm_dd_set_lean": (C.c_int, [_V, C.c_int32]),
     "swarm_dd_peer_region_bytes": (C.c_int64, [C.POINTER(DDGeom)]),
     "swarm_dd_peer_alloc": (C.c_int, [C.c_int32, C.POINTER(DDGeom), C.POINTER(_V), C.c_char_p]),
     "swarm_dd_peer_open": (C.c_int, [C.c_int32, C.c_char_p, C.POINTER(_V)]),

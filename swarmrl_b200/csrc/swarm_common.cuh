@@ -150,6 +150,10 @@ struct swarm {
   size_t vis_bytes = 0;
   long long vis_prev_n = -1;   // the bounding box of the previous vision call is usable for this n / range
   double vis_prev_range = 0.0;
+  bool dd_lean = false;                 // swarm_dd_set_lean: counters are cleared by the merge's last kernel, not by memsets
+  int *dd_clean_counts = nullptr;       //   the counts8 buffer that kernel cleared (the next merge's output)
+  double *dd_send_l = nullptr, *dd_send_r = nullptr;            //   the send buffers whose record counts it cleared
+  double *dd_last_send_l = nullptr, *dd_last_send_r = nullptr;  //   the send buffers of the last pack
   int run_flags = 0;                    // swarm_run_part: SWARM_RUN_* of the run being enqueued
   unsigned int *dd_tickets = nullptr;   // swarm_dd_push: one ticket counter per face
   const int *vis_image = nullptr;   // swarm_bind_images: periodic image count per slot (domain decomposition), or NULL

@@ -138,10 +138,18 @@ __global__ void k_dd_merge(swarm_dd_geom_t G, long long n_bound, const int *n_de
   }
 }
 
-__global__ void k_dd_finish(int *counts) {
+// lean mode (swarm_dd_set_lean): the counters the NEXT exchange starts from are cleared here, behind the merge that was their
+// last reader, instead of by four memset launches in front of the next pack and merge
+__global__ void k_dd_finish(int *counts, int *old_counts, double *send_left, double *send_right) {
   const unsigned long long n = *(unsigned long long *)(counts + 4);
   counts[0] = (int)n;
   counts[3] |= counts[2];   // sticky error bits: survive the next merge's reset of counts[2]
+  if (old_counts) {
+    old_counts[0] = 0; old_counts[1] = 0; old_counts[2] = 0;
+    old_counts[4] = 0; old_counts[5] = 0; old_counts[6] = 0; old_counts[7] = 0;
+    *(unsigned long long *)send_left = 0ULL;
+    *(unsigned long long *)send_right = 0ULL;
+  }
 }
 
 static int dd_check(const swarm_dd_geom_t *g) {
@@ -166,8 +174,12 @@ extern "C" int swarm_dd_pack(swarm_t *s, const swarm_dd_geom_t *g, int64_t n, co
   if (rc) return rc;
   SW_CUDA(cudaSetDevice(s->cfg.device));
   cudaStream_t st = (cudaStream_t)stream;
-  SW_CUDA(cudaMemsetAsync(send_left_dev, 0, 8, st));
-  SW_CUDA(cudaMemsetAsync(send_right_dev, 0, 8, st));
+  if (!(s->dd_lean && s->dd_send_l == send_left_dev && s->dd_send_r == send_right_dev)) {   // lean: cleared by the last merge
+    SW_CUDA(cudaMemsetAsync(send_left_dev, 0, 8, st));
+    SW_CUDA(cudaMemsetAsync(send_right_dev, 0, 8, st));
+  }
+  s->dd_send_l = nullptr; s->dd_send_r = nullptr;
+  s->dd_last_send_l = send_left_dev; s->dd_last_send_r = send_right_dev;
   if (n > 0) {
     k_dd_pack<<<(unsigned)((n + DD_THREADS - 1) / DD_THREADS), DD_THREADS, 0, st>>>(*g, n, (const int *)n_dev, dd_arrays(loc), send_left_dev, send_right_dev);
     s->launches += 1;
@@ -187,12 +199,17 @@ extern "C" int swarm_dd_merge(swarm_t *s, const swarm_dd_geom_t *g, int64_t n_ol
   SW_CUDA(cudaSetDevice(s->cfg.device));
   cudaStream_t st = (cudaStream_t)stream;
   // counts[3] (sticky error bits) survives; everything else restarts
-  SW_CUDA(cudaMemsetAsync(counts8_dev, 0, 3 * sizeof(int), st));
-  SW_CUDA(cudaMemsetAsync(counts8_dev + 4, 0, 4 * sizeof(int), st));
+  if (!(s->dd_lean && s->dd_clean_counts == counts8_dev)) {   // lean: cleared by the previous merge
+    SW_CUDA(cudaMemsetAsync(counts8_dev, 0, 3 * sizeof(int), st));
+    SW_CUDA(cudaMemsetAsync(counts8_dev + 4, 0, 4 * sizeof(int), st));
+  }
+  s->dd_clean_counts = nullptr;
   const long long total = n_old + 2LL * g->cap;
   k_dd_merge<<<(unsigned)((total + DD_THREADS - 1) / DD_THREADS), DD_THREADS, 0, st>>>(*g, n_old, (const int *)n_old_dev, dd_arrays(old_loc), recv_left_dev, recv_right_dev, cap_new,
                                                              dd_arrays(new_loc), counts8_dev);
-  k_dd_finish<<<1, 1, 0, st>>>(counts8_dev);
+  const bool lean = s->dd_lean && n_old_dev && s->dd_last_send_l && s->dd_last_send_r;
+  k_dd_finish<<<1, 1, 0, st>>>(counts8_dev, lean ? (int *)n_old_dev : nullptr, s->dd_last_send_l, s->dd_last_send_r);
+  if (lean) { s->dd_clean_counts = (int *)n_old_dev; s->dd_send_l = s->dd_last_send_l; s->dd_send_r = s->dd_last_send_r; }
   s->launches += 2;
   SW_CUDA(cudaGetLastError());
   return SWARM_OK;
@@ -263,6 +280,13 @@ __global__ void k_dd_wait(const unsigned long long *flag_left, const unsigned lo
       __nanosleep(200);
     }
   }
+}
+
+extern "C" int swarm_dd_set_lean(swarm_t *s, int32_t on) {
+  if (!s) return SWARM_ERR_INVALID;
+  s->dd_lean = on != 0;
+  s->dd_clean_counts = nullptr; s->dd_send_l = nullptr; s->dd_send_r = nullptr; s->dd_last_send_l = nullptr; s->dd_last_send_r = nullptr;
+  return SWARM_OK;
 }
 
 extern "C" int64_t swarm_dd_peer_region_bytes(const swarm_dd_geom_t *g) {

@@ -209,6 +209,7 @@ class DomainSwarm:
         self.counts_host = torch.zeros((2, 8), dtype=torch.int32).pin_memory()
         self.out = torch.zeros(self.cap, **f64)
         _lib.check(self.lib.swarm_reserve(self.h, self.cap))
+        _lib.check(self.lib.swarm_dd_set_lean(self.h, 1))   # the two halves alternate: counters are cleared by the merge itself
         self._peer_setup()
 
     def _peer_setup(self):
@@ -459,11 +460,11 @@ class DomainSwarm:
             _lib.check(self.lib.swarm_dd_obs_field(self.h, self.cap, self.counts[self.cur].data_ptr(), C.byref(a), self.plan["x_offset"], self.plan["box_x"], s3, b2,
                                                    int(decay), float(c0), float(c1), float(scale), int(bool(clip)),
                                                    int(bool(init_only)), self.out.data_ptr(), self._stream()))
-            red = self.sw.reduce_mean(self.out)      # slots past the live count were written as 0
-            tot = red[:1].clone()
+            red = self.sw.reduce_mean(self.out)      # slots past the live count were written as 0; a fresh 2-element tensor per call
             if defer:
-                self._deferred_sums.append(tot)
+                self._deferred_sums.append(red[:1])
                 return self.out, None
+            tot = red[:1].clone()
             self.transport.all_reduce_sum(tot)
         return self.out, torch.cat([tot, tot / float(self.n_global)])
 
