@@ -13,7 +13,7 @@ slice.  One bench "step" = one action slice of `SwarmEngine.integrate`:
     SubdividedVisionCones observable (range 10, half angle pi/2, 5 cones)  subdivided_vision_cones.py:83-258
     GradientSensing reward + its mean                                      gradient_sensing.py:92-150, trainer.py:92-95
 value  = N * 100 * K / (device time of K slices), inputs resident in HBM.
-e2e    = the same slice through the host-buffer C-ABI (swarm_set_actions_host -> run -> observable ->
+e2e    = the same slice through the host-buffer C-ABI (swarm_set_actions_host_2d -> run -> observable ->
          D2H of the observable and the reward mean), actions coming from pinned host memory.
 N > 1  : ensemble sharding -- every rank advances its own independent 100k-agent swarm (weak scaling,
          no data-path collective; torch.distributed only for the barrier and the max-over-ranks time).
@@ -302,7 +302,9 @@ class Rollout:
         sets = action_sets(n, 7 + seed)
         # device-resident action sets (value) and pinned host copies (e2e)
         self.act_dev = [(torch.from_numpy(f).to(d.dev), torch.from_numpy(np.ascontiguousarray(t.T)).to(d.dev)) for f, t in sets]
-        self.act_pin = [(torch.from_numpy(f).pin_memory(), torch.from_numpy(t).pin_memory()) for f, t in sets]
+        # a 2-D swarm: the host passes (f_swim, tau_z) per agent -- swarm_set_actions_host_2d (the x, y torque components are zero)
+        assert all(not t[:, :2].any() for _, t in sets)
+        self.act_pin = [(torch.from_numpy(f).pin_memory(), torch.from_numpy(np.ascontiguousarray(t[:, 2])).pin_memory()) for f, t in sets]
         self.obs_pin = torch.empty((n, VISION["n_cones"], 1), dtype=torch.float64).pin_memory()
         self.mean_pin = torch.empty(2, dtype=torch.float64).pin_memory()
         self.step_idx = 0
@@ -344,7 +346,7 @@ class Rollout:
 
         f, t = self.act_pin[k % len(self.act_pin)]
         d = self.d
-        _lib.check(d.lib.swarm_set_actions_host(d.h, C.c_void_p(f.data_ptr()), C.c_void_p(t.data_ptr()), d._stream()))
+        _lib.check(d.lib.swarm_set_actions_host_2d(d.h, C.c_void_p(f.data_ptr()), C.c_void_p(t.data_ptr()), d._stream()))
         obs, mean = self._physics_and_obs(False)
         self.obs_pin.copy_(obs, non_blocking=True)
         self.mean_pin.copy_(mean, non_blocking=True)

@@ -387,6 +387,10 @@ int swarm_policy_forward(swarm_t *s, const swarm_policy_t *net, const double *ob
 /* ---- host-buffer entry points (what a cgo/ctypes binding of the reference would call) --- */
 /* manage_forces: write f_swim and ext torque of every particle (espresso.py:1227-1235) */
 int swarm_set_actions_host(swarm_t *s, const double *f_swim_host, const double *torque3n_host, void *stream);
+/* the same for a 2-D swarm: only the z component of the torque turns a director in the plane (the x, y components the
+ * reference writes at espresso.py:1232 are zero there and never read by the 2-D kernels), so the host passes tau_z [n]:
+ * half the host -> device bytes, no de-interleave kernel */
+int swarm_set_actions_host_2d(swarm_t *s, const double *f_swim_host, const double *torque_z_host, void *stream);
 /* Measurement hook (no reference counterpart): DFMA throughput of the device with `ilp` (1, 4 or 8) independent chains per
  * thread -- the fp64 peak the roofline notes of DESIGN.md / BASELINE.md divide by.  out4: DFMA/s, ms, SM count, ilp used. */
 int swarm_microbench_dfma(int32_t device, int32_t ilp, int32_t iters, double out4[4]);

@@ -144,6 +144,7 @@ SYMBOLS = {
     "swarm_obs_field_mean_noalloc": (C.c_int, [_V, _V, C.c_int64, _DP, _DP, _V, C.c_int32, C.c_double, C.c_double, C.c_double, C.c_int32, _V, _V, _V]),
     "swarm_policy_forward": (C.c_int, [_V, C.POINTER(Policy), _V, _V, C.c_uint64, C.c_int32, _V, _V, _V, _V, _V, _V, _V]),
     "swarm_set_actions_host": (C.c_int, [_V, _V, _V, _V]),
+    "swarm_set_actions_host_2d": (C.c_int, [_V, _V, _V, _V]),
     "swarm_microbench_dfma": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, _DP]),
     "swarm_snapshot_dev": (C.c_int, [_V, _V, _V, _V, _V]),
     "swarm_get_particle_data_host": (C.c_int, [_V, _V, _V, _V, _V]),

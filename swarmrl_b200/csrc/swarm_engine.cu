@@ -1777,6 +1777,21 @@ extern "C" int swarm_set_actions_host(swarm_t *s, const double *f_swim_host, con
   return SWARM_OK;
 }
 
+// 2-D swarms: the torque of an action has one component that matters (espresso.py:1232 writes the 3-vector because ESPResSo
+// is 3-D; in the plane only tau_z turns the director, and the 2-D kernels read nothing else).  Half the host -> device bytes
+// of swarm_set_actions_host and no de-interleave kernel.
+extern "C" int swarm_set_actions_host_2d(swarm_t *s, const double *f_swim_host, const double *torque_z_host, void *stream) {
+  if (!s || !s->state_bound || !s->actions_bound) { sw_set_error("state and actions must be bound"); return SWARM_ERR_STATE; }
+  if (s->P.n_dims != 2) { sw_set_error("swarm_set_actions_host_2d needs a 2-D swarm"); return SWARM_ERR_INVALID; }
+  SW_CUDA(cudaSetDevice(s->cfg.device));
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long n = s->A.n;
+  if (n == 0) return SWARM_OK;
+  if (f_swim_host) SW_CUDA(cudaMemcpyAsync(s->A.f_swim, f_swim_host, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, st));
+  if (torque_z_host) SW_CUDA(cudaMemcpyAsync(s->A.tqz, torque_z_host, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, st));
+  return SWARM_OK;
+}
+
 // One frame of the trajectory (espresso.py:1110-1130: Unwrapped_Positions, Velocities, Directors, each (N, 3)) written
 // into DEVICE memory by one kernel on the caller's stream: the snapshot ring of the asynchronous trajectory writer
 // (swarmrl_b200/trajectory.py) is filled without touching the host; the D2H copy runs on the writer's own stream.

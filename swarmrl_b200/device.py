@@ -282,6 +282,13 @@ class DeviceSwarm:
         """manage_forces' writes through host buffers (espresso.py:1227-1235)."""
         f = np.ascontiguousarray(f_swim, dtype=np.float64)
         t = np.ascontiguousarray(torque, dtype=np.float64).reshape(-1, 3)
+        if self.n_dims == 2 and not t[:, :2].any():
+            # in the plane only tau_z matters: half the bytes, no de-interleave kernel (swarm_set_actions_host_2d)
+            tz = np.ascontiguousarray(t[:, 2])
+            self._hold = [f, tz]
+            _lib.check(self.lib.swarm_set_actions_host_2d(self.h, f.ctypes.data, tz.ctypes.data, self._stream()))
+            self.torch.cuda.current_stream(self.dev).synchronize()
+            return
         self._hold = [f, t]  # keep alive until the async copies have run
         _lib.check(self.lib.swarm_set_actions_host(self.h, f.ctypes.data, t.ctypes.data, self._stream()))
         self.torch.cuda.current_stream(self.dev).synchronize()

@@ -490,3 +490,38 @@ def test_config2_noise_statistics_over_32_replicas():
     # free-diffusion scale (collisions slow the swarm down, the first contacts of the jittered lattice push it apart)
     D = KT_300 / gt
     assert 0.5 * 4 * D * times[-1] * dt < msd_g[-1].mean() < 1.5 * 4 * D * times[-1] * dt
+
+
+def test_set_actions_host_2d_writes_what_the_three_vector_entry_writes():
+    """swarm_set_actions_host_2d (f_swim, tau_z per particle: half the host->device bytes of a 2-D slice) against
+    swarm_set_actions_host (espresso.py:1227-1235 writes a 3-vector torque); a 3-D swarm refuses it."""
+    import ctypes as C
+
+    from swarmrl_b200 import _lib
+    from swarmrl_b200.device import DeviceSwarm
+
+    rng = np.random.default_rng(2)
+    n, L = 3000, 200.0
+    sp, wca = species_for([1.0]), wca_for([1.0])
+    pos = jittered_lattice(n, L, 2, rng)
+    f = rng.uniform(0, 3, n)
+    tq = np.zeros((n, 3)); tq[:, 2] = rng.uniform(-1, 1, n)
+    got = []
+    for two_d in (False, True):
+        d = DeviceSwarm(2, (L,) * 3, True, 1e-3, 0.0, 1, sp, wca)
+        d.set_state(pos, np.zeros(n, dtype=np.int32), theta=np.zeros(n))
+        if two_d:
+            tz = np.ascontiguousarray(tq[:, 2])
+            _lib.check(d.lib.swarm_set_actions_host_2d(d.h, f.ctypes.data, tz.ctypes.data, d._stream()))
+        else:
+            _lib.check(d.lib.swarm_set_actions_host(d.h, f.ctypes.data, tq.ctypes.data, d._stream()))
+        d.synchronize()
+        d.run_checked(20, 0)
+        got.append((d.f_swim[:n].cpu().numpy(), d.torque[2, :n].cpu().numpy(), d.particle_data_host()[0], d.theta[:n].cpu().numpy()))
+    for a, b in zip(*got):
+        assert np.array_equal(a, b)
+    d3 = DeviceSwarm(3, (L,) * 3, True, 1e-3, 0.0, 1, sp, wca)
+    p3 = jittered_lattice(200, L, 3, rng)
+    q = np.zeros((200, 4)); q[:, 0] = 1.0
+    d3.set_state(p3, np.zeros(200, dtype=np.int32), quat=q)
+    assert d3.lib.swarm_set_actions_host_2d(d3.h, f.ctypes.data, f.ctypes.data, d3._stream()) != 0
