@@ -150,6 +150,7 @@ struct swarm {
   size_t vis_bytes = 0;
   long long vis_prev_n = -1;   // the bounding box of the previous vision call is usable for this n / range
   double vis_prev_range = 0.0;
+  bool cluster_ok = true;               // k_bd2d_cluster can be launched on this device (cleared by a failed launch)
   bool dd_lean = false;                 // swarm_dd_set_lean: counters are cleared by the merge's last kernel, not by memsets
   int *dd_clean_counts = nullptr;       //   the counts8 buffer that kernel cleared (the next merge's output)
   double *dd_send_l = nullptr, *dd_send_r = nullptr;            //   the send buffers whose record counts it cleared

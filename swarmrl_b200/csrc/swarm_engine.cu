@@ -612,7 +612,8 @@ __device__ __forceinline__ void grid_barrier64(unsigned long long *counter, unsi
 
 #include "swarm_bd2d.cuh"  // k_bd2d_resident: the hot kernel of the 2-D rollout
 #include "swarm_sort.cuh"  // spatial slot order (cell hash, counting sort, cell-start scan, permutation)
-#include "swarm_tiled.cuh" // k_bd2d_tiled: the same chunk on spatial CTA tiles, neighbourhood barrier instead of the grid barrier
+#include "swarm_tiled.cuh"
+#include "swarm_cluster.cuh" // k_bd2d_tiled: the same chunk on spatial CTA tiles, neighbourhood barrier instead of the grid barrier
 
 // ---------------------------------------------------------------------------------------------
 // one-launch-per-phase variant (SWARM_FLAG_NO_PERSISTENT): same device functions, kernel
@@ -1147,6 +1148,36 @@ static int sw_launch_resident(swarm *s, const RunArgs &R, cudaStream_t st, bool 
 
 
 // ---------------------------------------------------------------------------------------------
+// cluster kernel (swarm_cluster.cuh): small 2-D swarms on one thread-block cluster
+// ---------------------------------------------------------------------------------------------
+static bool sw_cluster_eligible(const swarm *s, const RunArgs &R) {
+  return s->persistent && s->P.n_dims == 2 && R.mode == MODE_BD && s->P.n_envs == 1 && s->A.n >= 1 && s->A.n <= SW_CL_MAXN &&
+         s->A.cap <= SW_CL_CAP && !s->A.gid && !s->A.okey && !s->A.n_dev && s->cluster_ok && s->tile.mode != 2 /* tiled kernel forced */ &&
+         !getenv("SWARM_B200_NO_CLUSTER");
+}
+
+template <bool NOISE>
+static int sw_launch_cluster(swarm *s, const RunArgs &R, cudaStream_t st, bool *done) {
+  auto kern = k_bd2d_cluster<NOISE>;
+  *done = false;
+  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SW_CL_DSM_BYTES) != cudaSuccess) {
+    cudaGetLastError();
+    s->cluster_ok = false;      // a device without clusters / the shared memory: the resident kernel takes over for good
+    return SWARM_OK;
+  }
+  DevParams P = s->P;
+  DevArrays A = s->A;
+  RunArgs Rr = R;
+  Rr.particles_per_cta = (int)((s->A.n + SW_CL_CTAS - 1) / SW_CL_CTAS);
+  kern<<<SW_CL_CTAS, SW_CL_THREADS, SW_CL_DSM_BYTES, st>>>(P, A, Rr);
+  if (cudaGetLastError() != cudaSuccess) { s->cluster_ok = false; return SWARM_OK; }
+  s->launches += 1;
+  s->list_space = 0;
+  *done = true;
+  return SWARM_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
 // tiled 2-D kernel (swarm_tiled.cuh): eligibility, spatial sort, launch
 // ---------------------------------------------------------------------------------------------
 #define SW_TILE_MIN_N 4096   // below this a swarm is a handful of CTAs and the grid barrier is cheap
@@ -1427,7 +1458,11 @@ static int sw_run_common(swarm *s, RunArgs R, cudaStream_t st) {
       done += Rc.n_steps;
       continue;
     }
-    if (sw_tile_eligible(s, Rc)) {
+    if (sw_cluster_eligible(s, Rc)) {
+      rc = noise ? sw_launch_cluster<true>(s, Rc, st, &done_resident) : sw_launch_cluster<false>(s, Rc, st, &done_resident);
+      if (rc) return rc;
+    }
+    if (!done_resident && sw_tile_eligible(s, Rc)) {
       rc = noise ? sw_launch_tiled<true>(s, Rc, st, &done_resident) : sw_launch_tiled<false>(s, Rc, st, &done_resident);
       if (rc) return rc;
     }
