@@ -525,3 +525,45 @@ def test_set_actions_host_2d_writes_what_the_three_vector_entry_writes():
     q = np.zeros((200, 4)); q[:, 0] = 1.0
     d3.set_state(p3, np.zeros(200, dtype=np.int32), quat=q)
     assert d3.lib.swarm_set_actions_host_2d(d3.h, f.ctypes.data, f.ctypes.data, d3._stream()) != 0
+
+
+@pytest.mark.parametrize("n,L,radii,walls", [(10, 1000.0, (1.0,), False), (100, 60.0, (1.0,), False), (1500, 150.0, (1.0, 1.5), False),
+                                             (2048, 170.0, (1.0,), True)])
+def test_cluster_kernel_is_the_resident_kernel_bit_for_bit(n, L, radii, walls):
+    """k_bd2d_cluster (one 8-CTA thread-block cluster: positions in distributed shared memory, hardware cluster barrier,
+    in-cluster rebuild -- all pairs up to 128 particles, a shared-memory cell list above) against k_bd2d_resident
+    (SWARM_B200_NO_CLUSTER=1) on the same noisy swarm, launches cut at odd and even steps: the same bits.  A missed pair in
+    the cluster kernel's Verlet lists would show as a different trajectory (two species, walls, 2 048 = the largest size)."""
+    import os
+
+    from swarmrl_b200.device import DeviceSwarm
+
+    rng = np.random.default_rng(8)
+    sp, wca = species_for(list(radii)), wca_for(list(radii))
+    pos = jittered_lattice(n, L, 2, rng) if n > 10 else np.c_[rng.uniform(100, 900, (n, 2)), np.zeros(n)]
+    th = rng.uniform(0, 2 * np.pi, n)
+    sidx = (np.arange(n) % len(radii)).astype(np.int32)
+    gt, gr = sp[0]["gamma_t"][0], sp[0]["gamma_r"][0]
+    wl = None
+    if walls:
+        wl = dict(sigma=np.array([2.0 * 2 ** (-1 / 6)]), eps=np.array([1.0]), cut=np.array([2.0]))
+    out = []
+    for no_cluster in (False, True):
+        if no_cluster:
+            os.environ["SWARM_B200_NO_CLUSTER"] = "1"
+        try:
+            d = DeviceSwarm(2, (L, L, L), not walls, 1e-3, KT_300, 42, sp, wca, walls=wl, skin=0.4)
+            d.set_state(pos, sidx, theta=th)
+            d.set_actions_host(np.full(n, 5.0 * gt), np.tile([0, 0, gr * 4 * np.pi / 180], (n, 1)))
+            step = 0
+            for m in (37, 100, 1):
+                st = d.run_checked(m, step)
+                assert st.steps_done == m and not st.overflow
+                step += m
+            p, v, e = d.particle_data_host()
+            out.append((p, v, e, int(st.rebuilds)))
+        finally:
+            os.environ.pop("SWARM_B200_NO_CLUSTER", None)
+    (p0, v0, e0, rb0), (p1, v1, e1, rb1) = out
+    assert np.array_equal(p0, p1) and np.array_equal(e0, e1) and np.array_equal(v0, v1)
+    assert rb0 >= 3 and rb1 >= 1      # the cluster kernel rebuilds at the start of each of the three launches
