@@ -1331,6 +1331,8 @@ static int sw_launch_tiled(swarm *s, const RunArgs &R, cudaStream_t st, bool *fi
   G.tag0 = t.tag_next;
   t.tag_next += 4ULL * (unsigned long long)R.n_steps + 16ULL;   // more than the rebuilds (and rolled-back ones) of this launch
   G.perm = t.perm; G.rim = (RimRec *)t.rim[0]; G.rim_stride = s->A.n_pad; G.ppc = ppc; G.k_init = 8; G.k_cap = SW_TILE_KMAX;
+  G.k_safety = 0.9;
+  if (const char *e = getenv("SWARM_B200_TILE_SAFETY")) { const double f = atof(e); if (f > 0.1 && f <= 0.95) G.k_safety = f; }   // 1.0 predicts the limit itself: nearly every period is rolled back
   if (const char *e = getenv("SWARM_B200_TILE_KCAP")) { const int k = atoi(e); if (k >= 1 && k <= SW_TILE_KMAX) G.k_cap = k; }
   G.flag0 = (unsigned int)((t.launches_total + 1) << 15);
   if (const char *e = getenv("SWARM_B200_TILE_KINIT")) { const int k = atoi(e); if (k >= 1 && k <= SW_TILE_KMAX) G.k_init = k; }

@@ -69,6 +69,7 @@ struct TileArgs {
   int ppc;                  // slots per CTA
   int k_init;               // first cadence when the handle has none yet
   int k_cap;                // upper bound of the cadence (SW_TILE_KMAX; lower for measurements: SWARM_B200_TILE_KCAP)
+  double k_safety;          // the next period = (steps the list lasted, extrapolated) x this factor (SWARM_B200_TILE_SAFETY)
   unsigned int flag0;       // flag of this launch's epoch 0: EVEN (flag parity = epoch parity = record slot) and above
                             // every flag of the previous launch (launch counter << 15; a launch runs < 2^15 epochs)
 };
@@ -528,7 +529,7 @@ __global__ void __launch_bounds__(SW_RES_MAXT, 1) k_bd2d_tiled(const __grid_cons
         // drift, conservative for diffusion, whose largest displacement grows like the square root of the time).
         double ratio = (dm > 0.0) ? sqrt(lim2 / dm) : 4.0;
         if (ratio > 4.0) ratio = 4.0;
-        long long Kn = (long long)((double)(since > 0 ? since : 1) * ratio * 0.9);
+        long long Kn = (long long)((double)(since > 0 ? since : 1) * ratio * G.k_safety);
         if (bad) {
           if (Kn > K / 2) Kn = K / 2;
           K = (int)(Kn < 1 ? 1 : Kn);
