@@ -95,3 +95,18 @@ def test_gloo_neighbour_transport(world):
         assert from_left == 10.0 * left + 2.0      # my left neighbour's send_r
         assert from_right == 10.0 * right + 1.0    # my right neighbour's send_l
         assert tot == world * (world + 1) / 2
+
+
+def test_slab_plan_widens_the_halo_by_the_observable_range():
+    """"per slice a wider halo" -- a per-agent observable of range R (vision cones) is exact for the
+    particles the integration needs only if the rank also holds everything within R of THEM."""
+    from swarmrl_b200.domain import slab_plan
+
+    base = slab_plan(1000.0, 4, 1, exchange_every=10, max_cut=2.0, margin=0.25)
+    wide = slab_plan(1000.0, 4, 1, exchange_every=10, max_cut=2.0, margin=0.25, halo_extra=12.5)
+    assert wide["halo"] == pytest.approx(base["halo"] + 12.5) and wide["halo_extra"] == 12.5 and base["halo_extra"] == 0.0
+    assert wide["x_offset"] == pytest.approx(wide["x0"] - wide["halo"])
+    with pytest.raises(ValueError):
+        slab_plan(100.0, 4, 0, exchange_every=2, max_cut=2.0, halo_extra=10.0)     # 25-wide slabs cannot hold two 15-wide halos
+    with pytest.raises(ValueError):
+        slab_plan(1000.0, 4, 0, exchange_every=2, max_cut=2.0, halo_extra=-1.0)
