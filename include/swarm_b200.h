@@ -229,7 +229,8 @@ int swarm_bind_count(swarm_t *s, const int32_t *n_dev);
 typedef struct {
   double slab_w;
   double halo;
-  int32_t n_aux;             /* user channels that travel with a particle (observable histories) */
+  int32_t n_aux;             /* channels that travel with a particle: observable histories (two per history), and vx, vy,
+                              * omega_z when the Langevin integrator runs on the decomposed swarm */
   int32_t cap;               /* record capacity of one exchange buffer */
   int32_t image_shift_left;  /* added to the periodic image count of records sent left (-1 on rank 0) */
   int32_t image_shift_right; /* ... sent right (+1 on the last rank) */
