@@ -252,3 +252,35 @@ def test_langevin_chunks_restart_with_a_force_recalculation():
         out.append(o.pos.copy())
     assert not np.array_equal(out[0], out[1])
     assert np.abs(out[0] - out[1]).max() < 1e-4
+
+
+def test_2d_brownian_step_takes_its_normals_as_documented():
+    """The noise rule of a 2-D Brownian step (swarm_math.cuh, orc_bd_steps): translation = pair 0 of the draw of step s
+    (g[0], g[1] of orc_gaussians(seed, id, s, 0)); rotation = pair 1 of the draw of the EVEN step s & ~1 -- its sine
+    (g[3]) on the even step, its cosine (g[2]) on the odd one.  Free particles (no force, no torque): every increment is
+    sigma x one of those normals, so the rule is pinned value by value; and sine / cosine of one pair are uncorrelated."""
+    from oracle import oracle
+
+    sp, wca = species_for([1.0]), wca_for([1.0])
+    n, dt, seed, step0 = 64, 1e-3, 42, 7      # an odd first step: its rotational normal comes from the draw of step 6
+    rng = np.random.default_rng(0)
+    pos = jittered_lattice(n, 2000.0, 2, rng)
+    o = OracleSwarm(2, (2000.0,) * 3, True, dt, KT_300, seed, sp, wca)
+    o.set_state(pos, np.zeros(n, dtype=np.int32), theta=np.zeros(n))
+    gt, gr = sp[0]["gamma_t"][0], sp[0]["gamma_r"][0]
+    sg_t, sg_r = np.sqrt(2 * KT_300 * dt / gt), np.sqrt(2 * KT_300 * dt / gr)
+    for s in range(step0, step0 + 6):
+        x0, th0 = o.pos.copy(), np.arctan2(o.directors[:, 1], o.directors[:, 0])
+        o.bd_steps(s, 1)
+        th1 = np.arctan2(o.directors[:, 1], o.directors[:, 0])
+        g_own = np.array([oracle.gaussians(seed, i, s, 0) for i in range(n)])
+        g_even = np.array([oracle.gaussians(seed, i, s & ~1, 0) for i in range(n)])
+        assert np.allclose(o.pos[:, 0] - x0[:, 0], sg_t * g_own[:, 0], rtol=0, atol=1e-9 * sg_t)
+        assert np.allclose(o.pos[:, 1] - x0[:, 1], sg_t * g_own[:, 1], rtol=0, atol=1e-9 * sg_t)
+        want = sg_r * (g_even[:, 2] if s & 1 else g_even[:, 3])
+        dth = (th1 - th0 + np.pi) % (2 * np.pi) - np.pi
+        assert np.allclose(dth, want, rtol=0, atol=1e-9)
+    g = np.array([oracle.gaussians(seed, i, 2 * k, 0) for i in range(200) for k in range(50)])
+    c = np.corrcoef(g[:, 2], g[:, 3])[0, 1]
+    assert abs(c) < 4.0 / np.sqrt(len(g))
+    assert abs(g[:, 2].var() - 1) < 0.06 and abs(g[:, 3].var() - 1) < 0.06
