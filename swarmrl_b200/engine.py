@@ -758,6 +758,20 @@ class SwarmEngine(Engine):
         for val in self.traj_holder.values():
             val.clear()
 
+    def reward_means(self, agent):
+        """Device tensor (n_evaluations, 2) of the [sum, mean] of every reward evaluation a `DeviceAgent(reward_mean=True)`
+        collected (trainers/trainer.py:92-95 takes the mean on the host).  On a decomposed swarm the per-rank sums are
+        reduced over the ranks here, in ONE collective for the whole rollout -- every rank must call it."""
+        import torch
+
+        means = list(agent.reward_means)
+        be = self._backend
+        if getattr(be, "is_domain", False):
+            return be.all_reduce_means(means)
+        if not means:
+            return torch.zeros((0, 2), dtype=torch.float64)
+        return torch.stack(means)
+
     # ---------------------------------------------------------------- read-out
     def _fetch_host_state(self):
         if self._backend is None:

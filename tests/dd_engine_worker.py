@@ -72,12 +72,8 @@ def rollout(tmp, domain, thermostat="brownian"):
     e.finalize()
     data = e.get_particle_data()
     be = e._backend
-    if domain is not None:
-        means = be.all_reduce_means(agent.reward_means).cpu().numpy()
-        extra = dict(exchanges=be.dd.exchanges, owned=be.dd.n_owned)
-    else:
-        means = np.array([m.cpu().numpy() for m in agent.reward_means])
-        extra = dict(exchanges=0, owned=CASE["n"])
+    means = e.reward_means(agent).cpu().numpy()      # one collective on a decomposed swarm, a stack on one GPU
+    extra = dict(exchanges=be.dd.exchanges, owned=be.dd.n_owned) if domain is not None else dict(exchanges=0, owned=CASE["n"])
     return dict(pos=data["Unwrapped_Positions"], dirs=data["Directors"], vel=data["Velocities"], means=means, step_idx=e.step_idx, **extra)
 
 
