@@ -70,3 +70,24 @@ def test_product_never_imports_the_oracle():
         if f.suffix in (".py", ".cu", ".cuh", ".h"):
             txt = f.read_text()
             assert "import oracle" not in txt and "from oracle" not in txt and "swarm_oracle" not in txt, f
+
+
+def test_cluster_kernel_compiles_to_the_hardware_cluster_barrier():
+    """k_bd2d_cluster (csrc/swarm_cluster.cuh) must reach the thread-block-cluster hardware, not a software barrier: its SASS
+    for sm_100a holds the cluster barrier's arrive / wait pair (UCGABAR_ARV / UCGABAR_WAIT) and the library is built for
+    sm_100a only.  Needs cuobjdump (part of the CUDA toolkit the build uses), no GPU."""
+    import shutil
+    import subprocess
+
+    import pytest
+
+    from swarmrl_b200 import _lib
+
+    tool = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not pathlib.Path(tool).exists():
+        pytest.skip("cuobjdump not found")
+    elf = subprocess.run([tool, "-lelf", str(_lib.LIB_PATH)], capture_output=True, text=True).stdout
+    assert "sm_100a" in elf and "sm_90" not in elf and "sm_80" not in elf
+    sass = subprocess.run([tool, "-sass", "-fun", "_Z14k_bd2d_clusterILb1EEv9DevParams9DevArrays7RunArgs", str(_lib.LIB_PATH)],
+                          capture_output=True, text=True).stdout
+    assert sass.count("UCGABAR_ARV") >= 2 and sass.count("UCGABAR_WAIT") >= 2
